@@ -1,0 +1,383 @@
+// gemm.cu — K2/K6: persistent, warp-specialised bf16 GEMM on tcgen05 for the four linears of
+// the decoder layer and their gradients (hybrid_model.py:125-131,157-163,497-511).
+//
+//   warp 0      TMA producer: one lane streams 128xBK A tiles and BNxBK B tiles into a
+//               4..6-stage shared-memory ring (128-byte swizzle), signalling `full` mbarriers
+//   warp 1      MMA issuer: one lane issues tcgen05.mma (M=128, N=BN, K=16) into one of two
+//               TMEM accumulators (2 x BN fp32 columns), tcgen05.commit frees ring slots
+//   warps 2..5  epilogue: tcgen05.ld the finished accumulator (one row per thread), apply
+//               bias / GELU / GELU' / accumulate, store bf16 or fp32 — overlapped with the
+//               next tile's main loop through the second accumulator
+//
+// Operands may be K-major or MN-major in memory (Paddle's [in,out] weights make the forward
+// B operand MN-major and the weight gradient MN-major on both sides); the shared-memory
+// descriptors carry the difference, so no transposed copies are ever made.
+#include "common.cuh"
+#include "tc5.cuh"
+
+namespace fx {
+namespace gemm {
+
+using namespace tc5;
+
+constexpr int BM = 128;
+constexpr int BK = 64;  // 64 bf16 = 128 B = one swizzle row
+constexpr int NUM_THREADS = 192;
+constexpr int A_STAGE_BYTES = BM * BK * 2;
+constexpr int CHUNK_BYTES = BK * 128;  // one 64-wide MN chunk of an MN-major operand
+
+struct Params {
+  int M, N, K;
+  int a_mn, b_mn;
+  void* C;
+  int ldc, c_f32, accumulate;
+  int epi;
+  const __nv_bfloat16* bias;
+  __nv_bfloat16* aux;
+  int ldaux;
+  int num_m, num_n, num_tiles, num_kb;
+};
+
+template <int BN>
+struct Cfg {
+  static constexpr int B_STAGE_BYTES = BN * BK * 2;
+  static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+  static constexpr int STAGES = BN == 256 ? 4 : 6;
+  static constexpr int BAR_BYTES = 256;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + 1024;
+  static constexpr int TMEM_COLS = 2 * BN;
+};
+
+__device__ __forceinline__ void tile_coords(const Params& p, int tile, int& m_blk, int& n_blk) {
+  constexpr int GROUP = 8;  // 8 M-blocks share each B tile while it is hot in L2
+  const int per_group = GROUP * p.num_n;
+  const int g = tile / per_group;
+  const int first_m = g * GROUP;
+  const int gsize = min(GROUP, p.num_m - first_m);
+  const int r = tile - g * per_group;
+  m_blk = first_m + r % gsize;
+  n_blk = r / gsize;
+}
+
+__device__ __forceinline__ float gelu_tanh(float z) {
+  // 0.5 z (1 + tanh(u)) == z * sigmoid(2u),  u = sqrt(2/pi) (z + 0.044715 z^3)
+  const float u = 0.7978845608028654f * z * (1.0f + 0.044715f * z * z);
+  return z / (1.0f + __expf(-2.0f * u));
+}
+__device__ __forceinline__ float gelu_tanh_grad(float z) {
+  const float z2 = z * z;
+  const float u = 0.7978845608028654f * z * (1.0f + 0.044715f * z2);
+  const float s = 1.0f / (1.0f + __expf(-2.0f * u));  // = 0.5 (1 + tanh u)
+  const float du = 0.7978845608028654f * (1.0f + 3.0f * 0.044715f * z2);
+  // d/dz [z s(2u)] = s + z * 2 s (1 - s) du
+  return s + 2.0f * z * s * (1.0f - s) * du;
+}
+
+// One thread owns 32 consecutive columns [col0, col0+32) of output row `row`.
+__device__ __forceinline__ void epilogue_store(const Params& p, int row, int col0,
+                                               const uint32_t (&r)[32]) {
+  if (col0 >= p.N) return;
+  const int ncols = min(32, p.N - col0);  // multiple of 8
+  float v[32];
+#pragma unroll
+  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+
+  if (p.epi == FX_EPI_BIAS || p.epi == FX_EPI_BIAS_GELU) {
+    const uint4* bp = reinterpret_cast<const uint4*>(p.bias + col0);
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      if (g * 8 < ncols) {
+        const uint4 b = __ldg(bp + g);
+        const uint32_t w[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          v[g * 8 + 2 * j] += bf16_lo(w[j]);
+          v[g * 8 + 2 * j + 1] += bf16_hi(w[j]);
+        }
+      }
+    }
+  }
+  if (row >= p.M) return;
+
+  if (p.epi == FX_EPI_BIAS_GELU) {
+    if (p.aux != nullptr) {
+      uint4* zp = reinterpret_cast<uint4*>(p.aux + (size_t)row * p.ldaux + col0);
+#pragma unroll
+      for (int g = 0; g < 4; ++g)
+        if (g * 8 < ncols)
+          zp[g] = make_uint4(pack_bf16(v[g * 8 + 0], v[g * 8 + 1]), pack_bf16(v[g * 8 + 2], v[g * 8 + 3]),
+                             pack_bf16(v[g * 8 + 4], v[g * 8 + 5]), pack_bf16(v[g * 8 + 6], v[g * 8 + 7]));
+    }
+    // the activation is applied to the bf16-rounded pre-activation, exactly what a
+    // non-fused linear -> gelu pair (hybrid_model.py:558-559) would see
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = gelu_tanh(__bfloat162float(__float2bfloat16_rn(v[i])));
+  } else if (p.epi == FX_EPI_DGELU) {
+    const uint4* zp = reinterpret_cast<const uint4*>(p.aux + (size_t)row * p.ldaux + col0);
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      if (g * 8 < ncols) {
+        const uint4 z = __ldg(zp + g);
+        const uint32_t w[4] = {z.x, z.y, z.z, z.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          v[g * 8 + 2 * j] *= gelu_tanh_grad(bf16_lo(w[j]));
+          v[g * 8 + 2 * j + 1] *= gelu_tanh_grad(bf16_hi(w[j]));
+        }
+      }
+    }
+  }
+
+  if (p.c_f32) {
+    float4* cp = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.C) + (size_t)row * p.ldc + col0);
+#pragma unroll
+    for (int g = 0; g < 8; ++g) {
+      if (g * 4 < ncols) {
+        float4 o = make_float4(v[g * 4], v[g * 4 + 1], v[g * 4 + 2], v[g * 4 + 3]);
+        if (p.accumulate) {
+          const float4 old = cp[g];
+          o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
+        }
+        cp[g] = o;
+      }
+    }
+  } else {
+    uint4* cp = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.C) + (size_t)row * p.ldc + col0);
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      if (g * 8 < ncols) {
+        if (p.accumulate) {
+          const uint4 old = cp[g];
+          const uint32_t w[4] = {old.x, old.y, old.z, old.w};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            v[g * 8 + 2 * j] += bf16_lo(w[j]);
+            v[g * 8 + 2 * j + 1] += bf16_hi(w[j]);
+          }
+        }
+        cp[g] = make_uint4(pack_bf16(v[g * 8 + 0], v[g * 8 + 1]), pack_bf16(v[g * 8 + 2], v[g * 8 + 3]),
+                           pack_bf16(v[g * 8 + 4], v[g * 8 + 5]), pack_bf16(v[g * 8 + 6], v[g * 8 + 7]));
+      }
+    }
+  }
+}
+
+template <int BN>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+            const Params p) {
+  using C = Cfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + C::STAGES * C::STAGE_BYTES);
+  uint64_t* empty = full + C::STAGES;
+  uint64_t* tfull = empty + C::STAGES;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tma_a);
+    tma_prefetch_desc(&tma_b);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int i = 0; i < C::STAGES; ++i) {
+        mbar_init(&full[i], 1);
+        mbar_init(&empty[i], 1);
+      }
+      for (int i = 0; i < 2; ++i) {
+        mbar_init(&tfull[i], 1);
+        mbar_init(&tempty[i], 4);
+      }
+      mbar_fence_init();
+    }
+    __syncwarp();
+    tmem_alloc<C::TMEM_COLS>(tmem_slot);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ---------------------------------------------------------------- TMA producer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+        int m_blk, n_blk;
+        tile_coords(p, tile, m_blk, n_blk);
+        const int m0 = m_blk * BM, n0 = n_blk * BN;
+        for (int kb = 0; kb < p.num_kb; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1, 1);
+          mbar_expect_tx(&full[stage], C::STAGE_BYTES);
+          uint8_t* sa = smem + stage * C::STAGE_BYTES;
+          uint8_t* sb = sa + A_STAGE_BYTES;
+          const int k0 = kb * BK;
+          if (!p.a_mn) {
+            tma_load_2d(sa, &tma_a, &full[stage], k0, m0);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BM / 64; ++j)
+              tma_load_2d(sa + j * CHUNK_BYTES, &tma_a, &full[stage], m0 + j * 64, k0);
+          }
+          if (!p.b_mn) {
+            tma_load_2d(sb, &tma_b, &full[stage], k0, n0);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j)
+              tma_load_2d(sb + j * CHUNK_BYTES, &tma_b, &full[stage], n0 + j * 64, k0);
+          }
+          if (++stage == C::STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ---------------------------------------------------------------- MMA issuer
+    const uint32_t idesc = instr_desc_bf16(BM, BN, (uint32_t)p.a_mn, (uint32_t)p.b_mn);
+    int stage = 0;
+    uint32_t phase = 0;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+      mbar_wait(&tempty[acc], acc_phase ^ 1, 2);
+      tc_fence_after();
+      const uint32_t tmem_d = tmem_base + acc * BN;
+      for (int kb = 0; kb < p.num_kb; ++kb) {
+        mbar_wait(&full[stage], phase, 3);
+        tc_fence_after();
+        if (lane == 0) {
+          const uint32_t sa = smem_u32(smem + stage * C::STAGE_BYTES);
+          const uint32_t sb = sa + A_STAGE_BYTES;
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            const uint64_t da = p.a_mn ? smem_desc_sw128(sa + k * 16 * 128, CHUNK_BYTES, 1024)
+                                       : smem_desc_sw128(sa + k * 32, 0, 1024);
+            const uint64_t db = p.b_mn ? smem_desc_sw128(sb + k * 16 * 128, CHUNK_BYTES, 1024)
+                                       : smem_desc_sw128(sb + k * 32, 0, 1024);
+            umma_ss(tmem_d, da, db, idesc, (kb | k) != 0);
+          }
+          umma_commit(&empty[stage]);
+          if (kb == p.num_kb - 1) umma_commit(&tfull[acc]);
+        }
+        __syncwarp();
+        if (++stage == C::STAGES) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1;
+    }
+  } else {
+    // ---------------------------------------------------------------- epilogue
+    const int q = warp & 3;  // TMEM lane quarter this warp may read
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+      int m_blk, n_blk;
+      tile_coords(p, tile, m_blk, n_blk);
+      const int row = m_blk * BM + q * 32 + lane;
+      const int n0 = n_blk * BN;
+      mbar_wait(&tfull[acc], acc_phase, 4);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(taddr + c * 32, r);
+        tmem_ld_wait();
+        epilogue_store(p, row, n0 + c * 32, r);
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty[acc]);
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<C::TMEM_COLS>(tmem_base);
+}
+
+template <int BN>
+static int launch(cudaStream_t stream, const CUtensorMap& ta, const CUtensorMap& tb, Params& p) {
+  using C = Cfg<BN>;
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  FX_CUDA(cudaGetDevice(&dev));
+  if (dev < 64 && !attr_set[dev]) {
+    FX_CUDA(cudaFuncSetAttribute(gemm_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 C::SMEM_BYTES));
+    attr_set[dev] = true;
+  }
+  p.num_m = ceil_div(p.M, BM);
+  p.num_n = ceil_div(p.N, BN);
+  p.num_tiles = p.num_m * p.num_n;
+  p.num_kb = ceil_div(p.K, BK);
+  const int grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();
+  gemm_kernel<BN><<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(ta, tb, p);
+  FX_LAUNCH_CHECK();
+  return FX_OK;
+}
+
+}  // namespace gemm
+}  // namespace fx
+
+extern "C" int fx_gemm_bf16(void* stream, int trans_a, int trans_b, int M, int N, int K,
+                            const void* A, int lda, const void* B, int ldb, void* C, int ldc,
+                            int c_dtype, int accumulate, int epilogue, const void* bias, void* aux,
+                            int ldaux) {
+  using namespace fx;
+  FX_CHECK_ARG(M > 0 && N > 0 && K > 0, "fx_gemm_bf16: M, N, K must be positive (got %d %d %d)", M, N, K);
+  FX_CHECK_ARG(M % 8 == 0 && N % 8 == 0 && K % 8 == 0,
+               "fx_gemm_bf16: M, N, K must be multiples of 8 (got %d %d %d)", M, N, K);
+  FX_CHECK_ARG(A && B && C, "fx_gemm_bf16: null operand");
+  FX_CHECK_ARG(lda % 8 == 0 && ldb % 8 == 0 && ldc % 8 == 0, "fx_gemm_bf16: leading dims must be multiples of 8");
+  FX_CHECK_ARG(lda >= (trans_a ? M : K) && ldb >= (trans_b ? K : N) && ldc >= N,
+               "fx_gemm_bf16: leading dimension smaller than the row length");
+  FX_CHECK_ARG(c_dtype == FX_BF16 || c_dtype == FX_F32, "fx_gemm_bf16: bad c_dtype %d", c_dtype);
+  FX_CHECK_ARG(epilogue >= FX_EPI_NONE && epilogue <= FX_EPI_DGELU, "fx_gemm_bf16: bad epilogue %d", epilogue);
+  FX_CHECK_ARG(!(epilogue == FX_EPI_BIAS || epilogue == FX_EPI_BIAS_GELU) || bias,
+               "fx_gemm_bf16: epilogue needs a bias");
+  FX_CHECK_ARG(epilogue != FX_EPI_DGELU || aux, "fx_gemm_bf16: FX_EPI_DGELU needs aux");
+  FX_CHECK_ARG(!aux || (ldaux % 8 == 0 && ldaux >= N), "fx_gemm_bf16: bad ldaux %d", ldaux);
+  FX_CHECK_ARG(((uintptr_t)A | (uintptr_t)B | (uintptr_t)C | (uintptr_t)bias | (uintptr_t)aux) % 16 == 0,
+               "fx_gemm_bf16: pointers must be 16-byte aligned");
+
+  const int sms = num_sms();
+  auto cost = [&](int bn) {
+    const long tiles = (long)ceil_div(M, gemm::BM) * ceil_div(N, bn);
+    return ((tiles + sms - 1) / sms) * bn;
+  };
+  const int BN = (N > 128 && cost(256) <= cost(128)) ? 256 : 128;
+
+  CUtensorMap ta, tb;
+  int rc;
+  if (!trans_a) rc = make_tma_bf16_2d(&ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda * 2, 64, gemm::BM);
+  else rc = make_tma_bf16_2d(&ta, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda * 2, 64, gemm::BK);
+  if (rc) return rc;
+  if (trans_b) rc = make_tma_bf16_2d(&tb, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb * 2, 64, BN);
+  else rc = make_tma_bf16_2d(&tb, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb * 2, 64, gemm::BK);
+  if (rc) return rc;
+
+  gemm::Params p{};
+  p.M = M; p.N = N; p.K = K;
+  p.a_mn = trans_a ? 1 : 0;
+  p.b_mn = trans_b ? 0 : 1;
+  p.C = C; p.ldc = ldc; p.c_f32 = (c_dtype == FX_F32); p.accumulate = accumulate ? 1 : 0;
+  p.epi = epilogue;
+  p.bias = static_cast<const __nv_bfloat16*>(bias);
+  p.aux = static_cast<__nv_bfloat16*>(aux);
+  p.ldaux = ldaux;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  return BN == 256 ? gemm::launch<256>(st, ta, tb, p) : gemm::launch<128>(st, ta, tb, p);
+}

@@ -1,0 +1,176 @@
+"""Raw operator calls: torch tensors in, C-ABI calls out.
+
+torch is plumbing here (device memory, the current stream); every function hands raw device
+pointers to libfleetx_b200.so. Nothing in this module computes on the host.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _lib
+from ._lib import FX_BF16, FX_EPI_BIAS, FX_EPI_BIAS_GELU, FX_EPI_DGELU, FX_EPI_NONE, FX_F32, check
+
+__all__ = [
+    "layernorm_fwd", "layernorm_bwd", "bias_dropout_residual_fwd", "bias_dropout_residual_bwd",
+    "colsum", "gemm", "attn_causal_fwd", "attn_causal_bwd",
+    "FX_EPI_NONE", "FX_EPI_BIAS", "FX_EPI_BIAS_GELU", "FX_EPI_DGELU",
+]
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _p(t) -> int | None:
+    return None if t is None else t.data_ptr()
+
+
+def _need(t: torch.Tensor, dtype, name: str) -> torch.Tensor:
+    if not t.is_cuda:
+        raise _lib.FleetXError(f"{name}: expected a CUDA tensor (there is no CPU path)")
+    if t.dtype != dtype:
+        raise _lib.FleetXError(f"{name}: expected {dtype}, got {t.dtype}")
+    if not t.is_contiguous():
+        raise _lib.FleetXError(f"{name}: expected a contiguous tensor")
+    return t
+
+
+_ws_cache: dict = {}
+
+
+def _workspace(nbytes: int, device) -> torch.Tensor:
+    """Per-device, per-stream scratch buffer, grown on demand (caller-owned per the ABI)."""
+    key = (device, torch.cuda.current_stream(device).cuda_stream)
+    buf = _ws_cache.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
+        _ws_cache[key] = buf
+    return buf
+
+
+# ------------------------------------------------------------------------------- LayerNorm
+def layernorm_fwd(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float = 1e-5):
+    h = x.shape[-1]
+    x2 = _need(x, torch.bfloat16, "x").view(-1, h)
+    rows = x2.shape[0]
+    _need(gamma, torch.float32, "gamma"), _need(beta, torch.float32, "beta")
+    y = torch.empty_like(x2)
+    mean = torch.empty(rows, dtype=torch.float32, device=x.device)
+    rstd = torch.empty(rows, dtype=torch.float32, device=x.device)
+    check(_lib.lib().fx_layernorm_fwd(_stream(), _p(x2), _p(gamma), _p(beta), _p(y), _p(mean), _p(rstd),
+                                      rows, h, float(eps)), "fx_layernorm_fwd")
+    return y.view(x.shape), mean, rstd
+
+
+def layernorm_bwd(dy, x, gamma, mean, rstd, dresidual=None):
+    h = x.shape[-1]
+    x2 = _need(x, torch.bfloat16, "x").view(-1, h)
+    dy2 = _need(dy, torch.bfloat16, "dy").view(-1, h)
+    rows = x2.shape[0]
+    dr = None if dresidual is None else _need(dresidual, torch.bfloat16, "dresidual")
+    dx = torch.empty_like(x2)
+    dgamma = torch.empty(h, dtype=torch.float32, device=x.device)
+    dbeta = torch.empty(h, dtype=torch.float32, device=x.device)
+    ws = _workspace(_lib.lib().fx_layernorm_bwd_workspace_bytes(rows, h), x.device)
+    check(_lib.lib().fx_layernorm_bwd(_stream(), _p(dy2), _p(x2), _p(gamma), _p(mean), _p(rstd), _p(dr),
+                                      _p(dx), _p(dgamma), _p(dbeta), _p(ws), rows, h), "fx_layernorm_bwd")
+    return dx.view(x.shape), dgamma, dbeta
+
+
+# ------------------------------------------------------------------------------- dropout
+def bias_dropout_residual_fwd(y, bias, residual, p: float, seed: int, offset: int,
+                              mask_in=None, return_mask: bool = False):
+    h = y.shape[-1]
+    y2 = _need(y, torch.bfloat16, "y").view(-1, h)
+    r2 = _need(residual, torch.bfloat16, "residual").view(-1, h)
+    if bias is not None:
+        _need(bias, torch.bfloat16, "bias")
+    if mask_in is not None:
+        _need(mask_in, torch.uint8, "mask_in")
+    out = torch.empty_like(y2)
+    mask_out = torch.empty(y2.shape, dtype=torch.uint8, device=y.device) if return_mask else None
+    check(_lib.lib().fx_bias_dropout_residual_fwd(_stream(), _p(y2), _p(bias), _p(r2), _p(out), y2.shape[0], h,
+                                                  float(p), int(seed), int(offset), _p(mask_in), _p(mask_out)),
+          "fx_bias_dropout_residual_fwd")
+    out = out.view(y.shape)
+    return (out, mask_out.view(y.shape)) if return_mask else out
+
+
+def bias_dropout_residual_bwd(dout, p: float, seed: int, offset: int, mask_in=None):
+    h = dout.shape[-1]
+    d2 = _need(dout, torch.bfloat16, "dout").view(-1, h)
+    if mask_in is not None:
+        _need(mask_in, torch.uint8, "mask_in")
+    dy = torch.empty_like(d2)
+    check(_lib.lib().fx_bias_dropout_residual_bwd(_stream(), _p(d2), _p(dy), d2.shape[0], h, float(p),
+                                                  int(seed), int(offset), _p(mask_in)),
+          "fx_bias_dropout_residual_bwd")
+    return dy.view(dout.shape)
+
+
+def colsum(x: torch.Tensor, out_dtype=torch.bfloat16) -> torch.Tensor:
+    n = x.shape[-1]
+    x2 = _need(x, torch.bfloat16, "x").view(-1, n)
+    rows = x2.shape[0]
+    out = torch.empty(n, dtype=out_dtype, device=x.device)
+    ws = _workspace(_lib.lib().fx_colsum_workspace_bytes(rows, n), x.device)
+    check(_lib.lib().fx_colsum_bf16(_stream(), _p(x2), n, _p(out), FX_F32 if out_dtype == torch.float32 else FX_BF16,
+                                    _p(ws), rows, n), "fx_colsum_bf16")
+    return out
+
+
+# ------------------------------------------------------------------------------- GEMM
+def gemm(a: torch.Tensor, b: torch.Tensor, *, trans_a: bool = False, trans_b: bool = False,
+         out: torch.Tensor | None = None, out_dtype=torch.bfloat16, accumulate: bool = False,
+         epilogue: int = FX_EPI_NONE, bias=None, aux=None) -> torch.Tensor:
+    """C[M,N] = op(A) · op(B); a, b are 2-D contiguous bf16 (see fx_gemm_bf16 for the layouts)."""
+    _need(a, torch.bfloat16, "a"), _need(b, torch.bfloat16, "b")
+    if a.dim() != 2 or b.dim() != 2:
+        raise _lib.FleetXError("gemm: operands must be 2-D")
+    M, K = (a.shape[1], a.shape[0]) if trans_a else (a.shape[0], a.shape[1])
+    Kb, N = (b.shape[1], b.shape[0]) if trans_b else (b.shape[0], b.shape[1])
+    if K != Kb:
+        raise _lib.FleetXError(f"gemm: contraction mismatch {K} vs {Kb}")
+    if out is None:
+        if accumulate:
+            raise _lib.FleetXError("gemm: accumulate needs an existing output")
+        out = torch.empty(M, N, dtype=out_dtype, device=a.device)
+    c_dtype = FX_F32 if out.dtype == torch.float32 else FX_BF16
+    if out.dtype not in (torch.float32, torch.bfloat16) or not out.is_contiguous() or tuple(out.shape) != (M, N):
+        raise _lib.FleetXError("gemm: bad output tensor")
+    if bias is not None:
+        _need(bias, torch.bfloat16, "bias")
+    if aux is not None:
+        _need(aux, torch.bfloat16, "aux")
+    check(_lib.lib().fx_gemm_bf16(_stream(), int(trans_a), int(trans_b), M, N, K, _p(a), a.shape[1], _p(b),
+                                  b.shape[1], _p(out), N, c_dtype, int(accumulate), int(epilogue), _p(bias),
+                                  _p(aux), N if aux is not None else 0), "fx_gemm_bf16")
+    return out
+
+
+# ------------------------------------------------------------------------------- attention
+def attn_causal_fwd(qkv: torch.Tensor, nh: int, hd: int, scale: float, p_drop: float = 0.0,
+                    seed: int = 0, offset: int = 0):
+    """qkv: bf16 [b, s, nh*3*hd] (packed per head q|k|v). Returns out [b, s, nh*hd], lse [b, nh, s]."""
+    _need(qkv, torch.bfloat16, "qkv")
+    b, s = qkv.shape[0], qkv.shape[1]
+    if qkv.numel() != b * s * nh * 3 * hd:
+        raise _lib.FleetXError("attn_causal_fwd: qkv shape does not match (nh, hd)")
+    out = torch.empty(b, s, nh * hd, dtype=torch.bfloat16, device=qkv.device)
+    lse = torch.empty(b, nh, s, dtype=torch.float32, device=qkv.device)
+    check(_lib.lib().fx_attn_causal_fwd(_stream(), _p(qkv), _p(out), _p(lse), b, s, nh, hd, float(scale),
+                                        float(p_drop), int(seed), int(offset)), "fx_attn_causal_fwd")
+    return out, lse
+
+
+def attn_causal_bwd(dout, qkv, out, lse, nh: int, hd: int, scale: float, p_drop: float = 0.0,
+                    seed: int = 0, offset: int = 0):
+    _need(dout, torch.bfloat16, "dout"), _need(qkv, torch.bfloat16, "qkv"), _need(out, torch.bfloat16, "out")
+    _need(lse, torch.float32, "lse")
+    b, s = qkv.shape[0], qkv.shape[1]
+    dqkv = torch.empty_like(qkv)
+    ws = _workspace(_lib.lib().fx_attn_causal_bwd_workspace_bytes(b, s, nh, hd), qkv.device)
+    check(_lib.lib().fx_attn_causal_bwd(_stream(), _p(dout), _p(qkv), _p(out), _p(lse), _p(dqkv), _p(ws), b, s,
+                                        nh, hd, float(scale), float(p_drop), int(seed), int(offset)),
+          "fx_attn_causal_bwd")
+    return dqkv

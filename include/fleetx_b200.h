@@ -1,0 +1,118 @@
+/* fleetx_b200.h — C ABI of libfleetx_b200.so
+ *
+ * B200 (sm_100a) kernels for ONE path of PaddleFleetX (gongweibao/FleetX): the GPT hybrid-
+ * parallel TransformerDecoderLayer, forward and backward
+ * (ppfleetx/models/language_model/gpt/dygraph/hybrid_model.py:69-347, 439-571).
+ *
+ * The reference has no FFI for this path: its layer is Python over Paddle ops. This header is
+ * therefore the boundary a Paddle custom op (PD_BUILD_OP), a ctypes stub or any other host would
+ * bind; every entry point names the reference lines whose arithmetic it replaces.
+ *
+ * Conventions
+ *  - plain pointers and sizes; all tensor pointers are DEVICE pointers unless a name says host;
+ *  - `stream` is a cudaStream_t passed as void*; calls enqueue work and return without syncing;
+ *  - activations / linear weights / linear biases are bf16, LayerNorm gamma/beta and all
+ *    statistics are fp32; matrices are row-major; linear weights use Paddle's [in, out] layout;
+ *  - the caller owns every buffer, including workspaces (sizes from the *_workspace_bytes
+ *    functions); nothing is retained after return;
+ *  - return value: FX_OK (0) or a negative FX_ERR_*; fx_last_error() gives thread-local text;
+ *  - there is no CPU fallback: without a CUDA device every compute entry point fails.
+ */
+#ifndef FLEETX_B200_H_
+#define FLEETX_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum {
+  FX_OK = 0,
+  FX_ERR_INVALID_ARGUMENT = -1,
+  FX_ERR_CUDA = -2,
+  FX_ERR_UNSUPPORTED = -3,
+  FX_ERR_COMM = -4
+};
+
+enum { FX_BF16 = 0, FX_F32 = 1 };
+
+/* GEMM epilogues (fused into the TMEM drain of fx_gemm_bf16). */
+enum {
+  FX_EPI_NONE = 0,      /* C = acc                                                          */
+  FX_EPI_BIAS = 1,      /* C = acc + bias[n]                                                */
+  FX_EPI_BIAS_GELU = 2, /* Z = acc + bias[n] (stored to aux if non-null); C = gelu_tanh(Z)  */
+  FX_EPI_DGELU = 3      /* C = acc * gelu_tanh'(aux[m,n])   (aux = saved pre-activation Z)  */
+};
+
+/* ---- runtime -------------------------------------------------------------------------------- */
+const char* fx_last_error(void);
+int fx_version(void);
+/* Number of kernels this library has launched in this process (all threads). */
+uint64_t fx_launch_count(void);
+
+/* ---- LayerNorm: nn.LayerNorm(d_model, epsilon=1e-5), hybrid_model.py:513-514, used :534,:554 -- */
+/* y = (x - mean) * rstd * gamma + beta over the last dim (biased variance). x,y bf16 [rows,h];
+ * mean,rstd fp32 [rows] are saved for the backward pass. h % 8 == 0, h <= 16384. */
+int fx_layernorm_fwd(void* stream, const void* x, const float* gamma, const float* beta, void* y,
+                     float* mean, float* rstd, int rows, int h, float eps);
+size_t fx_layernorm_bwd_workspace_bytes(int rows, int h);
+/* dx = LN'(dy) (+ dresidual if non-null: the gradient arriving on the skip path, fused so the
+ * residual fan-in add of hybrid_model.py:547/:561 costs no extra pass); dgamma,dbeta fp32 [h]. */
+int fx_layernorm_bwd(void* stream, const void* dy, const void* x, const float* gamma,
+                     const float* mean, const float* rstd, const void* dresidual, void* dx,
+                     float* dgamma, float* dbeta, void* workspace, int rows, int h);
+
+/* ---- bias + dropout + residual: hybrid_model.py:546-547 (dropout1) and :556-561 (dropout2) ---- */
+/* out = residual + dropout(y + bias, p, upscale_in_train). bias may be null. The keep mask is a
+ * pure function of (seed, offset, element index) (Philox4x32-10) so backward and recompute
+ * (hybrid_model.py:332-335, 406-408, 537-539) regenerate it. mask_in (uint8 [rows*h], 1 = keep)
+ * overrides the generator when non-null (parity tests inject masks); mask_out, when non-null,
+ * receives the mask that was used. All of y, residual, out are bf16 [rows,h]; h % 8 == 0. */
+int fx_bias_dropout_residual_fwd(void* stream, const void* y, const void* bias,
+                                 const void* residual, void* out, int rows, int h, float p,
+                                 uint64_t seed, uint64_t offset, const uint8_t* mask_in,
+                                 uint8_t* mask_out);
+/* dy = dout * mask / (1-p)  (bf16 [rows,h]); the residual branch gradient is dout itself. */
+int fx_bias_dropout_residual_bwd(void* stream, const void* dout, void* dy, int rows, int h,
+                                 float p, uint64_t seed, uint64_t offset, const uint8_t* mask_in);
+
+/* Column sum of a bf16 [rows,n] matrix into fp32 or bf16 [n] (bias gradients of the four
+ * linears: paddle autograd of `x·W + b`, hybrid_model.py:125-131,157-163,497-511). */
+size_t fx_colsum_workspace_bytes(int rows, int n);
+int fx_colsum_bf16(void* stream, const void* x, int ldx, void* out, int out_dtype, void* workspace,
+                   int rows, int n);
+
+/* ---- GEMM: the four linears and their gradients ------------------------------------------------
+ * qkv_proj hybrid_model.py:125-131,166; out_proj :157-163,340; linear1 :497-503,559;
+ * linear2 :505-511,558 (fleet.meta_parallel Column/RowParallelLinear local matmuls).
+ * C[M,N] = op(A)[M,K] * op(B)[K,N], bf16 operands, fp32 accumulation in TMEM (tcgen05).
+ *   trans_a = 0: A stored [M,K] row-major (lda >= K);  1: A stored [K,M] (lda >= M)
+ *   trans_b = 0: B stored [K,N] row-major (ldb >= N);  1: B stored [N,K] (ldb >= K)
+ * forward y = x·W: (0,0); dgrad dx = dy·W^T: (0,1); wgrad dW = x^T·dy: (1,0).
+ * c_dtype FX_BF16 or FX_F32; accumulate != 0 adds into C. bias bf16 [N]; aux bf16 [M,ldaux].
+ * All leading dimensions and M, N, K must be multiples of 8; pointers 16-byte aligned. */
+int fx_gemm_bf16(void* stream, int trans_a, int trans_b, int M, int N, int K, const void* A,
+                 int lda, const void* B, int ldb, void* C, int ldc, int c_dtype, int accumulate,
+                 int epilogue, const void* bias, void* aux, int ldaux);
+
+/* ---- fused causal self-attention: hybrid_model.py:165-186 (_fuse_prepare_qkv) + :268-298 ------
+ * qkv is the UNTOUCHED output of qkv_proj, bf16 [b, s, nh_local, 3, hd] (per head q|k|v, as the
+ * reshape/transpose/split at :167-173 reads it); out is bf16 [b, s, nh_local*hd], i.e. already
+ * in the merged-head layout of :293-296. softmax(scale·QK^T + causal) is computed online, the
+ * s×s matrix never reaches HBM; lse fp32 [b, nh_local, s] is saved for backward. Dropout on the
+ * probabilities (:279-285, 'local_seed' stream) uses Philox keyed on (seed, offset, b, head,
+ * row, col). hd is 64 or 128. */
+int fx_attn_causal_fwd(void* stream, const void* qkv, void* out, float* lse, int b, int s, int nh,
+                       int hd, float scale, float p_drop, uint64_t seed, uint64_t offset);
+size_t fx_attn_causal_bwd_workspace_bytes(int b, int s, int nh, int hd);
+/* dqkv bf16, same packed layout as qkv, fully overwritten. */
+int fx_attn_causal_bwd(void* stream, const void* dout, const void* qkv, const void* out,
+                       const float* lse, void* dqkv, void* workspace, int b, int s, int nh, int hd,
+                       float scale, float p_drop, uint64_t seed, uint64_t offset);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FLEETX_B200_H_ */
