@@ -1,14 +1,971 @@
-// attention.cu — placeholder while the tcgen05 kernels land; every entry point fails loudly.
+// attention.cu — K3/K4: fused causal self-attention, forward and backward, on tcgen05.
+//
+// Replaces hybrid_model.py:165-186 (_fuse_prepare_qkv: reshape/transpose/split of the packed
+// qkv_proj output) and :268-298 (core_attn: scaled QK^T, causal softmax, dropout under the
+// 'local_seed' stream, PV, head merge). The s x s score / probability tensors the reference
+// writes three times never leave the SM here.
+//
+// Data layout: qkv [b, s, nh, 3, hd] bf16 exactly as qkv_proj produced it — Q, K and V tiles
+// are cut out of it by ONE 4-D TMA tensor map (dims hd | 3·nh | s | b), so the head split costs
+// no copy; out / dout are [b, s, nh·hd] (heads merged), dqkv has the qkv layout again.
+//
+// Forward (one CTA = 128 query rows of one head; 192 threads):
+//   warp 0     TMA: Q once, then K_j / V_j through a 2-deep ring
+//   warp 1     MMA: S_j = Q·K_j^T (128x128, K = hd) and PV_j = P_j·V_j (128 x hd, K = 128) into
+//              TMEM; V is consumed as an MN-major operand straight from the same TMA box
+//   warps 2-5  softmax: one query row per thread; two sweeps over S in TMEM (max, then exp2),
+//              P_j (with dropout folded in) goes back to shared memory as bf16 in the
+//              128B-swizzled K-major layout the PV MMA reads; O is kept in registers and updated
+//              as O = alpha·O + PV_j one step behind, so the tensor core always has work queued
+// Backward (two kernels, deterministic, no atomics):
+//   dKV kernel: CTA owns a 128-row KV tile, walks the query tiles at or below the diagonal:
+//              S^T = K·Q^T, dP^T = V·dO^T, dV += P^T·dO, dK += dS^T·Q
+//   dQ  kernel: CTA owns a 128-row Q tile, walks KV tiles: S = Q·K^T, dP = dO·V^T, dQ += dS·K
+//   with delta = rowsum(dO ∘ O) from a small pre-pass (workspace, fp32 [b, nh, s]).
 #include "common.cuh"
+#include "philox.cuh"
+#include "tc5.cuh"
 
-extern "C" int fx_attn_causal_fwd(void*, const void*, void*, float*, int, int, int, int, float, float,
-                                  uint64_t, uint64_t) {
-  fx::set_error("fx_attn_causal_fwd: not built yet");
-  return FX_ERR_UNSUPPORTED;
+namespace fx {
+namespace attn {
+
+using namespace tc5;
+
+constexpr int NUM_THREADS = 192;
+constexpr float LOG2E = 1.4426950408889634f;
+
+// byte offset of 16-byte chunk `c16` of row `r` inside a [rows x 64 bf16] 128B-swizzled tile
+__device__ __forceinline__ uint32_t sw128_off(int r, int c16) {
+  return static_cast<uint32_t>(r * 128 + ((c16 ^ (r & 7)) << 4));
 }
-extern "C" size_t fx_attn_causal_bwd_workspace_bytes(int, int, int, int) { return 0; }
-extern "C" int fx_attn_causal_bwd(void*, const void*, const void*, const void*, const float*, void*, void*,
-                                  int, int, int, int, float, float, uint64_t, uint64_t) {
-  fx::set_error("fx_attn_causal_bwd: not built yet");
-  return FX_ERR_UNSUPPORTED;
+
+__device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+
+struct FwdParams {
+  __nv_bfloat16* out;
+  float* lse;
+  int b, s, nh;
+  float scale, p_drop, inv_keep;
+  uint32_t thresh;
+  uint64_t seed, offset;
+};
+
+template <int HD>
+struct FwdCfg {
+  static constexpr int TILE_BYTES = 128 * HD * 2;  // one Q / K / V tile
+  static constexpr int SUB_BYTES = 128 * 128;      // one [128 rows x 64 cols] swizzled sub-tile
+  static constexpr int P_BYTES = 128 * 128 * 2;
+  static constexpr int NS = HD == 64 ? 1 : 2;      // S accumulators in TMEM
+  static constexpr int OFF_Q = 0;
+  static constexpr int OFF_K = TILE_BYTES;
+  static constexpr int OFF_V = 3 * TILE_BYTES;
+  static constexpr int OFF_P = 5 * TILE_BYTES;
+  static constexpr int OFF_BAR = OFF_P + P_BYTES;
+  static constexpr int SMEM_BYTES = OFF_BAR + 256;
+  static constexpr int TMEM_PV = NS * 128;         // column of the first PV accumulator
+  static constexpr int TMEM_COLS = HD == 64 ? 256 : 512;
+  static constexpr int MIN_CTAS = HD == 64 ? 2 : 1;
+};
+
+template <int HD>
+__global__ void __launch_bounds__(NUM_THREADS, FwdCfg<HD>::MIN_CTAS)
+attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FwdParams p) {
+  using C = FwdCfg<HD>;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::OFF_BAR);
+  uint64_t* q_full = bars;            // 1
+  uint64_t* k_full = bars + 1;        // 2
+  uint64_t* k_empty = bars + 3;       // 2
+  uint64_t* v_full = bars + 5;        // 2
+  uint64_t* v_empty = bars + 7;       // 2
+  uint64_t* s_full = bars + 9;        // 2
+  uint64_t* s_empty = bars + 11;      // 2
+  uint64_t* p_full = bars + 13;       // 1
+  uint64_t* p_empty = bars + 14;      // 1
+  uint64_t* pv_full = bars + 15;      // 2
+  uint64_t* pv_empty = bars + 17;     // 2
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 19);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int num_qt = (p.s + 127) / 128;
+  const int qt = num_qt - 1 - blockIdx.x;  // heaviest (longest KV walk) tiles first
+  const int head = blockIdx.y;
+  const int batch = blockIdx.z;
+  const int n_kv = qt + 1;
+
+  if (threadIdx.x == 0 && (smem_u32(smem) & 1023u) != 0) {
+    printf("fleetx_b200: attention shared memory is not 1024-byte aligned\n");
+    __trap();
+  }
+  if (warp == 0 && lane == 0) tma_prefetch_desc(&tma_qkv);
+  if (warp == 1) {
+    if (lane == 0) {
+      mbar_init(q_full, 1);
+      for (int i = 0; i < 2; ++i) {
+        mbar_init(&k_full[i], 1);
+        mbar_init(&k_empty[i], 1);
+        mbar_init(&v_full[i], 1);
+        mbar_init(&v_empty[i], 1);
+        mbar_init(&s_full[i], 1);
+        mbar_init(&s_empty[i], 4);
+        mbar_init(&pv_full[i], 1);
+        mbar_init(&pv_empty[i], 4);
+      }
+      mbar_init(p_full, 4);
+      mbar_init(p_empty, 1);
+      mbar_fence_init();
+    }
+    __syncwarp();
+    tmem_alloc<C::TMEM_COLS>(tmem_slot);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      mbar_expect_tx(q_full, C::TILE_BYTES);
+#pragma unroll
+      for (int h2 = 0; h2 < HD / 64; ++h2)
+        tma_load_4d(smem + C::OFF_Q + h2 * C::SUB_BYTES, &tma_qkv, q_full, h2 * 64, head * 3 + 0, qt * 128, batch);
+      for (int j = 0; j < n_kv; ++j) {
+        const int buf = j & 1;
+        const uint32_t ph = (j >> 1) & 1;
+        mbar_wait(&k_empty[buf], ph ^ 1, 10);
+        mbar_expect_tx(&k_full[buf], C::TILE_BYTES);
+#pragma unroll
+        for (int h2 = 0; h2 < HD / 64; ++h2)
+          tma_load_4d(smem + C::OFF_K + buf * C::TILE_BYTES + h2 * C::SUB_BYTES, &tma_qkv, &k_full[buf], h2 * 64,
+                      head * 3 + 1, j * 128, batch);
+        mbar_wait(&v_empty[buf], ph ^ 1, 11);
+        mbar_expect_tx(&v_full[buf], C::TILE_BYTES);
+#pragma unroll
+        for (int h2 = 0; h2 < HD / 64; ++h2)
+          tma_load_4d(smem + C::OFF_V + buf * C::TILE_BYTES + h2 * C::SUB_BYTES, &tma_qkv, &v_full[buf], h2 * 64,
+                      head * 3 + 2, j * 128, batch);
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
+    const uint32_t idesc_s = instr_desc_bf16(128, 128, 0, 0);
+    const uint32_t idesc_pv = instr_desc_bf16(128, HD, 0, 1);
+    const uint32_t q_addr = smem_u32(smem + C::OFF_Q);
+    const uint32_t p_addr = smem_u32(smem + C::OFF_P);
+
+    auto issue_s = [&](int j) {
+      const int buf = j & 1, sb = j % C::NS;
+      mbar_wait(&k_full[buf], (j >> 1) & 1, 20);
+      mbar_wait(&s_empty[sb], ((j / C::NS) & 1) ^ 1, 21);
+      tc_fence_after();
+      if (lane == 0) {
+        const uint32_t k_addr = smem_u32(smem + C::OFF_K + buf * C::TILE_BYTES);
+#pragma unroll
+        for (int kk = 0; kk < HD / 16; ++kk) {
+          const uint32_t off = (kk >> 2) * C::SUB_BYTES + (kk & 3) * 32;
+          umma_ss(tmem_base + sb * 128, smem_desc_sw128(q_addr + off, 0, 1024),
+                  smem_desc_sw128(k_addr + off, 0, 1024), idesc_s, kk != 0);
+        }
+        umma_commit(&s_full[sb]);
+        umma_commit(&k_empty[buf]);
+      }
+      __syncwarp();
+    };
+
+    mbar_wait(q_full, 0, 22);
+    issue_s(0);
+    for (int j = 0; j < n_kv; ++j) {
+      if (j + 1 < n_kv) issue_s(j + 1);
+      const int buf = j & 1;
+      const uint32_t ph = (j >> 1) & 1;
+      mbar_wait(p_full, j & 1, 23);
+      mbar_wait(&v_full[buf], ph, 24);
+      mbar_wait(&pv_empty[buf], ph ^ 1, 25);
+      tc_fence_after();
+      if (lane == 0) {
+        const uint32_t v_addr = smem_u32(smem + C::OFF_V + buf * C::TILE_BYTES);
+#pragma unroll
+        for (int kk = 0; kk < 8; ++kk) {
+          umma_ss(tmem_base + C::TMEM_PV + buf * HD,
+                  smem_desc_sw128(p_addr + (kk >> 2) * C::SUB_BYTES + (kk & 3) * 32, 0, 1024),
+                  smem_desc_sw128(v_addr + kk * 2048, C::SUB_BYTES, 1024), idesc_pv, kk != 0);
+        }
+        umma_commit(&pv_full[buf]);
+        umma_commit(&v_empty[buf]);
+        umma_commit(p_empty);
+      }
+      __syncwarp();
+    }
+  } else {
+    // ------------------------------------------------------------------ softmax / output
+    const int quarter = warp & 3;
+    const int row_local = quarter * 32 + lane;
+    const int row = qt * 128 + row_local;
+    const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16);
+    const uint32_t p_addr = smem_u32(smem + C::OFF_P);
+    const float sl2 = p.scale * LOG2E;
+    const bool drop = p.p_drop > 0.f;
+    const uint64_t s8 = static_cast<uint64_t>((p.s + 7) / 8);
+    const uint64_t grp_row = (static_cast<uint64_t>(batch * p.nh + head) * p.s + row) * s8;
+
+    float o[HD];
+#pragma unroll
+    for (int i = 0; i < HD; ++i) o[i] = 0.f;
+    float m = -INFINITY, l = 0.f, alpha_prev = 0.f;
+
+    auto o_update = [&](int j, float alpha) {
+      const int buf = j & 1;
+      mbar_wait(&pv_full[buf], (j >> 1) & 1, 30);
+      tc_fence_after();
+#pragma unroll
+      for (int c = 0; c < HD / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(lane_base + C::TMEM_PV + buf * HD + c * 32, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) o[c * 32 + i] = o[c * 32 + i] * alpha + __uint_as_float(r[i]);
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&pv_empty[buf]);
+    };
+
+    for (int j = 0; j < n_kv; ++j) {
+      const int sb = j % C::NS;
+      const bool diag = (j == qt);
+      mbar_wait(&s_full[sb], (j / C::NS) & 1, 31);
+      tc_fence_after();
+      // sweep 1: row maximum of the raw scores
+      float mx = -INFINITY;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(lane_base + sb * 128 + c * 32, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          const float v = __uint_as_float(r[i]);
+          const bool masked = diag && (c * 32 + i > row_local);
+          mx = fmaxf(mx, masked ? -INFINITY : v);
+        }
+      }
+      const float m_new = fmaxf(m, mx);
+      const float alpha = exp2f((m - m_new) * sl2);
+      const float m_sc = m_new * sl2;
+      // P buffer must have been consumed by PV_{j-1}
+      mbar_wait(p_empty, (j & 1) ^ 1, 32);
+      // sweep 2: probabilities -> bf16 P tile (dropout folded in), row sum of the undropped p
+      float rowsum = 0.f;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(lane_base + sb * 128 + c * 32, r);
+        tmem_ld_wait();
+        float pr[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          const bool masked = diag && (c * 32 + i > row_local);
+          const float e = exp2f(__uint_as_float(r[i]) * sl2 - m_sc);
+          pr[i] = masked ? 0.f : e;
+          rowsum += pr[i];
+        }
+        if (drop) {
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            const Philox8 rnd = philox4x32_10(p.seed, p.offset, grp_row + static_cast<uint64_t>(j * 16 + c * 4 + g));
+#pragma unroll
+            for (int e = 0; e < 8; ++e)
+              pr[g * 8 + e] = philox_keep(rnd, e, p.thresh) ? pr[g * 8 + e] * p.inv_keep : 0.f;
+          }
+        }
+        // columns [c*32, c*32+32) live in sub-tile c/2, 16-byte chunks (c&1)*4 .. +3
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          const uint32_t addr = p_addr + (c >> 1) * C::SUB_BYTES + sw128_off(row_local, (c & 1) * 4 + g);
+          st_shared_v4(addr, pack_bf16(pr[g * 8 + 0], pr[g * 8 + 1]), pack_bf16(pr[g * 8 + 2], pr[g * 8 + 3]),
+                       pack_bf16(pr[g * 8 + 4], pr[g * 8 + 5]), pack_bf16(pr[g * 8 + 6], pr[g * 8 + 7]));
+        }
+      }
+      tc_fence_before();
+      fence_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive(&s_empty[sb]);
+        mbar_arrive(p_full);
+      }
+      l = l * alpha + rowsum;
+      m = m_new;
+      if (j > 0) o_update(j - 1, alpha_prev);
+      alpha_prev = alpha;
+    }
+    o_update(n_kv - 1, alpha_prev);
+
+    if (row < p.s) {
+      const float inv_l = 1.0f / l;
+      uint4* op = reinterpret_cast<uint4*>(p.out + (static_cast<size_t>(batch) * p.s + row) * (p.nh * HD) + head * HD);
+#pragma unroll
+      for (int g = 0; g < HD / 8; ++g)
+        op[g] = make_uint4(pack_bf16(o[g * 8 + 0] * inv_l, o[g * 8 + 1] * inv_l),
+                           pack_bf16(o[g * 8 + 2] * inv_l, o[g * 8 + 3] * inv_l),
+                           pack_bf16(o[g * 8 + 4] * inv_l, o[g * 8 + 5] * inv_l),
+                           pack_bf16(o[g * 8 + 6] * inv_l, o[g * 8 + 7] * inv_l));
+      p.lse[(static_cast<size_t>(batch) * p.nh + head) * p.s + row] = m * p.scale + __logf(l);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<C::TMEM_COLS>(tmem_base);
+}
+
+static int make_qkv_map(CUtensorMap* map, const void* qkv, int b, int s, int nh, int hd) {
+  const uint64_t dims[4] = {(uint64_t)hd, (uint64_t)3 * nh, (uint64_t)s, (uint64_t)b};
+  const uint64_t strides[3] = {(uint64_t)hd * 2, (uint64_t)nh * 3 * hd * 2, (uint64_t)s * nh * 3 * hd * 2};
+  const uint32_t box[4] = {64, 1, 128, 1};
+  return make_tma_bf16(map, qkv, 4, dims, strides, box);
+}
+
+template <int HD>
+static int launch_fwd(cudaStream_t st, const CUtensorMap& map, const FwdParams& p) {
+  using C = FwdCfg<HD>;
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  FX_CUDA(cudaGetDevice(&dev));
+  if (dev < 64 && !attr_set[dev]) {
+    FX_CUDA(cudaFuncSetAttribute(attn_fwd_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+    attr_set[dev] = true;
+  }
+  dim3 grid((p.s + 127) / 128, p.nh, p.b);
+  attn_fwd_kernel<HD><<<grid, NUM_THREADS, C::SMEM_BYTES, st>>>(map, p);
+  FX_LAUNCH_CHECK();
+  return FX_OK;
+}
+
+
+// =====================================================================================
+// Backward
+// =====================================================================================
+constexpr int BWD_THREADS = 320;  // warp 0 TMA, warp 1 MMA, warps 2..9 elementwise (2 per TMEM lane quarter)
+
+struct BwdParams {
+  const float* lse;     // [b, nh, s]
+  const float* delta;   // [b, nh, s] rowsum(dO * O)
+  __nv_bfloat16* dqkv;  // [b, s, nh, 3, hd]
+  int b, s, nh;
+  float scale, p_drop, inv_keep;
+  uint32_t thresh;
+  uint64_t seed, offset;
+};
+
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+// delta[b, h, row] = sum_d dO[b, row, h, d] * O[b, row, h, d]
+__global__ void __launch_bounds__(256)
+attn_delta_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16* __restrict__ out,
+                  float* __restrict__ delta, int b, int s, int nh, int hd) {
+  const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;  // over [b, s, nh]
+  const size_t total = (size_t)b * s * nh;
+  if (idx >= total) return;
+  const int head = (int)(idx % nh);
+  const size_t br = idx / nh;  // b * s + row
+  const int row = (int)(br % s);
+  const int batch = (int)(br / s);
+  const uint4* a = reinterpret_cast<const uint4*>(dout + idx * hd);
+  const uint4* o = reinterpret_cast<const uint4*>(out + idx * hd);
+  float acc = 0.f;
+  for (int v = 0; v < hd / 8; ++v) {
+    const uint4 x = __ldg(a + v), y = __ldg(o + v);
+    const uint32_t xs[4] = {x.x, x.y, x.z, x.w}, ys[4] = {y.x, y.y, y.z, y.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc += bf16_lo(xs[j]) * bf16_lo(ys[j]) + bf16_hi(xs[j]) * bf16_hi(ys[j]);
+  }
+  delta[((size_t)batch * nh + head) * s + row] = acc;
+}
+
+// ---------------------------------------------------------------------------- dQ kernel
+template <int HD>
+struct DqCfg {
+  static constexpr int QT_BYTES = 128 * HD * 2;   // Q / dO tile (128 rows)
+  static constexpr int KV_BYTES = 64 * HD * 2;    // K / V tile (64 rows)
+  static constexpr int KV_SUB = 64 * 128;         // one 64-col sub-tile of a 64-row tile
+  static constexpr int DS_BYTES = 128 * 64 * 2;
+  static constexpr int OFF_Q = 0;
+  static constexpr int OFF_DO = QT_BYTES;
+  static constexpr int OFF_K = 2 * QT_BYTES;
+  static constexpr int OFF_V = OFF_K + 2 * KV_BYTES;
+  static constexpr int OFF_DS = OFF_V + 2 * KV_BYTES;
+  static constexpr int OFF_BAR = OFF_DS + 2 * DS_BYTES;
+  static constexpr int SMEM_BYTES = OFF_BAR + 256;
+  static constexpr int TM_S = 0, TM_DP = 128, TM_DQ = 256;
+  static constexpr int TMEM_COLS = 512;
+};
+
+template <int HD>
+__global__ void __launch_bounds__(BWD_THREADS, 1)
+attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tma_q,   // qkv, box rows 128
+                   const __grid_constant__ CUtensorMap tma_kv,  // qkv, box rows 64
+                   const __grid_constant__ CUtensorMap tma_do,  // dout, box rows 128
+                   const BwdParams p) {
+  using C = DqCfg<HD>;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::OFF_BAR);
+  uint64_t* qdo_full = bars;        // 1
+  uint64_t* kv_full = bars + 1;     // 2
+  uint64_t* kv_empty = bars + 3;    // 2
+  uint64_t* s_full = bars + 5;      // 2
+  uint64_t* s_empty = bars + 7;     // 2
+  uint64_t* ds_full = bars + 9;     // 2
+  uint64_t* ds_empty = bars + 11;   // 2
+  uint64_t* dq_full = bars + 13;    // 1
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 14);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int num_qt = (p.s + 127) / 128;
+  const int qt = num_qt - 1 - blockIdx.x;
+  const int head = blockIdx.y, batch = blockIdx.z;
+  const int n_kv = min((p.s + 63) / 64, 2 * qt + 2);
+
+  if (threadIdx.x == 0 && (smem_u32(smem) & 1023u) != 0) __trap();
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tma_q);
+    tma_prefetch_desc(&tma_kv);
+    tma_prefetch_desc(&tma_do);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      mbar_init(qdo_full, 1);
+      mbar_init(dq_full, 1);
+      for (int i = 0; i < 2; ++i) {
+        mbar_init(&kv_full[i], 1);
+        mbar_init(&kv_empty[i], 1);
+        mbar_init(&s_full[i], 1);
+        mbar_init(&s_empty[i], 8);
+        mbar_init(&ds_full[i], 8);
+        mbar_init(&ds_empty[i], 1);
+      }
+      mbar_fence_init();
+    }
+    __syncwarp();
+    tmem_alloc<C::TMEM_COLS>(tmem_slot);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_expect_tx(qdo_full, 2 * C::QT_BYTES);
+#pragma unroll
+      for (int h2 = 0; h2 < HD / 64; ++h2) {
+        tma_load_4d(smem + C::OFF_Q + h2 * 16384, &tma_q, qdo_full, h2 * 64, head * 3 + 0, qt * 128, batch);
+        tma_load_4d(smem + C::OFF_DO + h2 * 16384, &tma_do, qdo_full, h2 * 64, head, qt * 128, batch);
+      }
+      for (int j = 0; j < n_kv; ++j) {
+        const int buf = j & 1;
+        mbar_wait(&kv_empty[buf], ((j >> 1) & 1) ^ 1, 40);
+        mbar_expect_tx(&kv_full[buf], 2 * C::KV_BYTES);
+#pragma unroll
+        for (int h2 = 0; h2 < HD / 64; ++h2) {
+          tma_load_4d(smem + C::OFF_K + buf * C::KV_BYTES + h2 * C::KV_SUB, &tma_kv, &kv_full[buf], h2 * 64,
+                      head * 3 + 1, j * 64, batch);
+          tma_load_4d(smem + C::OFF_V + buf * C::KV_BYTES + h2 * C::KV_SUB, &tma_kv, &kv_full[buf], h2 * 64,
+                      head * 3 + 2, j * 64, batch);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    const uint32_t idesc_s = instr_desc_bf16(128, 64, 0, 0);
+    const uint32_t idesc_dq = instr_desc_bf16(128, HD, 0, 1);
+    const uint32_t q_addr = smem_u32(smem + C::OFF_Q), do_addr = smem_u32(smem + C::OFF_DO);
+
+    auto issue_sdp = [&](int j) {
+      const int buf = j & 1;
+      const uint32_t ph = (j >> 1) & 1;
+      mbar_wait(&kv_full[buf], ph, 41);
+      mbar_wait(&s_empty[buf], ph ^ 1, 42);
+      tc_fence_after();
+      if (lane == 0) {
+        const uint32_t k_addr = smem_u32(smem + C::OFF_K + buf * C::KV_BYTES);
+        const uint32_t v_addr = smem_u32(smem + C::OFF_V + buf * C::KV_BYTES);
+#pragma unroll
+        for (int kk = 0; kk < HD / 16; ++kk) {
+          const uint32_t offa = (kk >> 2) * 16384 + (kk & 3) * 32, offb = (kk >> 2) * C::KV_SUB + (kk & 3) * 32;
+          umma_ss(tmem_base + C::TM_S + buf * 64, smem_desc_sw128(q_addr + offa, 0, 1024),
+                  smem_desc_sw128(k_addr + offb, 0, 1024), idesc_s, kk != 0);
+        }
+#pragma unroll
+        for (int kk = 0; kk < HD / 16; ++kk) {
+          const uint32_t offa = (kk >> 2) * 16384 + (kk & 3) * 32, offb = (kk >> 2) * C::KV_SUB + (kk & 3) * 32;
+          umma_ss(tmem_base + C::TM_DP + buf * 64, smem_desc_sw128(do_addr + offa, 0, 1024),
+                  smem_desc_sw128(v_addr + offb, 0, 1024), idesc_s, kk != 0);
+        }
+        umma_commit(&s_full[buf]);
+      }
+      __syncwarp();
+    };
+
+    mbar_wait(qdo_full, 0, 43);
+    issue_sdp(0);
+    for (int j = 0; j < n_kv; ++j) {
+      if (j + 1 < n_kv) issue_sdp(j + 1);
+      const int buf = j & 1;
+      mbar_wait(&ds_full[buf], (j >> 1) & 1, 44);
+      tc_fence_after();
+      if (lane == 0) {
+        const uint32_t ds_addr = smem_u32(smem + C::OFF_DS + buf * C::DS_BYTES);
+        const uint32_t k_addr = smem_u32(smem + C::OFF_K + buf * C::KV_BYTES);
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)
+          umma_ss(tmem_base + C::TM_DQ, smem_desc_sw128(ds_addr + kk * 32, 0, 1024),
+                  smem_desc_sw128(k_addr + kk * 2048, C::KV_SUB, 1024), idesc_dq, (j | kk) != 0);
+        umma_commit(&ds_empty[buf]);
+        umma_commit(&kv_empty[buf]);
+        if (j == n_kv - 1) umma_commit(dq_full);
+      }
+      __syncwarp();
+    }
+  } else {
+    const int quarter = warp & 3, half = (warp - 2) >> 2;
+    const int row_local = quarter * 32 + lane;
+    const int row = qt * 128 + row_local;
+    const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16);
+    const float sl2 = p.scale * LOG2E;
+    const bool drop = p.p_drop > 0.f;
+    const uint64_t s8 = static_cast<uint64_t>((p.s + 7) / 8);
+    const size_t stat_idx = (static_cast<size_t>(batch) * p.nh + head) * p.s + row;
+    const uint64_t grp_row = static_cast<uint64_t>(stat_idx) * s8;
+    const float lse_r = row < p.s ? p.lse[stat_idx] * LOG2E : 0.f;
+    const float delta_r = row < p.s ? p.delta[stat_idx] : 0.f;
+
+    for (int j = 0; j < n_kv; ++j) {
+      const int buf = j & 1;
+      const uint32_t ph = (j >> 1) & 1;
+      mbar_wait(&s_full[buf], ph, 45);
+      tc_fence_after();
+      uint32_t rs[32], rp[32];
+      tmem_ld_32x32(lane_base + C::TM_S + buf * 64 + half * 32, rs);
+      tmem_ld_32x32(lane_base + C::TM_DP + buf * 64 + half * 32, rp);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&s_empty[buf]);
+      const int kv0 = j * 64 + half * 32;
+      float ds[32];
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        Philox8 rnd;
+        if (drop) rnd = philox4x32_10(p.seed, p.offset, grp_row + static_cast<uint64_t>((kv0 >> 3) + g));
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const int i = g * 8 + e;
+          const bool masked = (kv0 + i > row);
+          const float pr = masked ? 0.f : exp2f(__uint_as_float(rs[i]) * sl2 - lse_r);
+          float dp = __uint_as_float(rp[i]);
+          if (drop) dp = philox_keep(rnd, e, p.thresh) ? dp * p.inv_keep : 0.f;
+          ds[i] = pr * (dp - delta_r);
+        }
+      }
+      mbar_wait(&ds_empty[buf], ph ^ 1, 46);
+      const uint32_t ds_addr = smem_u32(smem + C::OFF_DS + buf * C::DS_BYTES);
+#pragma unroll
+      for (int g = 0; g < 4; ++g)
+        st_shared_v4(ds_addr + sw128_off(row_local, half * 4 + g), pack_bf16(ds[g * 8 + 0], ds[g * 8 + 1]),
+                     pack_bf16(ds[g * 8 + 2], ds[g * 8 + 3]), pack_bf16(ds[g * 8 + 4], ds[g * 8 + 5]),
+                     pack_bf16(ds[g * 8 + 6], ds[g * 8 + 7]));
+      fence_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&ds_full[buf]);
+    }
+
+    // dQ = scale * (dS · K): this warp drains columns [half*HD/2, +HD/2) of its 32 rows
+    mbar_wait(dq_full, 0, 47);
+    tc_fence_after();
+    __nv_bfloat16* dst = p.dqkv + ((static_cast<size_t>(batch) * p.s + row) * p.nh + head) * (3 * HD) + half * (HD / 2);
+#pragma unroll
+    for (int c = 0; c < HD / 64; ++c) {
+      uint32_t r[32];
+      tmem_ld_32x32(lane_base + C::TM_DQ + half * (HD / 2) + c * 32, r);
+      tmem_ld_wait();
+      if (row < p.s) {
+        uint4* o = reinterpret_cast<uint4*>(dst + c * 32);
+#pragma unroll
+        for (int g = 0; g < 4; ++g)
+          o[g] = make_uint4(pack_bf16(__uint_as_float(r[g * 8 + 0]) * p.scale, __uint_as_float(r[g * 8 + 1]) * p.scale),
+                            pack_bf16(__uint_as_float(r[g * 8 + 2]) * p.scale, __uint_as_float(r[g * 8 + 3]) * p.scale),
+                            pack_bf16(__uint_as_float(r[g * 8 + 4]) * p.scale, __uint_as_float(r[g * 8 + 5]) * p.scale),
+                            pack_bf16(__uint_as_float(r[g * 8 + 6]) * p.scale, __uint_as_float(r[g * 8 + 7]) * p.scale));
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<C::TMEM_COLS>(tmem_base);
+}
+
+// ---------------------------------------------------------------------------- dK/dV kernel
+template <int HD>
+struct DkvCfg {
+  static constexpr int KV_BYTES = 128 * HD * 2;  // K / V tile (128 rows), persistent
+  static constexpr int Q_BYTES = 64 * HD * 2;    // Q / dO tile (64 rows), 2-deep ring
+  static constexpr int Q_SUB = 64 * 128;
+  static constexpr int PT_BYTES = 128 * 64 * 2;  // P^T / dS^T tile [128 kv x 64 q]
+  static constexpr int OFF_K = 0;
+  static constexpr int OFF_V = KV_BYTES;
+  static constexpr int OFF_Q = 2 * KV_BYTES;
+  static constexpr int OFF_DO = OFF_Q + 2 * Q_BYTES;
+  static constexpr int OFF_PT = OFF_DO + 2 * Q_BYTES;
+  static constexpr int OFF_DST = OFF_PT + 2 * PT_BYTES;
+  static constexpr int OFF_MASK = OFF_DST + 2 * PT_BYTES;  // [2][64 q][16 bytes]: keep bits of 128 kv
+  static constexpr int OFF_BAR = OFF_MASK + 2 * 1024;
+  static constexpr int SMEM_BYTES = OFF_BAR + 256;
+  static constexpr int TM_ST = 0, TM_DPT = 128, TM_DV = 256, TM_DK = 256 + HD;
+  static constexpr int TMEM_COLS = 512;
+};
+
+template <int HD>
+__global__ void __launch_bounds__(BWD_THREADS, 1)
+attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tma_kv,  // qkv, box rows 128
+                    const __grid_constant__ CUtensorMap tma_q,   // qkv, box rows 64
+                    const __grid_constant__ CUtensorMap tma_do,  // dout, box rows 64
+                    const BwdParams p) {
+  using C = DkvCfg<HD>;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::OFF_BAR);
+  uint64_t* kv_full = bars;          // 1
+  uint64_t* q_full = bars + 1;       // 2
+  uint64_t* q_empty = bars + 3;      // 2
+  uint64_t* st_full = bars + 5;      // 2
+  uint64_t* st_empty = bars + 7;     // 2
+  uint64_t* pt_full = bars + 9;      // 2
+  uint64_t* pt_empty = bars + 11;    // 2
+  uint64_t* acc_full = bars + 13;    // 1
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 14);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int jt = blockIdx.x;  // KV tile; low tiles walk the most query tiles and start first
+  const int head = blockIdx.y, batch = blockIdx.z;
+  const int i0 = 2 * jt;                  // first 64-row query tile at or below the diagonal
+  const int n_q = (p.s + 63) / 64 - i0;   // >= 1 because jt*128 < s
+
+  if (threadIdx.x == 0 && (smem_u32(smem) & 1023u) != 0) __trap();
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tma_kv);
+    tma_prefetch_desc(&tma_q);
+    tma_prefetch_desc(&tma_do);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      mbar_init(kv_full, 1);
+      mbar_init(acc_full, 1);
+      for (int i = 0; i < 2; ++i) {
+        mbar_init(&q_full[i], 1);
+        mbar_init(&q_empty[i], 1);
+        mbar_init(&st_full[i], 1);
+        mbar_init(&st_empty[i], 8);
+        mbar_init(&pt_full[i], 8);
+        mbar_init(&pt_empty[i], 1);
+      }
+      mbar_fence_init();
+    }
+    __syncwarp();
+    tmem_alloc<C::TMEM_COLS>(tmem_slot);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_expect_tx(kv_full, 2 * C::KV_BYTES);
+#pragma unroll
+      for (int h2 = 0; h2 < HD / 64; ++h2) {
+        tma_load_4d(smem + C::OFF_K + h2 * 16384, &tma_kv, kv_full, h2 * 64, head * 3 + 1, jt * 128, batch);
+        tma_load_4d(smem + C::OFF_V + h2 * 16384, &tma_kv, kv_full, h2 * 64, head * 3 + 2, jt * 128, batch);
+      }
+      for (int t = 0; t < n_q; ++t) {
+        const int buf = t & 1;
+        mbar_wait(&q_empty[buf], ((t >> 1) & 1) ^ 1, 50);
+        mbar_expect_tx(&q_full[buf], 2 * C::Q_BYTES);
+#pragma unroll
+        for (int h2 = 0; h2 < HD / 64; ++h2) {
+          tma_load_4d(smem + C::OFF_Q + buf * C::Q_BYTES + h2 * C::Q_SUB, &tma_q, &q_full[buf], h2 * 64, head * 3 + 0,
+                      (i0 + t) * 64, batch);
+          tma_load_4d(smem + C::OFF_DO + buf * C::Q_BYTES + h2 * C::Q_SUB, &tma_do, &q_full[buf], h2 * 64, head,
+                      (i0 + t) * 64, batch);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    const uint32_t idesc_st = instr_desc_bf16(128, 64, 0, 0);
+    const uint32_t idesc_acc = instr_desc_bf16(128, HD, 0, 1);
+    const uint32_t k_addr = smem_u32(smem + C::OFF_K), v_addr = smem_u32(smem + C::OFF_V);
+
+    auto issue_st = [&](int t) {
+      const int buf = t & 1;
+      const uint32_t ph = (t >> 1) & 1;
+      mbar_wait(&q_full[buf], ph, 51);
+      mbar_wait(&st_empty[buf], ph ^ 1, 52);
+      tc_fence_after();
+      if (lane == 0) {
+        const uint32_t q_addr = smem_u32(smem + C::OFF_Q + buf * C::Q_BYTES);
+        const uint32_t do_addr = smem_u32(smem + C::OFF_DO + buf * C::Q_BYTES);
+#pragma unroll
+        for (int kk = 0; kk < HD / 16; ++kk) {
+          const uint32_t offa = (kk >> 2) * 16384 + (kk & 3) * 32, offb = (kk >> 2) * C::Q_SUB + (kk & 3) * 32;
+          umma_ss(tmem_base + C::TM_ST + buf * 64, smem_desc_sw128(k_addr + offa, 0, 1024),
+                  smem_desc_sw128(q_addr + offb, 0, 1024), idesc_st, kk != 0);
+        }
+#pragma unroll
+        for (int kk = 0; kk < HD / 16; ++kk) {
+          const uint32_t offa = (kk >> 2) * 16384 + (kk & 3) * 32, offb = (kk >> 2) * C::Q_SUB + (kk & 3) * 32;
+          umma_ss(tmem_base + C::TM_DPT + buf * 64, smem_desc_sw128(v_addr + offa, 0, 1024),
+                  smem_desc_sw128(do_addr + offb, 0, 1024), idesc_st, kk != 0);
+        }
+        umma_commit(&st_full[buf]);
+      }
+      __syncwarp();
+    };
+
+    mbar_wait(kv_full, 0, 53);
+    issue_st(0);
+    for (int t = 0; t < n_q; ++t) {
+      if (t + 1 < n_q) issue_st(t + 1);
+      const int buf = t & 1;
+      mbar_wait(&pt_full[buf], (t >> 1) & 1, 54);
+      tc_fence_after();
+      if (lane == 0) {
+        const uint32_t pt_addr = smem_u32(smem + C::OFF_PT + buf * C::PT_BYTES);
+        const uint32_t dst_addr = smem_u32(smem + C::OFF_DST + buf * C::PT_BYTES);
+        const uint32_t q_addr = smem_u32(smem + C::OFF_Q + buf * C::Q_BYTES);
+        const uint32_t do_addr = smem_u32(smem + C::OFF_DO + buf * C::Q_BYTES);
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)
+          umma_ss(tmem_base + C::TM_DV, smem_desc_sw128(pt_addr + kk * 32, 0, 1024),
+                  smem_desc_sw128(do_addr + kk * 2048, C::Q_SUB, 1024), idesc_acc, (t | kk) != 0);
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)
+          umma_ss(tmem_base + C::TM_DK, smem_desc_sw128(dst_addr + kk * 32, 0, 1024),
+                  smem_desc_sw128(q_addr + kk * 2048, C::Q_SUB, 1024), idesc_acc, (t | kk) != 0);
+        umma_commit(&pt_empty[buf]);
+        umma_commit(&q_empty[buf]);
+        if (t == n_q - 1) umma_commit(acc_full);
+      }
+      __syncwarp();
+    }
+  } else {
+    const int quarter = warp & 3, half = (warp - 2) >> 2;
+    const int r_local = quarter * 32 + lane;  // kv row inside the tile
+    const int kv = jt * 128 + r_local;
+    const int tid = threadIdx.x - 64;         // 0..255 among the elementwise warps
+    const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16);
+    const float sl2 = p.scale * LOG2E;
+    const bool drop = p.p_drop > 0.f;
+    const uint64_t s8 = static_cast<uint64_t>((p.s + 7) / 8);
+    const size_t stat_base = (static_cast<size_t>(batch) * p.nh + head) * p.s;
+    uint8_t* mask = smem + C::OFF_MASK;
+
+    for (int t = 0; t < n_q; ++t) {
+      const int buf = t & 1;
+      const uint32_t ph = (t >> 1) & 1;
+      const int q0 = (i0 + t) * 64;
+      if (drop) {
+        // keep bits are defined along kv (8 per Philox call, attention fwd draws them per query
+        // row); here a thread owns a kv row, so the 64x128 tile of bits is built cooperatively
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int idx = tid * 4 + k;  // 0..1023 = q_local * 16 + kv group
+          const int ql = idx >> 4, g = idx & 15;
+          const Philox8 rnd = philox4x32_10(p.seed, p.offset,
+                                            static_cast<uint64_t>(stat_base + q0 + ql) * s8 + static_cast<uint64_t>(jt * 16 + g));
+          uint32_t bits = 0;
+#pragma unroll
+          for (int e = 0; e < 8; ++e) bits |= (philox_keep(rnd, e, p.thresh) ? 1u : 0u) << e;
+          mask[buf * 1024 + idx] = static_cast<uint8_t>(bits);
+        }
+        named_bar_sync(1, 256);
+      }
+      mbar_wait(&st_full[buf], ph, 55);
+      tc_fence_after();
+      uint32_t rs[32], rp[32];
+      tmem_ld_32x32(lane_base + C::TM_ST + buf * 64 + half * 32, rs);
+      tmem_ld_32x32(lane_base + C::TM_DPT + buf * 64 + half * 32, rp);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&st_empty[buf]);
+
+      float pd[32], ds[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        const int ql = half * 32 + i;
+        const int q = q0 + ql;
+        const bool valid = (q >= kv) && (q < p.s);
+        const float lse_q = valid ? __ldg(p.lse + stat_base + q) * LOG2E : 0.f;
+        const float delta_q = valid ? __ldg(p.delta + stat_base + q) : 0.f;
+        const float pr = valid ? exp2f(__uint_as_float(rs[i]) * sl2 - lse_q) : 0.f;
+        float dp = __uint_as_float(rp[i]);
+        float pk = pr;
+        if (drop) {
+          const bool keep = (mask[buf * 1024 + ql * 16 + (r_local >> 3)] >> (r_local & 7)) & 1;
+          dp = keep ? dp * p.inv_keep : 0.f;
+          pk = keep ? pr * p.inv_keep : 0.f;
+        }
+        pd[i] = pk;
+        ds[i] = pr * (dp - delta_q);
+      }
+      mbar_wait(&pt_empty[buf], ph ^ 1, 56);
+      const uint32_t pt_addr = smem_u32(smem + C::OFF_PT + buf * C::PT_BYTES);
+      const uint32_t dst_addr = smem_u32(smem + C::OFF_DST + buf * C::PT_BYTES);
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        const uint32_t off = sw128_off(r_local, half * 4 + g);
+        st_shared_v4(pt_addr + off, pack_bf16(pd[g * 8 + 0], pd[g * 8 + 1]), pack_bf16(pd[g * 8 + 2], pd[g * 8 + 3]),
+                     pack_bf16(pd[g * 8 + 4], pd[g * 8 + 5]), pack_bf16(pd[g * 8 + 6], pd[g * 8 + 7]));
+        st_shared_v4(dst_addr + off, pack_bf16(ds[g * 8 + 0], ds[g * 8 + 1]), pack_bf16(ds[g * 8 + 2], ds[g * 8 + 3]),
+                     pack_bf16(ds[g * 8 + 4], ds[g * 8 + 5]), pack_bf16(ds[g * 8 + 6], ds[g * 8 + 7]));
+      }
+      fence_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&pt_full[buf]);
+    }
+
+    // dV = P_drop^T · dO, dK = scale * dS^T · Q; this warp drains columns [half*HD/2, +HD/2)
+    mbar_wait(acc_full, 0, 57);
+    tc_fence_after();
+    __nv_bfloat16* base = p.dqkv + ((static_cast<size_t>(batch) * p.s + kv) * p.nh + head) * (3 * HD) + half * (HD / 2);
+#pragma unroll
+    for (int which = 0; which < 2; ++which) {  // 0: dK, 1: dV
+      const float mul = which == 0 ? p.scale : 1.0f;
+#pragma unroll
+      for (int c = 0; c < HD / 64; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(lane_base + (which == 0 ? C::TM_DK : C::TM_DV) + half * (HD / 2) + c * 32, r);
+        tmem_ld_wait();
+        if (kv < p.s) {
+          uint4* o = reinterpret_cast<uint4*>(base + (which + 1) * HD + c * 32);
+#pragma unroll
+          for (int g = 0; g < 4; ++g)
+            o[g] = make_uint4(pack_bf16(__uint_as_float(r[g * 8 + 0]) * mul, __uint_as_float(r[g * 8 + 1]) * mul),
+                              pack_bf16(__uint_as_float(r[g * 8 + 2]) * mul, __uint_as_float(r[g * 8 + 3]) * mul),
+                              pack_bf16(__uint_as_float(r[g * 8 + 4]) * mul, __uint_as_float(r[g * 8 + 5]) * mul),
+                              pack_bf16(__uint_as_float(r[g * 8 + 6]) * mul, __uint_as_float(r[g * 8 + 7]) * mul));
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<C::TMEM_COLS>(tmem_base);
+}
+
+static int make_qkv_map_rows(CUtensorMap* map, const void* qkv, int b, int s, int nh, int hd, uint32_t box_rows) {
+  const uint64_t dims[4] = {(uint64_t)hd, (uint64_t)3 * nh, (uint64_t)s, (uint64_t)b};
+  const uint64_t strides[3] = {(uint64_t)hd * 2, (uint64_t)nh * 3 * hd * 2, (uint64_t)s * nh * 3 * hd * 2};
+  const uint32_t box[4] = {64, 1, box_rows, 1};
+  return make_tma_bf16(map, qkv, 4, dims, strides, box);
+}
+static int make_out_map_rows(CUtensorMap* map, const void* out, int b, int s, int nh, int hd, uint32_t box_rows) {
+  const uint64_t dims[4] = {(uint64_t)hd, (uint64_t)nh, (uint64_t)s, (uint64_t)b};
+  const uint64_t strides[3] = {(uint64_t)hd * 2, (uint64_t)nh * hd * 2, (uint64_t)s * nh * hd * 2};
+  const uint32_t box[4] = {64, 1, box_rows, 1};
+  return make_tma_bf16(map, out, 4, dims, strides, box);
+}
+
+template <int HD>
+static int launch_bwd(cudaStream_t st, const void* dout, const void* qkv, const void* out, const BwdParams& p,
+                      float* delta) {
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  FX_CUDA(cudaGetDevice(&dev));
+  if (dev < 64 && !attr_set[dev]) {
+    FX_CUDA(cudaFuncSetAttribute(attn_bwd_dq_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, DqCfg<HD>::SMEM_BYTES));
+    FX_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, DkvCfg<HD>::SMEM_BYTES));
+    attr_set[dev] = true;
+  }
+  CUtensorMap qkv128, qkv64, do128, do64;
+  int rc;
+  if ((rc = make_qkv_map_rows(&qkv128, qkv, p.b, p.s, p.nh, HD, 128))) return rc;
+  if ((rc = make_qkv_map_rows(&qkv64, qkv, p.b, p.s, p.nh, HD, 64))) return rc;
+  if ((rc = make_out_map_rows(&do128, dout, p.b, p.s, p.nh, HD, 128))) return rc;
+  if ((rc = make_out_map_rows(&do64, dout, p.b, p.s, p.nh, HD, 64))) return rc;
+
+  const size_t total = (size_t)p.b * p.s * p.nh;
+  attn_delta_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(
+      static_cast<const __nv_bfloat16*>(dout), static_cast<const __nv_bfloat16*>(out), delta, p.b, p.s, p.nh, HD);
+  FX_LAUNCH_CHECK();
+  dim3 grid((p.s + 127) / 128, p.nh, p.b);
+  attn_bwd_dkv_kernel<HD><<<grid, BWD_THREADS, DkvCfg<HD>::SMEM_BYTES, st>>>(qkv128, qkv64, do64, p);
+  FX_LAUNCH_CHECK();
+  attn_bwd_dq_kernel<HD><<<grid, BWD_THREADS, DqCfg<HD>::SMEM_BYTES, st>>>(qkv128, qkv64, do128, p);
+  FX_LAUNCH_CHECK();
+  return FX_OK;
+}
+
+}  // namespace attn
+}  // namespace fx
+
+extern "C" int fx_attn_causal_fwd(void* stream, const void* qkv, void* out, float* lse, int b, int s,
+                                  int nh, int hd, float scale, float p_drop, uint64_t seed,
+                                  uint64_t offset) {
+  using namespace fx;
+  FX_CHECK_ARG(b > 0 && s > 0 && nh > 0, "fx_attn_causal_fwd: empty input (b %d, s %d, nh %d)", b, s, nh);
+  FX_CHECK_ARG(hd == 64 || hd == 128, "fx_attn_causal_fwd: head_dim must be 64 or 128 (got %d)", hd);
+  FX_CHECK_ARG(nh <= 65535 && b <= 65535, "fx_attn_causal_fwd: nh and b must be <= 65535");
+  FX_CHECK_ARG(p_drop >= 0.f && p_drop < 1.f, "fx_attn_causal_fwd: dropout p must be in [0,1) (got %f)", p_drop);
+  FX_CHECK_ARG(scale > 0.f, "fx_attn_causal_fwd: scale must be positive");
+  FX_CHECK_ARG(qkv && out && lse, "fx_attn_causal_fwd: null pointer");
+  FX_CHECK_ARG(((uintptr_t)qkv | (uintptr_t)out) % 16 == 0, "fx_attn_causal_fwd: pointers must be 16-byte aligned");
+  CUtensorMap map;
+  int rc = attn::make_qkv_map(&map, qkv, b, s, nh, hd);
+  if (rc) return rc;
+  attn::FwdParams p{};
+  p.out = static_cast<__nv_bfloat16*>(out);
+  p.lse = lse;
+  p.b = b; p.s = s; p.nh = nh;
+  p.scale = scale; p.p_drop = p_drop; p.inv_keep = 1.0f / (1.0f - p_drop);
+  p.thresh = dropout_threshold(p_drop);
+  p.seed = seed; p.offset = offset;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  return hd == 64 ? attn::launch_fwd<64>(st, map, p) : attn::launch_fwd<128>(st, map, p);
+}
+
+extern "C" size_t fx_attn_causal_bwd_workspace_bytes(int b, int s, int nh, int hd) {
+  (void)hd;
+  if (b <= 0 || s <= 0 || nh <= 0) return 0;
+  return (size_t)b * s * nh * sizeof(float);  // delta = rowsum(dO * O)
+}
+
+extern "C" int fx_attn_causal_bwd(void* stream, const void* dout, const void* qkv, const void* out,
+                                  const float* lse, void* dqkv, void* workspace, int b, int s, int nh,
+                                  int hd, float scale, float p_drop, uint64_t seed, uint64_t offset) {
+  using namespace fx;
+  FX_CHECK_ARG(b > 0 && s > 0 && nh > 0, "fx_attn_causal_bwd: empty input (b %d, s %d, nh %d)", b, s, nh);
+  FX_CHECK_ARG(hd == 64 || hd == 128, "fx_attn_causal_bwd: head_dim must be 64 or 128 (got %d)", hd);
+  FX_CHECK_ARG(nh <= 65535 && b <= 65535, "fx_attn_causal_bwd: nh and b must be <= 65535");
+  FX_CHECK_ARG(p_drop >= 0.f && p_drop < 1.f, "fx_attn_causal_bwd: dropout p must be in [0,1) (got %f)", p_drop);
+  FX_CHECK_ARG(scale > 0.f, "fx_attn_causal_bwd: scale must be positive");
+  FX_CHECK_ARG(dout && qkv && out && lse && dqkv && workspace, "fx_attn_causal_bwd: null pointer");
+  FX_CHECK_ARG(((uintptr_t)dout | (uintptr_t)qkv | (uintptr_t)out | (uintptr_t)dqkv | (uintptr_t)workspace) % 16 == 0,
+               "fx_attn_causal_bwd: pointers must be 16-byte aligned");
+  attn::BwdParams p{};
+  p.lse = lse;
+  p.delta = static_cast<const float*>(workspace);
+  p.dqkv = static_cast<__nv_bfloat16*>(dqkv);
+  p.b = b; p.s = s; p.nh = nh;
+  p.scale = scale; p.p_drop = p_drop; p.inv_keep = 1.0f / (1.0f - p_drop);
+  p.thresh = dropout_threshold(p_drop);
+  p.seed = seed; p.offset = offset;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  float* delta = static_cast<float*>(workspace);
+  return hd == 64 ? attn::launch_bwd<64>(st, dout, qkv, out, p, delta) : attn::launch_bwd<128>(st, dout, qkv, out, p, delta);
 }

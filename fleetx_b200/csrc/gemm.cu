@@ -5,13 +5,16 @@
 //               4..6-stage shared-memory ring (128-byte swizzle), signalling `full` mbarriers
 //   warp 1      MMA issuer: one lane issues tcgen05.mma (M=128, N=BN, K=16) into one of two
 //               TMEM accumulators (2 x BN fp32 columns), tcgen05.commit frees ring slots
-//   warps 2..5  epilogue: tcgen05.ld the finished accumulator (one row per thread), apply
-//               bias / GELU / GELU' / accumulate, store bf16 or fp32 — overlapped with the
-//               next tile's main loop through the second accumulator
+//   warps 2..5  epilogue: tcgen05.ld the finished accumulator (one row per thread), transpose
+//               32x32 blocks through shared memory so global accesses are sector-coalesced,
+//               apply bias / GELU / GELU' / accumulate, store bf16 or fp32 — overlapped with
+//               the next tile's main loop through the second accumulator
 //
 // Operands may be K-major or MN-major in memory (Paddle's [in,out] weights make the forward
 // B operand MN-major and the weight gradient MN-major on both sides); the shared-memory
 // descriptors carry the difference, so no transposed copies are ever made.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "tc5.cuh"
 
@@ -36,6 +39,7 @@ struct Params {
   __nv_bfloat16* aux;
   int ldaux;
   int num_m, num_n, num_tiles, num_kb;
+  int group;  // M-blocks per rasterisation group
 };
 
 template <int BN>
@@ -44,12 +48,13 @@ struct Cfg {
   static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
   static constexpr int STAGES = BN == 256 ? 4 : 6;
   static constexpr int BAR_BYTES = 256;
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + 1024;
+  static constexpr int STG_BYTES = 4 * 32 * 33 * 4;  // per-epilogue-warp 32x32 fp32 transpose tile (+1 pad)
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + STG_BYTES + 1024;
   static constexpr int TMEM_COLS = 2 * BN;
 };
 
 __device__ __forceinline__ void tile_coords(const Params& p, int tile, int& m_blk, int& n_blk) {
-  constexpr int GROUP = 8;  // 8 M-blocks share each B tile while it is hot in L2
+  const int GROUP = p.group;  // M-blocks that share each B tile while it is hot in L2
   const int per_group = GROUP * p.num_n;
   const int g = tile / per_group;
   const int first_m = g * GROUP;
@@ -73,91 +78,57 @@ __device__ __forceinline__ float gelu_tanh_grad(float z) {
   return s + 2.0f * z * s * (1.0f - s) * du;
 }
 
-// One thread owns 32 consecutive columns [col0, col0+32) of output row `row`.
-__device__ __forceinline__ void epilogue_store(const Params& p, int row, int col0,
-                                               const uint32_t (&r)[32]) {
-  if (col0 >= p.N) return;
-  const int ncols = min(32, p.N - col0);  // multiple of 8
-  float v[32];
-#pragma unroll
-  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
-
+// Epilogue math + store for one 32x32 fp32 block that a warp has just transposed through its
+// shared-memory staging tile: lane l owns columns [cl, cl+4) (cl = 4*(l%8)) of rows l/8 + 4*i,
+// so every global access of the warp covers whole 32-byte sectors of 4 consecutive rows.
+__device__ __forceinline__ void epilogue_block(const Params& p, const float* stg, int row0, int col0,
+                                               int lane) {
+  const int cl = (lane & 7) * 4;
+  const int col = col0 + cl;
+  if (col >= p.N) return;  // N % 8 == 0, so a 4-column group is entirely in or out
+  float bias[4] = {0.f, 0.f, 0.f, 0.f};
   if (p.epi == FX_EPI_BIAS || p.epi == FX_EPI_BIAS_GELU) {
-    const uint4* bp = reinterpret_cast<const uint4*>(p.bias + col0);
-#pragma unroll
-    for (int g = 0; g < 4; ++g) {
-      if (g * 8 < ncols) {
-        const uint4 b = __ldg(bp + g);
-        const uint32_t w[4] = {b.x, b.y, b.z, b.w};
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          v[g * 8 + 2 * j] += bf16_lo(w[j]);
-          v[g * 8 + 2 * j + 1] += bf16_hi(w[j]);
-        }
-      }
-    }
+    const uint2 b = __ldg(reinterpret_cast<const uint2*>(p.bias + col));
+    bias[0] = bf16_lo(b.x); bias[1] = bf16_hi(b.x); bias[2] = bf16_lo(b.y); bias[3] = bf16_hi(b.y);
   }
-  if (row >= p.M) return;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int rl = i * 4 + (lane >> 3);
+    const int row = row0 + rl;
+    if (row >= p.M) continue;
+    float v[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) v[j] = stg[rl * 33 + cl + j] + bias[j];
 
-  if (p.epi == FX_EPI_BIAS_GELU) {
-    if (p.aux != nullptr) {
-      uint4* zp = reinterpret_cast<uint4*>(p.aux + (size_t)row * p.ldaux + col0);
+    if (p.epi == FX_EPI_BIAS_GELU) {
+      if (p.aux != nullptr)
+        *reinterpret_cast<uint2*>(p.aux + (size_t)row * p.ldaux + col) =
+            make_uint2(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]));
+      // the activation sees the bf16-rounded pre-activation, exactly what a non-fused
+      // linear -> gelu pair (hybrid_model.py:558-559) would see
 #pragma unroll
-      for (int g = 0; g < 4; ++g)
-        if (g * 8 < ncols)
-          zp[g] = make_uint4(pack_bf16(v[g * 8 + 0], v[g * 8 + 1]), pack_bf16(v[g * 8 + 2], v[g * 8 + 3]),
-                             pack_bf16(v[g * 8 + 4], v[g * 8 + 5]), pack_bf16(v[g * 8 + 6], v[g * 8 + 7]));
+      for (int j = 0; j < 4; ++j) v[j] = gelu_tanh(__bfloat162float(__float2bfloat16_rn(v[j])));
+    } else if (p.epi == FX_EPI_DGELU) {
+      const uint2 z = __ldg(reinterpret_cast<const uint2*>(p.aux + (size_t)row * p.ldaux + col));
+      v[0] *= gelu_tanh_grad(bf16_lo(z.x)); v[1] *= gelu_tanh_grad(bf16_hi(z.x));
+      v[2] *= gelu_tanh_grad(bf16_lo(z.y)); v[3] *= gelu_tanh_grad(bf16_hi(z.y));
     }
-    // the activation is applied to the bf16-rounded pre-activation, exactly what a
-    // non-fused linear -> gelu pair (hybrid_model.py:558-559) would see
-#pragma unroll
-    for (int i = 0; i < 32; ++i) v[i] = gelu_tanh(__bfloat162float(__float2bfloat16_rn(v[i])));
-  } else if (p.epi == FX_EPI_DGELU) {
-    const uint4* zp = reinterpret_cast<const uint4*>(p.aux + (size_t)row * p.ldaux + col0);
-#pragma unroll
-    for (int g = 0; g < 4; ++g) {
-      if (g * 8 < ncols) {
-        const uint4 z = __ldg(zp + g);
-        const uint32_t w[4] = {z.x, z.y, z.z, z.w};
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          v[g * 8 + 2 * j] *= gelu_tanh_grad(bf16_lo(w[j]));
-          v[g * 8 + 2 * j + 1] *= gelu_tanh_grad(bf16_hi(w[j]));
-        }
-      }
-    }
-  }
 
-  if (p.c_f32) {
-    float4* cp = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.C) + (size_t)row * p.ldc + col0);
-#pragma unroll
-    for (int g = 0; g < 8; ++g) {
-      if (g * 4 < ncols) {
-        float4 o = make_float4(v[g * 4], v[g * 4 + 1], v[g * 4 + 2], v[g * 4 + 3]);
-        if (p.accumulate) {
-          const float4 old = cp[g];
-          o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
-        }
-        cp[g] = o;
+    if (p.c_f32) {
+      float4* cp = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.C) + (size_t)row * p.ldc + col);
+      float4 o = make_float4(v[0], v[1], v[2], v[3]);
+      if (p.accumulate) {
+        const float4 old = *cp;
+        o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
       }
-    }
-  } else {
-    uint4* cp = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.C) + (size_t)row * p.ldc + col0);
-#pragma unroll
-    for (int g = 0; g < 4; ++g) {
-      if (g * 8 < ncols) {
-        if (p.accumulate) {
-          const uint4 old = cp[g];
-          const uint32_t w[4] = {old.x, old.y, old.z, old.w};
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            v[g * 8 + 2 * j] += bf16_lo(w[j]);
-            v[g * 8 + 2 * j + 1] += bf16_hi(w[j]);
-          }
-        }
-        cp[g] = make_uint4(pack_bf16(v[g * 8 + 0], v[g * 8 + 1]), pack_bf16(v[g * 8 + 2], v[g * 8 + 3]),
-                           pack_bf16(v[g * 8 + 4], v[g * 8 + 5]), pack_bf16(v[g * 8 + 6], v[g * 8 + 7]));
+      *cp = o;
+    } else {
+      uint2* cp = reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.C) + (size_t)row * p.ldc + col);
+      if (p.accumulate) {
+        const uint2 old = *cp;
+        v[0] += bf16_lo(old.x); v[1] += bf16_hi(old.x); v[2] += bf16_lo(old.y); v[3] += bf16_hi(old.y);
       }
+      *cp = make_uint2(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]));
     }
   }
 }
@@ -174,6 +145,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
   uint64_t* tfull = empty + C::STAGES;
   uint64_t* tempty = tfull + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+  float* staging = reinterpret_cast<float*>(smem + C::STAGES * C::STAGE_BYTES + C::BAR_BYTES);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -278,12 +250,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
   } else {
     // ---------------------------------------------------------------- epilogue
     const int q = warp & 3;  // TMEM lane quarter this warp may read
+    float* stg = staging + (warp - 2) * (32 * 33);
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
       int m_blk, n_blk;
       tile_coords(p, tile, m_blk, n_blk);
-      const int row = m_blk * BM + q * 32 + lane;
+      const int row0 = m_blk * BM + q * 32;
       const int n0 = n_blk * BN;
       mbar_wait(&tfull[acc], acc_phase, 4);
       tc_fence_after();
@@ -293,7 +266,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
         uint32_t r[32];
         tmem_ld_32x32(taddr + c * 32, r);
         tmem_ld_wait();
-        epilogue_store(p, row, n0 + c * 32, r);
+        // thread = accumulator row -> staging row; (lane*33 + i) % 32 banks are conflict-free
+#pragma unroll
+        for (int i = 0; i < 32; ++i) stg[lane * 33 + i] = __uint_as_float(r[i]);
+        __syncwarp();
+        epilogue_block(p, stg, row0, n0 + c * 32, lane);
+        __syncwarp();
       }
       tc_fence_before();
       __syncwarp();
@@ -353,12 +331,18 @@ extern "C" int fx_gemm_bf16(void* stream, int trans_a, int trans_b, int M, int N
   FX_CHECK_ARG(((uintptr_t)A | (uintptr_t)B | (uintptr_t)C | (uintptr_t)bias | (uintptr_t)aux) % 16 == 0,
                "fx_gemm_bf16: pointers must be 16-byte aligned");
 
+  gemm::Params p{};
   const int sms = num_sms();
+  // Tile time is bound by L2->SM operand traffic per k-block: (128 + BN) * 64 * 2 bytes, i.e.
+  // 48 KB for BN = 256 and 32 KB for BN = 128 (for half the flops) — weigh waves by that.
   auto cost = [&](int bn) {
     const long tiles = (long)ceil_div(M, gemm::BM) * ceil_div(N, bn);
-    return ((tiles + sms - 1) / sms) * bn;
+    return ((tiles + sms - 1) / sms) * (bn == 256 ? 48 : 32);
   };
-  const int BN = (N > 128 && cost(256) <= cost(128)) ? 256 : 128;
+  int BN = (N > 128 && cost(256) <= cost(128)) ? 256 : 128;
+  p.group = 8;
+  if (const char* e = getenv("FX_GEMM_BN")) BN = atoi(e) == 128 ? 128 : 256;      // tuning knobs
+  if (const char* e = getenv("FX_GEMM_GROUP")) p.group = atoi(e) > 0 ? atoi(e) : 8;
 
   CUtensorMap ta, tb;
   int rc;
@@ -369,7 +353,6 @@ extern "C" int fx_gemm_bf16(void* stream, int trans_a, int trans_b, int M, int N
   else rc = make_tma_bf16_2d(&tb, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb * 2, 64, gemm::BK);
   if (rc) return rc;
 
-  gemm::Params p{};
   p.M = M; p.N = N; p.K = K;
   p.a_mn = trans_a ? 1 : 0;
   p.b_mn = trans_b ? 0 : 1;

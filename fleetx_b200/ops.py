@@ -124,9 +124,9 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, trans_a: bool = False, trans_b: bo
          out: torch.Tensor | None = None, out_dtype=torch.bfloat16, accumulate: bool = False,
          epilogue: int = FX_EPI_NONE, bias=None, aux=None) -> torch.Tensor:
     """C[M,N] = op(A) · op(B); a, b are 2-D contiguous bf16 (see fx_gemm_bf16 for the layouts)."""
-    _need(a, torch.bfloat16, "a"), _need(b, torch.bfloat16, "b")
-    if a.dim() != 2 or b.dim() != 2:
-        raise _lib.FleetXError("gemm: operands must be 2-D")
+    for name, t in (("a", a), ("b", b)):
+        if not t.is_cuda or t.dtype != torch.bfloat16 or t.dim() != 2 or t.stride(1) != 1:
+            raise _lib.FleetXError(f"gemm: {name} must be a 2-D CUDA bf16 tensor with unit column stride")
     M, K = (a.shape[1], a.shape[0]) if trans_a else (a.shape[0], a.shape[1])
     Kb, N = (b.shape[1], b.shape[0]) if trans_b else (b.shape[0], b.shape[1])
     if K != Kb:
@@ -142,8 +142,8 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, trans_a: bool = False, trans_b: bo
         _need(bias, torch.bfloat16, "bias")
     if aux is not None:
         _need(aux, torch.bfloat16, "aux")
-    check(_lib.lib().fx_gemm_bf16(_stream(), int(trans_a), int(trans_b), M, N, K, _p(a), a.shape[1], _p(b),
-                                  b.shape[1], _p(out), N, c_dtype, int(accumulate), int(epilogue), _p(bias),
+    check(_lib.lib().fx_gemm_bf16(_stream(), int(trans_a), int(trans_b), M, N, K, _p(a), a.stride(0), _p(b),
+                                  b.stride(0), _p(out), N, c_dtype, int(accumulate), int(epilogue), _p(bias),
                                   _p(aux), N if aux is not None else 0), "fx_gemm_bf16")
     return out
 
