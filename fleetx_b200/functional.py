@@ -1,0 +1,269 @@
+"""Forward / backward of the decoder layer as explicit kernel sequences, plus autograd glue.
+
+`decoder_layer_fwd` / `decoder_layer_bwd` are the hot path: every tensor op in them is a call
+into libfleetx_b200.so (fleetx_b200.ops); torch only allocates buffers and carries the stream.
+The order of operations follows TransformerDecoderLayer.forward (hybrid_model.py:525-566) and
+MultiHeadAttention.forward (:300-347); the backward is the hand-derived adjoint of that order
+(Paddle autograd in the reference), with the tensor-parallel collectives of
+fleet.meta_parallel.{Column,Row}ParallelLinear placed where Paddle places them:
+
+  forward   allreduce after out_proj's local matmul and after linear2's   (_mp_allreduce)
+  backward  allreduce of dX entering qkv_proj and linear1                  (_c_identity backward)
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Optional, Tuple
+
+import torch
+
+from . import ops
+from .ops import FX_EPI_BIAS, FX_EPI_BIAS_GELU, FX_EPI_DGELU, FX_EPI_NONE
+
+
+@dataclass
+class LayerParams:
+    """Per-rank parameter shards, names as in the reference layer."""
+    norm1_w: torch.Tensor  # fp32 [h]
+    norm1_b: torch.Tensor
+    qkv_w: torch.Tensor    # bf16 [h, 3h/n]
+    qkv_b: torch.Tensor    # bf16 [3h/n]
+    out_w: torch.Tensor    # bf16 [h/n, h]
+    out_b: torch.Tensor    # bf16 [h]
+    norm2_w: torch.Tensor
+    norm2_b: torch.Tensor
+    lin1_w: torch.Tensor   # bf16 [h, f/n]
+    lin1_b: torch.Tensor   # bf16 [f/n]
+    lin2_w: torch.Tensor   # bf16 [f/n, h]
+    lin2_b: torch.Tensor   # bf16 [h]
+
+    def tensors(self):
+        return (self.norm1_w, self.norm1_b, self.qkv_w, self.qkv_b, self.out_w, self.out_b,
+                self.norm2_w, self.norm2_b, self.lin1_w, self.lin1_b, self.lin2_w, self.lin2_b)
+
+
+@dataclass
+class LayerMeta:
+    nh_local: int
+    hd: int
+    p_attn: float
+    p_hidden1: float
+    p_hidden2: float
+    normalize_before: bool = True
+    eps: float = 1e-5
+    # (seed, offset) of the three dropout calls: attention ('local_seed'), dropout1, dropout2
+    # ('global_seed'); see fleetx_b200.rng
+    rng_attn: Tuple[int, int] = (0, 0)
+    rng_h1: Tuple[int, int] = (0, 0)
+    rng_h2: Tuple[int, int] = (0, 0)
+    # parity-test hooks: injected keep masks for dropout1 / dropout2 (uint8 [T, h])
+    mask_h1: Optional[torch.Tensor] = None
+    mask_h2: Optional[torch.Tensor] = None
+
+
+def decoder_layer_fwd(x: torch.Tensor, P: LayerParams, M: LayerMeta, group):
+    """x: bf16 [b, s, h] -> (out bf16 [b, s, h], saved activations for backward)."""
+    b, s, h = x.shape
+    T = b * s
+    x2 = x.reshape(T, h)
+    scale = M.hd ** -0.5
+
+    if M.normalize_before:
+        ln1, mean1, rstd1 = ops.layernorm_fwd(x2, P.norm1_w, P.norm1_b, M.eps)      # :534
+        attn_in = ln1
+    else:
+        ln1 = mean1 = rstd1 = None
+        attn_in = x2
+    qkv = ops.gemm(attn_in, P.qkv_w, epilogue=FX_EPI_BIAS, bias=P.qkv_b)            # :166
+    ctx, lse = ops.attn_causal_fwd(qkv.view(b, s, -1), M.nh_local, M.hd, scale, M.p_attn, *M.rng_attn)  # :167-173, :268-298
+    ctx2 = ctx.view(T, -1)
+    attn_out = ops.gemm(ctx2, P.out_w)                                              # :340 local matmul
+    group.all_reduce_(attn_out)                                                     # _mp_allreduce
+    r1 = ops.bias_dropout_residual_fwd(attn_out, P.out_b, x2, M.p_hidden1, *M.rng_h1, mask_in=M.mask_h1)  # :546-547
+    del attn_out
+    if M.normalize_before:
+        x1 = r1
+        ln2, mean2, rstd2 = ops.layernorm_fwd(x1, P.norm2_w, P.norm2_b, M.eps)      # :554
+        ffn_in = ln2
+    else:
+        x1, mean1, rstd1 = ops.layernorm_fwd(r1, P.norm1_w, P.norm1_b, M.eps)       # :550
+        ln2 = mean2 = rstd2 = None
+        ffn_in = x1
+    z = torch.empty(T, P.lin1_w.shape[1], dtype=torch.bfloat16, device=x.device)
+    act = ops.gemm(ffn_in, P.lin1_w, epilogue=FX_EPI_BIAS_GELU, bias=P.lin1_b, aux=z)  # :558-559
+    y2 = ops.gemm(act, P.lin2_w)                                                    # :558 local matmul
+    group.all_reduce_(y2)                                                           # _mp_allreduce
+    r2 = ops.bias_dropout_residual_fwd(y2, P.lin2_b, x1, M.p_hidden2, *M.rng_h2, mask_in=M.mask_h2)  # :556-561
+    del y2
+    if M.normalize_before:
+        out = r2
+        mean3 = rstd3 = None
+    else:
+        out, mean3, rstd3 = ops.layernorm_fwd(r2, P.norm2_w, P.norm2_b, M.eps)      # :564
+    saved = dict(x=x2, ln1=ln1, mean1=mean1, rstd1=rstd1, qkv=qkv, ctx=ctx2, lse=lse, r1=r1, x1=x1,
+                 ln2=ln2, mean2=mean2, rstd2=rstd2, z=z, act=act, r2=r2, mean3=mean3, rstd3=rstd3,
+                 shape=(b, s, h))
+    return out.view(b, s, h), saved
+
+
+def decoder_layer_bwd(dout: torch.Tensor, saved: dict, P: LayerParams, M: LayerMeta, group):
+    """dout bf16 [b, s, h] -> (dx, dict of per-rank parameter gradients, keyed like LayerParams)."""
+    b, s, h = saved["shape"]
+    T = b * s
+    d = dout.reshape(T, h)
+    scale = M.hd ** -0.5
+    g = {}
+
+    if not M.normalize_before:
+        # out = LN2(r2)
+        d, g["norm2_w"], g["norm2_b"] = ops.layernorm_bwd(d, saved["r2"], P.norm2_w, saved["mean3"], saved["rstd3"])
+    # r2 = x1 + dropout2(y2 + b2): d is d(r2); the skip-path share d(x1) += d is folded in later
+    d_y2 = ops.bias_dropout_residual_bwd(d, M.p_hidden2, *M.rng_h2, mask_in=M.mask_h2)
+    g["lin2_b"] = ops.colsum(d_y2)
+    g["lin2_w"] = ops.gemm(saved["act"], d_y2, trans_a=True)                       # dW2 = act^T · dY
+    d_z = ops.gemm(d_y2, P.lin2_w, trans_b=True, epilogue=FX_EPI_DGELU, aux=saved["z"])  # (dY · W2^T) ∘ gelu'(z)
+    del d_y2
+    g["lin1_b"] = ops.colsum(d_z)
+    ffn_in = saved["ln2"] if M.normalize_before else saved["x1"]
+    g["lin1_w"] = ops.gemm(ffn_in, d_z, trans_a=True)
+    d_ffn_in = ops.gemm(d_z, P.lin1_w, trans_b=True)
+    del d_z
+    group.all_reduce_(d_ffn_in)                                                     # backward of _c_identity
+    if M.normalize_before:
+        # x1 feeds LN2 and the skip: d(x1) = LN2'(d_ffn_in) + d
+        d_x1, g["norm2_w"], g["norm2_b"] = ops.layernorm_bwd(d_ffn_in, saved["x1"], P.norm2_w, saved["mean2"],
+                                                             saved["rstd2"], dresidual=d)
+        d_r1 = d_x1
+    else:
+        # x1 = LN1(r1) feeds linear1 and the skip: d(x1) = d_ffn_in + d (an add = dropout-free residual kernel)
+        d_x1 = ops.bias_dropout_residual_fwd(d_ffn_in, None, d, 0.0, 0, 0)
+        d_r1, g["norm1_w"], g["norm1_b"] = ops.layernorm_bwd(d_x1, saved["r1"], P.norm1_w, saved["mean1"], saved["rstd1"])
+    del d_ffn_in
+    # r1 = x + dropout1(attn_out + bo)
+    d_ao = ops.bias_dropout_residual_bwd(d_r1, M.p_hidden1, *M.rng_h1, mask_in=M.mask_h1)
+    g["out_b"] = ops.colsum(d_ao)
+    g["out_w"] = ops.gemm(saved["ctx"], d_ao, trans_a=True)
+    d_ctx = ops.gemm(d_ao, P.out_w, trans_b=True)
+    del d_ao
+    d_qkv = ops.attn_causal_bwd(d_ctx.view(b, s, -1), saved["qkv"].view(b, s, -1), saved["ctx"].view(b, s, -1),
+                                saved["lse"], M.nh_local, M.hd, scale, M.p_attn, *M.rng_attn).view(T, -1)
+    del d_ctx
+    g["qkv_b"] = ops.colsum(d_qkv)
+    attn_in = saved["ln1"] if M.normalize_before else saved["x"]
+    g["qkv_w"] = ops.gemm(attn_in, d_qkv, trans_a=True)
+    d_attn_in = ops.gemm(d_qkv, P.qkv_w, trans_b=True)
+    del d_qkv
+    group.all_reduce_(d_attn_in)                                                    # backward of _c_identity
+    if M.normalize_before:
+        dx, g["norm1_w"], g["norm1_b"] = ops.layernorm_bwd(d_attn_in, saved["x"], P.norm1_w, saved["mean1"],
+                                                           saved["rstd1"], dresidual=d_r1)
+    else:
+        dx = ops.bias_dropout_residual_fwd(d_attn_in, None, d_r1, 0.0, 0, 0)
+    return dx.view(b, s, h), g
+
+
+_GRAD_ORDER = ("norm1_w", "norm1_b", "qkv_w", "qkv_b", "out_w", "out_b",
+               "norm2_w", "norm2_b", "lin1_w", "lin1_b", "lin2_w", "lin2_b")
+
+
+class DecoderLayerFunction(torch.autograd.Function):
+    """One autograd node for the whole layer: no framework ops between the kernels."""
+
+    @staticmethod
+    def forward(ctx, x, meta, group, *params):
+        P = LayerParams(*params)
+        out, saved = decoder_layer_fwd(x, P, meta, group)
+        ctx.saved, ctx.P, ctx.meta, ctx.group = saved, P, meta, group
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        dx, g = decoder_layer_bwd(dout.contiguous(), ctx.saved, ctx.P, ctx.meta, ctx.group)
+        ctx.saved = None
+        return (dx, None, None) + tuple(g[k] for k in _GRAD_ORDER)
+
+
+# ---------------------------------------------------------------------------- standalone linears
+class ColumnParallelLinearFunction(torch.autograd.Function):
+    """y = x·W_shard + b_shard; backward allreduces dX over the mp group (_c_identity)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, group):
+        x2 = x.reshape(-1, x.shape[-1])
+        y = ops.gemm(x2, weight, epilogue=FX_EPI_BIAS if bias is not None else FX_EPI_NONE, bias=bias)
+        ctx.save_for_backward(x2, weight)
+        ctx.has_bias, ctx.group, ctx.in_shape = bias is not None, group, x.shape
+        return y.view(*x.shape[:-1], weight.shape[1])
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, weight = ctx.saved_tensors
+        dy2 = dy.reshape(-1, dy.shape[-1]).contiguous()
+        dw = ops.gemm(x2, dy2, trans_a=True)
+        db = ops.colsum(dy2) if ctx.has_bias else None
+        dx = ops.gemm(dy2, weight, trans_b=True)
+        ctx.group.all_reduce_(dx)
+        return dx.view(ctx.in_shape), dw, db, None
+
+
+class RowParallelLinearFunction(torch.autograd.Function):
+    """y = allreduce(x_shard·W_shard) + b; the bias is added once, after the allreduce."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, group):
+        x2 = x.reshape(-1, x.shape[-1])
+        if group.nranks == 1:
+            y = ops.gemm(x2, weight, epilogue=FX_EPI_BIAS if bias is not None else FX_EPI_NONE, bias=bias)
+        else:
+            y = ops.gemm(x2, weight)
+            group.all_reduce_(y)
+            if bias is not None:
+                y = _add_bias(y, bias)
+        ctx.save_for_backward(x2, weight)
+        ctx.has_bias, ctx.in_shape = bias is not None, x.shape
+        return y.view(*x.shape[:-1], weight.shape[1])
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, weight = ctx.saved_tensors
+        dy2 = dy.reshape(-1, dy.shape[-1]).contiguous()
+        dw = ops.gemm(x2, dy2, trans_a=True)
+        db = ops.colsum(dy2) if ctx.has_bias else None
+        dx = ops.gemm(dy2, weight, trans_b=True)
+        return dx.view(ctx.in_shape), dw, db, None
+
+
+def _add_bias(y: torch.Tensor, bias: torch.Tensor) -> torch.Tensor:
+    """y + bias after the allreduce, through the residual kernel with p = 0 and a zero residual
+    (cached per shape, so no memset on the hot path)."""
+    return ops.bias_dropout_residual_fwd(y, bias, _zeros_like_cached(y), 0.0, 0, 0)
+
+
+_zero_cache: dict = {}
+
+
+def _zeros_like_cached(t: torch.Tensor) -> torch.Tensor:
+    key = (t.device, tuple(t.shape))
+    z = _zero_cache.get(key)
+    if z is None:
+        z = torch.zeros_like(t)
+        _zero_cache[key] = z
+    return z
+
+
+class CausalSelfAttentionFunction(torch.autograd.Function):
+    """core_attn on the packed qkv_proj output (hybrid_model.py:165-186, 268-298)."""
+
+    @staticmethod
+    def forward(ctx, qkv, nh_local, hd, p_drop, seed, offset):
+        out, lse = ops.attn_causal_fwd(qkv, nh_local, hd, hd ** -0.5, p_drop, seed, offset)
+        ctx.save_for_backward(qkv, out, lse)
+        ctx.cfg = (nh_local, hd, p_drop, seed, offset)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        qkv, out, lse = ctx.saved_tensors
+        nh_local, hd, p_drop, seed, offset = ctx.cfg
+        dqkv = ops.attn_causal_bwd(dout.contiguous(), qkv, out, lse, nh_local, hd, hd ** -0.5, p_drop, seed, offset)
+        return dqkv, None, None, None, None, None

@@ -1,0 +1,265 @@
+"""Host-side mirror of the reference's layer API for the hot path — same class names, constructor
+arguments, parameter names and [in, out] weight layout, so it stays a drop-in:
+
+  ColumnParallelLinear / RowParallelLinear   fleet.meta_parallel.* (signatures mirrored in-tree at
+                                             sequence_parallel_utils.py:151-159, 236-244)
+  MultiHeadAttention                         hybrid_model.py:69-347
+  TransformerDecoderLayer                    hybrid_model.py:439-571
+
+torch.nn.Module stands in for paddle.nn.Layer (Paddle is not installable here; INTEGRATION.md
+shows the Paddle custom-op binding over the same C ABI). All arithmetic runs in
+libfleetx_b200.so; a CPU tensor or a missing library is an error, never a fallback.
+"""
+from __future__ import annotations
+
+import collections
+from typing import Optional
+
+import torch
+from torch import nn
+
+from . import functional as Fn
+from .dist import resolve_group
+from .rng import get_rng_state_tracker
+
+_INIT_STD = 0.02  # initializer_range (hybrid_model.py:671-673)
+
+
+def _init_weight(shape, device, dtype) -> torch.Tensor:
+    return (torch.randn(*shape, dtype=torch.float32) * _INIT_STD).to(device=device, dtype=dtype)
+
+
+class ColumnParallelLinear(nn.Module):
+    """Y = X·W + b with W [in, out] split by columns over the mp group; gather_output is not
+    supported on this path (the decoder layer always passes gather_output=False,
+    hybrid_model.py:125-131, 497-503)."""
+
+    def __init__(self, in_features, out_features, weight_attr=None, has_bias=None, gather_output=True,
+                 fuse_matmul_bias=False, mp_group=None, name=None, device="cuda", dtype=torch.bfloat16):
+        super().__init__()
+        self.model_parallel_group = resolve_group(mp_group)
+        self.world_size = self.model_parallel_group.nranks
+        self._name = name
+        self.is_mp = self.world_size > 1
+        self.gather_output = gather_output
+        if gather_output and self.world_size > 1:
+            raise NotImplementedError("ColumnParallelLinear(gather_output=True) is outside the decoder-layer path")
+        assert out_features % self.world_size == 0, (
+            f"Number of column of the weight for linear ({out_features}) must be divisible by "
+            f"model parallel size ({self.world_size})")
+        self.output_size_per_partition = out_features // self.world_size
+        self.fuse_matmul_bias = fuse_matmul_bias  # the bias add is always fused into the GEMM epilogue here
+        self.weight = nn.Parameter(_init_weight((in_features, self.output_size_per_partition), device, dtype))
+        self.weight.is_distributed = self.is_mp
+        if has_bias:
+            self.bias = nn.Parameter(torch.zeros(self.output_size_per_partition, device=device, dtype=dtype))
+            self.bias.is_distributed = self.is_mp
+        else:
+            self.bias = None
+
+    def forward(self, x):
+        return Fn.ColumnParallelLinearFunction.apply(x, self.weight, self.bias, self.model_parallel_group)
+
+
+class RowParallelLinear(nn.Module):
+    """Y = allreduce(X_shard·W_shard) + b with W [in, out] split by rows; input_is_parallel must be
+    True on this path (hybrid_model.py:157-163, 505-511)."""
+
+    def __init__(self, in_features, out_features, weight_attr=None, has_bias=True, input_is_parallel=False,
+                 fuse_matmul_bias=False, mp_group=None, name=None, device="cuda", dtype=torch.bfloat16):
+        super().__init__()
+        self.model_parallel_group = resolve_group(mp_group)
+        self.world_size = self.model_parallel_group.nranks
+        self._name = name
+        self.is_mp = self.world_size > 1
+        self.input_is_parallel = input_is_parallel
+        if not input_is_parallel and self.world_size > 1:
+            raise NotImplementedError("RowParallelLinear(input_is_parallel=False) is outside the decoder-layer path")
+        assert in_features % self.world_size == 0, (
+            f"Number of row of the weight for linear ({in_features}) must be divisible by "
+            f"model parallel size ({self.world_size})")
+        self.input_size_per_partition = in_features // self.world_size
+        self.fuse_matmul_bias = fuse_matmul_bias
+        self.weight = nn.Parameter(_init_weight((self.input_size_per_partition, out_features), device, dtype))
+        self.weight.is_distributed = self.is_mp
+        if has_bias:
+            self.bias = nn.Parameter(torch.zeros(out_features, device=device, dtype=dtype))  # replicated
+        else:
+            self.bias = None
+
+    def forward(self, x):
+        return Fn.RowParallelLinearFunction.apply(x, self.weight, self.bias, self.model_parallel_group)
+
+
+class LayerNorm(nn.Module):
+    """nn.LayerNorm(d_model, epsilon) with fp32 affine parameters (they stay fp32 under AMP-O2)."""
+
+    def __init__(self, normalized_shape, epsilon=1e-5, device="cuda"):
+        super().__init__()
+        self._epsilon = epsilon
+        self.weight = nn.Parameter(torch.ones(normalized_shape, device=device, dtype=torch.float32))
+        self.bias = nn.Parameter(torch.zeros(normalized_shape, device=device, dtype=torch.float32))
+
+
+class MultiHeadAttention(nn.Module):
+    """hybrid_model.py:69-163. Only the fused-qkv, self-attention, training/eval-without-cache
+    path the decoder layer takes (fuse=True, use_cache=False) is built."""
+
+    Cache = collections.namedtuple("Cache", ["k", "v"])
+    StaticCache = collections.namedtuple("StaticCache", ["k", "v"])
+
+    def __init__(self, embed_dim, num_heads, dropout=0., kdim=None, vdim=None, need_weights=False,
+                 weight_attr=None, bias_attr=None, fuse=True, num_partitions=1, fused_linear=False,
+                 use_recompute=False, recompute_granularity="full", sequence_parallel=False,
+                 mp_group=None, device="cuda", dtype=torch.bfloat16):
+        super().__init__()
+        self.embed_dim = embed_dim
+        self.kdim = kdim if kdim is not None else embed_dim
+        self.vdim = vdim if vdim is not None else embed_dim
+        self.num_heads = num_heads
+        self.dropout = dropout
+        self.need_weights = need_weights
+        self.fuse = fuse
+        self.use_recompute = use_recompute
+        self.recompute_granularity = recompute_granularity
+        self.sequence_parallel = sequence_parallel
+        if sequence_parallel:
+            raise NotImplementedError("sequence_parallel is the next scope row (SURVEY §8f #1), not built yet")
+        if not fuse:
+            raise NotImplementedError("only the fused qkv projection (fuse=True, the reference default) is built")
+        if need_weights:
+            raise NotImplementedError("need_weights=True would materialise the s x s matrix; not on this path")
+        self.head_dim = embed_dim // num_heads
+        assert self.head_dim * num_heads == self.embed_dim, "embed_dim must be divisible by num_heads"
+        assert self.num_heads % num_partitions == 0, "num_heads {} must be divisible by num_partitions {}".format(
+            self.num_heads, num_partitions)
+        self.model_parallel_group = resolve_group(mp_group, num_partitions)
+        self.num_heads = self.num_heads // num_partitions
+        assert self.kdim == embed_dim and self.vdim == embed_dim
+        self.qkv_proj = ColumnParallelLinear(embed_dim, 3 * embed_dim, weight_attr=weight_attr, has_bias=True,
+                                             gather_output=False, fuse_matmul_bias=fused_linear,
+                                             mp_group=self.model_parallel_group, device=device, dtype=dtype)
+        self.out_proj = RowParallelLinear(embed_dim, embed_dim, weight_attr=weight_attr, has_bias=True,
+                                          input_is_parallel=True, fuse_matmul_bias=fused_linear,
+                                          mp_group=self.model_parallel_group, device=device, dtype=dtype)
+
+    def gen_cache(self, key, value=None, type=Cache):
+        raise NotImplementedError("KV-cache inference is the next scope row (SURVEY §8f #4), not built yet")
+
+    def forward(self, query, key=None, value=None, attn_mask=None, use_cache=False, cache=None):
+        if use_cache or cache is not None:
+            raise NotImplementedError("use_cache/cache (inference) is outside the fwd+bwd path")
+        if attn_mask is not None:
+            raise NotImplementedError("only the causal mask is fused (training passes attn_mask=None, "
+                                      "hybrid_model.py:733-734); the model's eval mask is the same causal mask")
+        if (key is not None and key is not query) or (value is not None and value is not query):
+            raise NotImplementedError("self-attention only")
+        mix = self.qkv_proj(query)  # [b, s, 3h/n], packed per head q|k|v
+        p = self.dropout if self.training else 0.0
+        seed, offset = (0, 0)
+        if p > 0:
+            with get_rng_state_tracker().rng_state("local_seed"):  # :280
+                seed, offset = get_rng_state_tracker().draw()
+        out = Fn.CausalSelfAttentionFunction.apply(mix.contiguous(), self.num_heads, self.head_dim, p, seed, offset)
+        return self.out_proj(out)
+
+
+class TransformerDecoderLayer(nn.Module):
+    """hybrid_model.py:439-571. forward() runs the whole layer as one autograd node made of
+    libfleetx_b200 kernels."""
+
+    def __init__(self, d_model, nhead, dim_feedforward, dropout=0.1, activation="gelu", attn_dropout=None,
+                 act_dropout=None, normalize_before=True, weight_attr=None, bias_attr=None, num_partitions=1,
+                 fused_linear=False, recompute_attn=False, use_recompute=False, recompute_granularity="full",
+                 sequence_parallel=False, mp_group=None, device="cuda", dtype=torch.bfloat16):
+        config = {k: v for k, v in locals().items() if k not in ("self", "__class__")}
+        super().__init__()
+        self._config = config
+        attn_dropout = dropout if attn_dropout is None else attn_dropout
+        act_dropout = dropout if act_dropout is None else act_dropout
+        self.normalize_before = normalize_before
+        self.use_recompute = use_recompute
+        self.recompute_granularity = recompute_granularity
+        self.sequence_parallel = sequence_parallel
+        if sequence_parallel:
+            raise NotImplementedError("sequence_parallel is the next scope row (SURVEY §8f #1), not built yet")
+        if activation != "gelu":
+            # the reference stores `activation` but hard-codes F.gelu(approximate=True) (:523, :558)
+            raise NotImplementedError("the reference layer always applies tanh-GELU")
+        self.model_parallel_group = resolve_group(mp_group, num_partitions)
+        assert dim_feedforward % num_partitions == 0
+        self.self_attn = MultiHeadAttention(d_model, nhead, dropout=attn_dropout, weight_attr=weight_attr,
+                                            bias_attr=bias_attr, num_partitions=num_partitions,
+                                            fused_linear=fused_linear, use_recompute=use_recompute,
+                                            recompute_granularity=recompute_granularity,
+                                            mp_group=self.model_parallel_group, device=device, dtype=dtype)
+        self.linear1 = ColumnParallelLinear(d_model, dim_feedforward, weight_attr=weight_attr, gather_output=False,
+                                            has_bias=True, fuse_matmul_bias=fused_linear,
+                                            mp_group=self.model_parallel_group, device=device, dtype=dtype)
+        self.linear2 = RowParallelLinear(dim_feedforward, d_model, weight_attr=weight_attr, input_is_parallel=True,
+                                         has_bias=True, fuse_matmul_bias=fused_linear,
+                                         mp_group=self.model_parallel_group, device=device, dtype=dtype)
+        self.norm1 = LayerNorm(d_model, epsilon=1e-5, device=device)
+        self.norm2 = LayerNorm(d_model, epsilon=1e-5, device=device)
+        self.dropout1_p = dropout
+        self.dropout2_p = act_dropout
+        self.activation = activation
+        # parity-test hooks (uint8 keep masks [b*s, h]); None = use the Philox generator
+        self._inject_mask1: Optional[torch.Tensor] = None
+        self._inject_mask2: Optional[torch.Tensor] = None
+
+    def _params(self):
+        a = self.self_attn
+        return (self.norm1.weight, self.norm1.bias, a.qkv_proj.weight, a.qkv_proj.bias, a.out_proj.weight,
+                a.out_proj.bias, self.norm2.weight, self.norm2.bias, self.linear1.weight, self.linear1.bias,
+                self.linear2.weight, self.linear2.bias)
+
+    def _meta(self) -> Fn.LayerMeta:
+        tracker = get_rng_state_tracker()
+        train = self.training
+        p_attn = self.self_attn.dropout if train else 0.0
+        p1 = self.dropout1_p if train else 0.0
+        p2 = self.dropout2_p if train else 0.0
+        rng_attn = rng_h1 = rng_h2 = (0, 0)
+        # same consumption order as the reference forward: attention ('local_seed', :280), then
+        # dropout1 and dropout2 ('global_seed', :546 and :556)
+        if p_attn > 0:
+            rng_attn = tracker.draw("local_seed")
+        if p1 > 0 and self._inject_mask1 is None:
+            rng_h1 = tracker.draw("global_seed")
+        if p2 > 0 and self._inject_mask2 is None:
+            rng_h2 = tracker.draw("global_seed")
+        return Fn.LayerMeta(nh_local=self.self_attn.num_heads, hd=self.self_attn.head_dim, p_attn=p_attn,
+                            p_hidden1=p1, p_hidden2=p2, normalize_before=self.normalize_before,
+                            rng_attn=rng_attn, rng_h1=rng_h1, rng_h2=rng_h2,
+                            mask_h1=self._inject_mask1 if p1 > 0 else None,
+                            mask_h2=self._inject_mask2 if p2 > 0 else None)
+
+    def forward(self, tgt, memory=None, tgt_mask=None, use_cache=False, cache=None):
+        if use_cache or cache is not None:
+            raise NotImplementedError("use_cache/cache (inference) is outside the fwd+bwd path")
+        if tgt_mask is not None:
+            raise NotImplementedError("only the causal mask is fused (training passes tgt_mask=None)")
+        if not tgt.is_cuda:
+            raise RuntimeError("TransformerDecoderLayer needs CUDA tensors: there is no CPU path")
+        return Fn.DecoderLayerFunction.apply(tgt.contiguous(), self._meta(), self.model_parallel_group,
+                                             *self._params())
+
+    def gen_cache(self, memory):
+        return self.self_attn.gen_cache(memory, type=self.self_attn.Cache)
+
+    # -------------------------------------------------------------------------- checkpoints
+    def load_full_state(self, full: dict) -> None:
+        """Load FULL (unsharded) reference-named parameters, keeping this rank's shard — the
+        per-mp-rank layout of the reference's checkpoints (eager_engine.py:581-615)."""
+        from .dist import shard_columns, shard_rows
+
+        g = self.model_parallel_group
+        own = dict(self.named_parameters())
+        for name, t in full.items():
+            if name in ("self_attn.qkv_proj.weight", "self_attn.qkv_proj.bias", "linear1.weight", "linear1.bias"):
+                t = shard_columns(t, g.rank, g.nranks)
+            elif name in ("self_attn.out_proj.weight", "linear2.weight"):
+                t = shard_rows(t, g.rank, g.nranks)
+            with torch.no_grad():
+                own[name].copy_(t.to(own[name].dtype))
