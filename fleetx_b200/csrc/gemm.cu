@@ -5,7 +5,7 @@
 //               4..6-stage shared-memory ring (128-byte swizzle), signalling `full` mbarriers
 //   warp 1      MMA issuer: one lane issues tcgen05.mma (M=128, N=BN, K=16) into one of two
 //               TMEM accumulators (2 x BN fp32 columns), tcgen05.commit frees ring slots
-//   warps 2..5  epilogue: tcgen05.ld the finished accumulator (one row per thread), transpose
+//   warps 2..9  epilogue: tcgen05.ld the finished accumulator (one row per thread), transpose
 //               32x32 blocks through shared memory so global accesses are sector-coalesced,
 //               apply bias / GELU / GELU' / accumulate, store bf16 or fp32 — overlapped with
 //               the next tile's main loop through the second accumulator
@@ -25,7 +25,8 @@ using namespace tc5;
 
 constexpr int BM = 128;
 constexpr int BK = 64;  // 64 bf16 = 128 B = one swizzle row
-constexpr int NUM_THREADS = 192;
+constexpr int NUM_EPI_WARPS = 8;  // two per TMEM lane quarter, interleaved over 32-column chunks
+constexpr int NUM_THREADS = 64 + NUM_EPI_WARPS * 32;
 constexpr int A_STAGE_BYTES = BM * BK * 2;
 constexpr int CHUNK_BYTES = BK * 128;  // one 64-wide MN chunk of an MN-major operand
 
@@ -48,7 +49,7 @@ struct Cfg {
   static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
   static constexpr int STAGES = BN == 256 ? 4 : 6;
   static constexpr int BAR_BYTES = 256;
-  static constexpr int STG_BYTES = 4 * 32 * 33 * 4;  // per-epilogue-warp 32x32 fp32 transpose tile (+1 pad)
+  static constexpr int STG_BYTES = NUM_EPI_WARPS * 32 * 33 * 4;  // per-epilogue-warp 32x32 fp32 transpose tile (+1 pad)
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + STG_BYTES + 1024;
   static constexpr int TMEM_COLS = 2 * BN;
 };
@@ -64,18 +65,24 @@ __device__ __forceinline__ void tile_coords(const Params& p, int tile, int& m_bl
   n_blk = r / gsize;
 }
 
+__device__ __forceinline__ float tanh_approx(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));  // one MUFU op, rel. error 2^-11 (bf16 output: 2^-8)
+  return y;
+}
 __device__ __forceinline__ float gelu_tanh(float z) {
-  // 0.5 z (1 + tanh(u)) == z * sigmoid(2u),  u = sqrt(2/pi) (z + 0.044715 z^3)
-  const float u = 0.7978845608028654f * z * (1.0f + 0.044715f * z * z);
-  return z / (1.0f + __expf(-2.0f * u));
+  // 0.5 z (1 + tanh(u)),  u = sqrt(2/pi) (z + 0.044715 z^3)   (F.gelu(approximate=True), hybrid_model.py:558)
+  const float u = z * (0.7978845608028654f + 0.035677408136300125f * z * z);
+  const float hz = 0.5f * z;
+  return fmaf(hz, tanh_approx(u), hz);
 }
 __device__ __forceinline__ float gelu_tanh_grad(float z) {
   const float z2 = z * z;
-  const float u = 0.7978845608028654f * z * (1.0f + 0.044715f * z2);
-  const float s = 1.0f / (1.0f + __expf(-2.0f * u));  // = 0.5 (1 + tanh u)
-  const float du = 0.7978845608028654f * (1.0f + 3.0f * 0.044715f * z2);
-  // d/dz [z s(2u)] = s + z * 2 s (1 - s) du
-  return s + 2.0f * z * s * (1.0f - s) * du;
+  const float u = z * (0.7978845608028654f + 0.035677408136300125f * z2);
+  const float t = tanh_approx(u);
+  const float du = 0.7978845608028654f + 0.10703222440890037f * z2;  // du/dz
+  // d/dz [0.5 z (1 + t)] = 0.5 (1 + t) + 0.5 z (1 - t^2) du
+  return 0.5f * (1.0f + t) + 0.5f * z * (1.0f - t * t) * du;
 }
 
 // Epilogue math + store for one 32x32 fp32 block that a warp has just transposed through its
@@ -162,7 +169,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
       }
       for (int i = 0; i < 2; ++i) {
         mbar_init(&tfull[i], 1);
-        mbar_init(&tempty[i], 4);
+        mbar_init(&tempty[i], NUM_EPI_WARPS);
       }
       mbar_fence_init();
     }
@@ -262,7 +269,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
+      for (int c = (warp - 2) >> 2; c < BN / 32; c += NUM_EPI_WARPS / 4) {
         uint32_t r[32];
         tmem_ld_32x32(taddr + c * 32, r);
         tmem_ld_wait();

@@ -120,6 +120,20 @@ def colsum(x: torch.Tensor, out_dtype=torch.bfloat16) -> torch.Tensor:
 
 
 # ------------------------------------------------------------------------------- GEMM
+_gemm_profile = None
+
+
+def profile_gemm(enable: bool):
+    """bench.py hook: while enabled, every gemm() is bracketed by CUDA events on its stream.
+    Turning it off returns the records [(flops, start_event, end_event), ...]."""
+    global _gemm_profile
+    if enable:
+        _gemm_profile = []
+        return None
+    rec, _gemm_profile = _gemm_profile, None
+    return rec or []
+
+
 def gemm(a: torch.Tensor, b: torch.Tensor, *, trans_a: bool = False, trans_b: bool = False,
          out: torch.Tensor | None = None, out_dtype=torch.bfloat16, accumulate: bool = False,
          epilogue: int = FX_EPI_NONE, bias=None, aux=None) -> torch.Tensor:
@@ -142,9 +156,15 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, trans_a: bool = False, trans_b: bo
         _need(bias, torch.bfloat16, "bias")
     if aux is not None:
         _need(aux, torch.bfloat16, "aux")
+    if _gemm_profile is not None:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
     check(_lib.lib().fx_gemm_bf16(_stream(), int(trans_a), int(trans_b), M, N, K, _p(a), a.stride(0), _p(b),
                                   b.stride(0), _p(out), N, c_dtype, int(accumulate), int(epilogue), _p(bias),
                                   _p(aux), N if aux is not None else 0), "fx_gemm_bf16")
+    if _gemm_profile is not None:
+        e1.record()
+        _gemm_profile.append((2.0 * M * N * K, e0, e1))
     return out
 
 

@@ -97,16 +97,16 @@ def main():
             print(json.dumps({"op": "colsum", "rows": rows, "h": h, "ms": round(med, 4), "GBs": round(byt / med / 1e6, 1),
                               "frac_of_" + src: round(byt / med / 1e6 / hbm, 3)}), flush=True)
     if "attn" in which:
-        for b, s, nh, hd in ((8, 2048, 32, 64), (1, 2048, 32, 64), (2, 4096, 5, 128), (8, 2048, 4, 128)):
+        for b, s, nh, hd, pd in ((8, 2048, 32, 64, 0.1), (8, 2048, 32, 64, 0.0), (1, 2048, 32, 64, 0.1), (2, 4096, 5, 128, 0.1), (8, 2048, 4, 128, 0.1), (8, 2048, 4, 128, 0.0)):
             qkv = torch.randn(b, s, nh * 3 * hd, device=dev).to(torch.bfloat16)
             try:
-                med, _ = timeit(lambda: ops.attn_causal_fwd(qkv, nh, hd, hd ** -0.5, 0.1, 1, 0), flush=flush)
+                med, _ = timeit(lambda: ops.attn_causal_fwd(qkv, nh, hd, hd ** -0.5, pd, 1, 0), flush=flush, reps=2)
                 fl = 2.0 * b * nh * s * s * hd  # causal half of 4·b·nh·s²·hd
-                print(json.dumps({"op": "attn_fwd", "b": b, "s": s, "nh": nh, "hd": hd, "ms": round(med, 4),
+                print(json.dumps({"op": "attn_fwd", "b": b, "s": s, "nh": nh, "hd": hd, "p": pd, "ms": round(med, 4),
                                   "tflops": round(fl / med / 1e9, 1)}), flush=True)
-                out, lse = ops.attn_causal_fwd(qkv, nh, hd, hd ** -0.5, 0.1, 1, 0)
-                med, _ = timeit(lambda: ops.attn_causal_bwd(out, qkv, out, lse, nh, hd, hd ** -0.5, 0.1, 1, 0), flush=flush)
-                print(json.dumps({"op": "attn_bwd", "b": b, "s": s, "nh": nh, "hd": hd, "ms": round(med, 4),
+                out, lse = ops.attn_causal_fwd(qkv, nh, hd, hd ** -0.5, pd, 1, 0)
+                med, _ = timeit(lambda: ops.attn_causal_bwd(out, qkv, out, lse, nh, hd, hd ** -0.5, pd, 1, 0), flush=flush, reps=2)
+                print(json.dumps({"op": "attn_bwd", "b": b, "s": s, "nh": nh, "hd": hd, "p": pd, "ms": round(med, 4),
                                   "tflops": round(2.5 * fl / med / 1e9, 1)}), flush=True)
             except Exception as e:  # noqa: BLE001
                 print(json.dumps({"op": "attn", "error": str(e)[:200]}), flush=True)
