@@ -88,3 +88,43 @@ def shard_rows(t: torch.Tensor, rank: int, nranks: int) -> torch.Tensor:
     if t.shape[0] % nranks:
         raise ValueError(f"dimension {t.shape[0]} is not divisible by mp degree {nranks}")
     return t.chunk(nranks, dim=0)[rank].contiguous()
+
+
+# ------------------------------------------------------------------------------ autograd collectives
+class _CIdentity(torch.autograd.Function):
+    """Paddle's `_c_identity`: identity forward, allreduce(sum) of the gradient backward — what
+    ColumnParallelLinear puts in front of its matmul."""
+
+    @staticmethod
+    def forward(ctx, x, group):
+        ctx.group = group
+        return x
+
+    @staticmethod
+    def backward(ctx, dy):
+        dy = dy.contiguous().clone()
+        ctx.group.all_reduce_(dy)
+        return dy, None
+
+
+class _MpAllReduce(torch.autograd.Function):
+    """Paddle's `_mp_allreduce`: allreduce(sum) forward, identity backward — what
+    RowParallelLinear puts behind its matmul."""
+
+    @staticmethod
+    def forward(ctx, x, group):
+        y = x.contiguous().clone()
+        group.all_reduce_(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        return dy, None
+
+
+def c_identity(x: torch.Tensor, group) -> torch.Tensor:
+    return _CIdentity.apply(x, group)
+
+
+def mp_allreduce(x: torch.Tensor, group) -> torch.Tensor:
+    return _MpAllReduce.apply(x, group)

@@ -1,0 +1,103 @@
+"""world_size-2 (and 4) gloo runs on CPU of the multi-rank host logic: each process holds one mp
+rank's parameter shard, computes its share of the layer with the oracle's ops, and exchanges
+through fleetx_b200.dist (TorchDistGroup + the _c_identity / _mp_allreduce autograd pair). The
+result and every per-rank gradient must equal the single-process oracle."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from oracle import decoder_layer as O
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _rank_forward(x, shard, full, cfg, group, masks, rank):
+    from fleetx_b200.dist import c_identity, mp_allreduce
+
+    nhl, hd = cfg.nhead // cfg.num_partitions, cfg.hd
+    t = O.layer_norm(x, full["norm1.weight"], full["norm1.bias"])
+    mix = O.column_parallel_linear(c_identity(t, group), shard["self_attn.qkv_proj.weight"], shard["self_attn.qkv_proj.bias"])
+    q, k, v = O.fuse_prepare_qkv(mix, nhl, hd)
+    ctx = O.core_attn(q, k, v, hd, cfg.attn_dropout, masks.attn[rank] if masks.attn else None)
+    t = mp_allreduce(ctx @ shard["self_attn.out_proj.weight"], group) + full["self_attn.out_proj.bias"]
+    t = x + O.dropout(t, cfg.dropout, masks.hidden1)
+    res = t
+    t = O.layer_norm(t, full["norm2.weight"], full["norm2.bias"])
+    a = O.gelu_tanh(O.column_parallel_linear(c_identity(t, group), shard["linear1.weight"], shard["linear1.bias"]))
+    t = mp_allreduce(a @ shard["linear2.weight"], group) + full["linear2.bias"]
+    return res + O.dropout(t, cfg.act_dropout, masks.hidden2)
+
+
+def _worker(rank, world, port, ret):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from fleetx_b200.dist import TorchDistGroup, shard_columns, shard_rows
+        from fleetx_b200.rng import get_rng_state_tracker, set_seed
+
+        torch.set_num_threads(1)
+        group = TorchDistGroup()
+        assert (group.rank, group.nranks) == (rank, world)
+        cfg = O.LayerConfig(d_model=64, nhead=8, dim_feedforward=256, dropout=0.1, num_partitions=world)
+        full = O.init_params(cfg, 1024, dtype=torch.float64)
+        g = torch.Generator().manual_seed(11)
+        x = torch.randn(2, 16, 64, generator=g, dtype=torch.float64)
+        dy = torch.randn(2, 16, 64, generator=g, dtype=torch.float64)
+        masks = O.make_masks(cfg, 2, 16, 1024)
+        # the tracker on this rank must hand out exactly the seeds the oracle used for its masks
+        set_seed(1024, mp_rank=rank)
+        st = get_rng_state_tracker().get_states_tracker()
+        assert st["local_seed"][0] == O.rng_seeds(1024, rank)["local_seed"] and st["global_seed"][0] == 1024
+
+        shard = {}
+        for k, v in full.items():
+            if k in ("self_attn.qkv_proj.weight", "self_attn.qkv_proj.bias", "linear1.weight", "linear1.bias"):
+                shard[k] = shard_columns(v, rank, world)
+            elif k in ("self_attn.out_proj.weight", "linear2.weight"):
+                shard[k] = shard_rows(v, rank, world)
+        shard = {k: v.clone().requires_grad_(True) for k, v in shard.items()}
+        rep = {k: v.clone().requires_grad_(True) for k, v in full.items() if k not in shard}
+        xr = x.clone().requires_grad_(True)
+        y = _rank_forward(xr, shard, rep, cfg, group, masks, rank)
+        y.backward(dy)
+
+        y_ref, dx_ref, g_ref = O.decoder_layer_fwd_bwd(x, dy, full, cfg, masks)
+        ok = torch.allclose(y, y_ref, atol=1e-11) and torch.allclose(xr.grad, dx_ref, atol=1e-11)
+        ref_shard = O.shard_params(g_ref, cfg, rank)
+        for k, v in shard.items():
+            ok = ok and torch.allclose(v.grad, ref_shard[k], atol=1e-10)
+        for k, v in rep.items():  # replicated parameters see the full gradient on every rank
+            ok = ok and torch.allclose(v.grad, g_ref[k], atol=1e-10)
+        # plain collective plumbing
+        t = torch.full((4,), float(rank + 1), dtype=torch.float64)
+        group.all_reduce_(t)
+        ok = ok and bool((t == sum(range(1, world + 1))).all())
+        ret[rank] = bool(ok)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_tp_ranks_over_gloo_match_single_process_oracle(world):
+    ctx = mp.get_context("spawn")
+    ret = ctx.Manager().dict()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, ret)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=240)
+    for p in procs:
+        if p.is_alive():
+            p.kill()
+            pytest.fail("gloo worker hung")
+    assert all(ret.get(r) for r in range(world)), dict(ret)

@@ -1,0 +1,82 @@
+"""Host-side logic that needs no GPU: RNG tracker, sharding helpers, layer construction / API."""
+import pytest
+import torch
+
+from fleetx_b200 import dist as D
+from fleetx_b200.rng import RNGStatesTracker, get_rng_state_tracker, set_seed
+from oracle import decoder_layer as O
+
+
+def test_tracker_streams_and_errors():
+    t = RNGStatesTracker()
+    t.add("global_seed", 1024)
+    t.add("local_seed", 1147)
+    with pytest.raises(ValueError):
+        t.add("global_seed", 5)       # duplicate name
+    with pytest.raises(ValueError):
+        t.add("other", 1024)          # duplicate seed
+    with pytest.raises(ValueError):
+        with t.rng_state("missing"):
+            pass
+    with t.rng_state("global_seed"):
+        assert t.draw() == (1024, 0)
+        assert t.draw() == (1024, 1)
+    assert t.draw("local_seed") == (1147, 0)
+    state = t.get_states_tracker()
+    a = t.draw("global_seed")
+    t.set_states_tracker(state)       # recompute: restoring the state replays the same draws
+    assert t.draw("global_seed") == a
+
+
+def test_set_seed_matches_env_py_and_oracle():
+    for mp_rank in (0, 3):
+        set_seed(1024, mp_rank=mp_rank, pp_rank=1, data_world_rank=2)
+        st = get_rng_state_tracker().get_states_tracker()
+        want = O.rng_seeds(1024, mp_rank, 1, 2)
+        assert st["global_seed"][0] == want["global_seed"] and st["local_seed"][0] == want["local_seed"]
+
+
+def test_sharding_helpers_match_oracle_shards():
+    cfg = O.LayerConfig(d_model=64, nhead=8, dim_feedforward=256, num_partitions=4)
+    full = O.init_params(cfg)
+    for r in range(4):
+        ref = O.shard_params(full, cfg, r)
+        assert torch.equal(D.shard_columns(full["self_attn.qkv_proj.weight"], r, 4), ref["self_attn.qkv_proj.weight"])
+        assert torch.equal(D.shard_columns(full["linear1.bias"], r, 4), ref["linear1.bias"])
+        assert torch.equal(D.shard_rows(full["linear2.weight"], r, 4), ref["linear2.weight"])
+    with pytest.raises(ValueError):
+        D.shard_columns(torch.zeros(4, 6), 0, 4)
+
+
+def test_layer_api_surface_on_cpu():
+    from fleetx_b200.layers import ColumnParallelLinear, MultiHeadAttention, RowParallelLinear, TransformerDecoderLayer
+
+    layer = TransformerDecoderLayer(128, 2, 512, dropout=0.1, device="cpu")
+    names = sorted(n for n, _ in layer.named_parameters())
+    assert names == sorted(O.PARAM_NAMES)                      # checkpoint-compatible names
+    shapes = {n: tuple(p.shape) for n, p in layer.named_parameters()}
+    assert shapes["self_attn.qkv_proj.weight"] == (128, 384)   # Paddle [in, out] layout
+    assert shapes["linear2.weight"] == (512, 128)
+    assert layer.norm1.weight.dtype == torch.float32 and layer.linear1.weight.dtype == torch.bfloat16
+    assert layer._config["d_model"] == 128 and layer.self_attn.num_heads == 2 and layer.self_attn.head_dim == 64
+    with pytest.raises(ValueError):
+        TransformerDecoderLayer(128, 2, 512, num_partitions=2, device="cpu")   # group size is 1
+    with pytest.raises(NotImplementedError):
+        TransformerDecoderLayer(128, 2, 512, sequence_parallel=True, device="cpu")
+    with pytest.raises(AssertionError):
+        MultiHeadAttention(100, 3, device="cpu")
+    assert ColumnParallelLinear(16, 32, has_bias=True, gather_output=False, device="cpu").bias.shape == (32,)
+    assert RowParallelLinear(32, 16, input_is_parallel=True, device="cpu").weight.shape == (32, 16)
+    # load_full_state keeps this rank's shard
+    cfg = O.LayerConfig(d_model=128, nhead=2, dim_feedforward=512)
+    full = O.init_params(cfg)
+    layer.load_full_state(full)
+    assert torch.equal(layer.linear1.weight.float(), full["linear1.weight"].to(torch.bfloat16).float())
+
+
+def test_bench_flop_model_matches_survey():
+    import bench
+
+    # 327.2 MFLOP/token for 1.3B/s2048, 81.8 for 345M/s1024
+    assert abs(bench.layer_flops(1, 2048, 2048) / 1e6 - 327.2) < 0.1
+    assert abs(bench.layer_flops(1, 1024, 1024) / 1e6 - 81.8) < 0.1

@@ -1,0 +1,163 @@
+"""CPU tests of the oracle itself (no GPU): the restated ops against independent statements of
+the same definitions, hand-checkable values, the committed golden fixtures, TP equivalence and
+causality (the known-answer set SURVEY §8c asks for, since the reference has no tests)."""
+import math
+import os
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from oracle import decoder_layer as O
+from oracle import philox as OP
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+# ------------------------------------------------------------------------------------ Philox
+def test_philox_matches_random123_known_answers():
+    """Random123's published kat_vectors for philox4x32-10 (counter, key -> output)."""
+    kat = [
+        ((0, 0, 0, 0), (0, 0), "6627e8d5 e169c58d bc57ac4c 9b00dbd8"),
+        ((0xFFFFFFFF,) * 4, (0xFFFFFFFF, 0xFFFFFFFF), "408f276d 41c83b0e a20bc7c6 6d5451fd"),
+        ((0x243F6A88, 0x85A308D3, 0x13198A2E, 0x03707344), (0xA4093822, 0x299F31D0),
+         "d16cfe09 94fdcceb 5001e420 24126ea1"),
+    ]
+    for ctr, key, want in kat:
+        seed = key[0] | (key[1] << 32)
+        group = ctr[0] | (ctr[1] << 32)
+        offset = ctr[2] | (ctr[3] << 32)
+        w = OP.philox4x32_10(seed, offset, np.array([group], dtype=np.uint64))[0]
+        assert " ".join("%08x" % v for v in w) == want
+
+
+def test_philox_masks_match_committed_fixture_and_statistics():
+    fx = np.load(os.path.join(GOLD, "philox_masks.npz"))
+    assert np.array_equal(OP.philox4x32_10(1024, 3, np.arange(16, dtype=np.uint64)), fx["words"])
+    assert np.array_equal(OP.dropout_mask(1024, 0, 4 * 64, 0.1), fx["hidden"])
+    assert np.array_equal(OP.attn_dropout_mask(1147, 2, 1, 2, 24, 0.25), fx["attn"])
+    n, p = 1 << 20, 0.1
+    m = OP.dropout_mask(7, 0, n, p)
+    assert abs(m.mean() - (1 - p)) < 4 * math.sqrt(p * (1 - p) / n) + 1 / 65536
+    assert OP.dropout_mask(7, 0, 1000, 0.0).all()
+    # different offsets / seeds give independent masks
+    m2 = OP.dropout_mask(7, 1, n, p)
+    assert abs((m == m2).mean() - (p * p + (1 - p) ** 2)) < 0.01
+    # ragged length is a prefix of the padded stream
+    assert np.array_equal(OP.dropout_mask(7, 0, 13, 0.5), OP.dropout_mask(7, 0, 16, 0.5)[:13])
+
+
+def test_rng_seeds_follow_env_py():
+    # ppfleetx/utils/env.py:42-43
+    assert O.rng_seeds(1024) == {"global_seed": 1024, "local_seed": 1147}
+    assert O.rng_seeds(1024, mp_rank=3, pp_rank=2, data_world_rank=5) == {"global_seed": 1029, "local_seed": 1024 + 123 + 30 + 2000}
+
+
+# ------------------------------------------------------------------------------------ ops
+def test_ops_against_independent_statements():
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(3, 5, 32, generator=g, dtype=torch.float64)
+    gamma, beta = torch.randn(32, generator=g, dtype=torch.float64), torch.randn(32, generator=g, dtype=torch.float64)
+    assert torch.allclose(O.layer_norm(x, gamma, beta), F.layer_norm(x, (32,), gamma, beta, 1e-5), atol=1e-12)
+    assert torch.allclose(O.gelu_tanh(x), F.gelu(x, approximate="tanh"), atol=1e-12)
+    # hand-checkable GELU-tanh values
+    for z, want in ((0.0, 0.0), (1.0, 0.8411919906082768), (-1.0, -0.15880800939172324)):
+        assert abs(O.gelu_tanh(torch.tensor(z, dtype=torch.float64)).item() - want) < 1e-12
+    for z in (3.0, -2.5, 0.3):  # the defining formula, evaluated with the math module
+        want = 0.5 * z * (1.0 + math.tanh(math.sqrt(2.0 / math.pi) * (z + 0.044715 * z ** 3)))
+        assert abs(O.gelu_tanh(torch.tensor(z, dtype=torch.float64)).item() - want) < 1e-12
+    # dropout: upscale_in_train
+    keep = torch.tensor([1, 0, 1, 1], dtype=torch.uint8)
+    assert torch.equal(O.dropout(torch.tensor([1.0, 2.0, 3.0, 4.0]), 0.5, keep), torch.tensor([2.0, 0.0, 6.0, 8.0]))
+    # attention against torch's fused SDPA (causal)
+    b, nh, s, hd = 2, 3, 17, 8
+    mix = torch.randn(b, s, nh * 3 * hd, generator=g, dtype=torch.float64)
+    q, k, v = O.fuse_prepare_qkv(mix, nh, hd)
+    ref = F.scaled_dot_product_attention(q, k, v, is_causal=True).permute(0, 2, 1, 3).reshape(b, s, nh * hd)
+    assert torch.allclose(O.core_attn(q, k, v, hd), ref, atol=1e-12)
+    # explicit additive mask branch (:273-275) == fused causal branch (:277)
+    mask = torch.triu(torch.ones(s, s, dtype=torch.float64), 1) * -1e4
+    assert torch.allclose(O.core_attn(q, k, v, hd, attn_mask=mask), ref, atol=1e-9)
+
+
+def test_qkv_layout_is_per_head_q_k_v():
+    # hybrid_model.py:167-173: column c of the packed projection = head c//(3hd), slot (c%(3hd))//hd
+    b, s, nh, hd = 1, 2, 3, 4
+    mix = torch.arange(b * s * nh * 3 * hd, dtype=torch.float64).reshape(b, s, nh * 3 * hd)
+    q, k, v = O.fuse_prepare_qkv(mix, nh, hd)
+    assert q.shape == (b, nh, s, hd)
+    assert q[0, 1, 0].tolist() == [12, 13, 14, 15] and k[0, 1, 0].tolist() == [16, 17, 18, 19] and v[0, 1, 0].tolist() == [20, 21, 22, 23]
+
+
+def test_parameter_shapes_per_rank():
+    cfg = O.LayerConfig(d_model=64, nhead=8, dim_feedforward=256, num_partitions=4)
+    sh = {k: tuple(v.shape) for k, v in O.shard_params(O.init_params(cfg), cfg, 2).items()}
+    assert sh["self_attn.qkv_proj.weight"] == (64, 48) and sh["self_attn.qkv_proj.bias"] == (48,)
+    assert sh["self_attn.out_proj.weight"] == (16, 64) and sh["self_attn.out_proj.bias"] == (64,)
+    assert sh["linear1.weight"] == (64, 64) and sh["linear2.weight"] == (64, 64) and sh["linear2.bias"] == (64,)
+    assert sh["norm1.weight"] == (64,)
+    with pytest.raises(AssertionError):
+        O.LayerConfig(d_model=64, nhead=6, dim_feedforward=256, num_partitions=4)  # nhead % n != 0 (:117-118)
+
+
+# ------------------------------------------------------------------------------------ layer
+def _case(h=32, nh=4, f=128, b=2, s=12, n=1, dropout=0.0, pre=True, seed=3):
+    cfg = O.LayerConfig(d_model=h, nhead=nh, dim_feedforward=f, dropout=dropout, normalize_before=pre, num_partitions=n)
+    params = O.init_params(cfg, seed, dtype=torch.float64)
+    g = torch.Generator().manual_seed(seed)
+    for k in params:
+        if k.endswith("bias"):
+            params[k] = 0.05 * torch.randn(params[k].shape, generator=g, dtype=torch.float64)
+    x = torch.randn(b, s, h, generator=g, dtype=torch.float64)
+    dy = torch.randn(b, s, h, generator=g, dtype=torch.float64)
+    return cfg, params, x, dy
+
+
+@pytest.mark.parametrize("pre", [True, False])
+@pytest.mark.parametrize("n", [2, 4, 8])
+def test_tp_equivalence(n, pre):
+    """n = 1 result == summed n-shard simulation (hidden dropout shared, attention dropout off)."""
+    cfg1, params, x, dy = _case(h=64, nh=8, f=256, pre=pre)
+    y1, dx1, g1 = O.decoder_layer_fwd_bwd(x, dy, params, cfg1)
+    cfgn = O.LayerConfig(d_model=64, nhead=8, dim_feedforward=256, dropout=0.0, normalize_before=pre, num_partitions=n)
+    yn, dxn, gn = O.decoder_layer_fwd_bwd(x, dy, params, cfgn)
+    assert torch.allclose(y1, yn, atol=1e-12) and torch.allclose(dx1, dxn, atol=1e-12)
+    for k in g1:
+        assert torch.allclose(g1[k], gn[k], atol=1e-11), k
+
+
+def test_causality_and_eval_mode():
+    cfg, params, x, _ = _case()
+    y = O.decoder_layer_forward(x, params, cfg, training=False)
+    x2 = x.clone()
+    x2[:, 7:] += 1.0
+    y2 = O.decoder_layer_forward(x2, params, cfg, training=False)
+    assert torch.allclose(y[:, :7], y2[:, :7], atol=1e-13) and not torch.allclose(y[:, 7:], y2[:, 7:])
+    # eval ignores dropout masks
+    cfgd = O.LayerConfig(d_model=32, nhead=4, dim_feedforward=128, dropout=0.5)
+    masks = O.make_masks(cfgd, 2, 12, 1024)
+    assert torch.allclose(O.decoder_layer_forward(x, params, cfgd, masks, training=False), y, atol=1e-13)
+    assert not torch.allclose(O.decoder_layer_forward(x, params, cfgd, masks, training=True), y)
+
+
+def test_dropout_streams_global_shared_local_distinct():
+    cfg = O.LayerConfig(d_model=32, nhead=4, dim_feedforward=128, dropout=0.2, num_partitions=2)
+    m = O.make_masks(cfg, 2, 16, 1024)
+    assert len(m.attn) == 2 and not torch.equal(m.attn[0], m.attn[1])  # 'local_seed' differs per mp rank
+    assert not torch.equal(m.hidden1, m.hidden2)  # same stream, successive offsets
+
+
+@pytest.mark.parametrize("name", ["oracle_tiny_fp64_n1", "oracle_tiny_fp64_n2_dropout", "layer_gpu_small_fp32",
+                                  "layer_gpu_small_fp32_dropout"])
+def test_oracle_reproduces_golden_fixture(name):
+    fx = np.load(os.path.join(GOLD, name + ".npz"))
+    b, s, h, nh, f, n, p1000, seed = [int(v) for v in fx["cfg"]]
+    cfg = O.LayerConfig(d_model=h, nhead=nh, dim_feedforward=f, dropout=p1000 / 1000.0, num_partitions=n)
+    params = {k[6:]: torch.from_numpy(fx[k]) for k in fx.files if k.startswith("param.")}
+    masks = O.make_masks(cfg, b, s, seed) if p1000 else None
+    y, dx, grads = O.decoder_layer_fwd_bwd(torch.from_numpy(fx["x"]), torch.from_numpy(fx["dy"]), params, cfg, masks)
+    tol = 1e-12 if fx["x"].dtype == np.float64 else 2e-5
+    assert np.allclose(y.numpy(), fx["y"], atol=tol) and np.allclose(dx.numpy(), fx["dx"], atol=tol)
+    for k, v in grads.items():
+        assert np.allclose(v.numpy(), fx["grad." + k], atol=tol * 10, rtol=1e-4), k
