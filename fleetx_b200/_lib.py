@@ -28,6 +28,7 @@ SIGNATURES = {
     "fx_layernorm_fwd": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _f]),
     "fx_layernorm_bwd_workspace_bytes": (_sz, [_i, _i]),
     "fx_layernorm_bwd": (_i, [_vp] * 11 + [_i, _i]),
+    "fx_layernorm_bwd_noalloc": (_i, [_vp] * 10 + [_i, _i]),
     "fx_bias_dropout_residual_fwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _f, _u64, _u64, _vp, _vp]),
     "fx_bias_dropout_residual_bwd": (_i, [_vp, _vp, _vp, _i, _i, _f, _u64, _u64, _vp]),
     "fx_colsum_workspace_bytes": (_sz, [_i, _i]),

@@ -3,6 +3,8 @@
 // row, the row lives in registers (16-byte loads), statistics by warp shuffle + a 4-entry
 // shared-memory exchange. Algorithmic bytes per token (bf16): forward 4h (+8 stats),
 // backward 6h (8h with the fused skip-path gradient).
+#include <mutex>
+
 #include "common.cuh"
 #include "tc5.cuh"
 
@@ -308,6 +310,87 @@ extern "C" int fx_layernorm_bwd(void* stream, const void* dy, const void* x, con
   auto DX = static_cast<__nv_bfloat16*>(dx);
   float* part = static_cast<float*>(workspace);
   using namespace fx::ln;
+  FX_LN_DISPATCH(ln_bwd_kernel, DY, X, gamma, mean, rstd, DR, DX, part, rows, h);
+  FX_LAUNCH_CHECK();
+  ln::ln_bwd_finish_kernel<<<ceil_div(2 * h, 32), dim3(32, 8), 0, st>>>(part, dgamma, dbeta, grid, h);
+  FX_LAUNCH_CHECK();
+  return FX_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// LayerNorm backward for callers that may not allocate device memory.
+//
+// Who needs this: hosts that own all GPU memory up front and forbid allocation afterwards — a
+// serving or training runtime whose executor planned every buffer before the step started, a
+// Paddle/static-graph custom op that is handed exactly its declared inputs and outputs and no
+// allocator, code that runs where cudaMalloc would stall the whole device (it synchronises) or
+// is simply not permitted, e.g. inside a latency-critical loop. fx_layernorm_bwd needs a partial-
+// sum workspace from such a caller; this variant brings its own instead: a fixed array in the
+// library's device image. Every GPU that loads the library carries it until the process exits.
+//
+// Limits: h <= FX_LN_NOALLOC_MAX_H (4096); any number of rows. The array is 148 x 2 x 4096 fp32
+// = 4,849,664 bytes. The backward kernel runs on at most 148 CTAs here (the normal entry point
+// uses up to 592), so it is somewhat slower; results are the same up to fp32 summation order.
+namespace fx {
+namespace ln {
+
+constexpr int NOALLOC_PARTS = 148;
+constexpr int NOALLOC_MAX_H = 4096;
+
+// File-scope device array. In HOST code this name is only a handle for the runtime, not a device
+// address: it must go through cudaGetSymbolAddress before a kernel can be given it.
+static __device__ __align__(256) float g_ln_bwd_noalloc_scratch[NOALLOC_PARTS * 2 * NOALLOC_MAX_H];
+
+static std::mutex g_noalloc_mu;
+static float* g_noalloc_ptr[64] = {nullptr};  // per device, resolved once with that device current
+
+// Returns the device address of the scratch array on the CURRENT device (nullptr + error text on failure).
+static float* noalloc_scratch() {
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
+    set_error("fx_layernorm_bwd_noalloc: cannot identify the current CUDA device");
+    return nullptr;
+  }
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (g_noalloc_ptr[dev] == nullptr) {
+    float* ptr = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_ln_bwd_noalloc_scratch);
+    if (e != cudaSuccess || ptr == nullptr) {
+      set_error("fx_layernorm_bwd_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev,
+                cudaGetErrorString(e));
+      return nullptr;
+    }
+    g_noalloc_ptr[dev] = ptr;
+  }
+  return g_noalloc_ptr[dev];
+}
+
+}  // namespace ln
+}  // namespace fx
+
+extern "C" int fx_layernorm_bwd_noalloc(void* stream, const void* dy, const void* x, const float* gamma,
+                                        const float* mean, const float* rstd, const void* dresidual,
+                                        void* dx, float* dgamma, float* dbeta, int rows, int h) {
+  using namespace fx;
+  FX_CHECK_ARG(rows > 0 && h > 0, "fx_layernorm_bwd_noalloc: empty input (rows %d, h %d)", rows, h);
+  FX_CHECK_ARG(h % 8 == 0, "fx_layernorm_bwd_noalloc: h must be a multiple of 8 (got %d)", h);
+  FX_CHECK_ARG(h <= ln::NOALLOC_MAX_H,
+               "fx_layernorm_bwd_noalloc: h = %d exceeds the built-in scratch (max h %d); use fx_layernorm_bwd "
+               "with a caller-provided workspace", h, ln::NOALLOC_MAX_H);
+  FX_CHECK_ARG(dy && x && gamma && mean && rstd && dx && dgamma && dbeta, "fx_layernorm_bwd_noalloc: null pointer");
+  FX_CHECK_ARG(((uintptr_t)dy | (uintptr_t)x | (uintptr_t)dx | (uintptr_t)dresidual | (uintptr_t)gamma) % 16 == 0,
+               "fx_layernorm_bwd_noalloc: pointers must be 16-byte aligned");
+  float* part = ln::noalloc_scratch();  // first call on a device resolves the address (no allocation)
+  if (part == nullptr) return FX_ERR_CUDA;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int grid = rows < ln::NOALLOC_PARTS ? rows : ln::NOALLOC_PARTS;
+  auto DY = static_cast<const __nv_bfloat16*>(dy);
+  auto X = static_cast<const __nv_bfloat16*>(x);
+  auto DR = static_cast<const __nv_bfloat16*>(dresidual);
+  auto DX = static_cast<__nv_bfloat16*>(dx);
+  using namespace fx::ln;
+  // Nothing in the scratch has to start at zero: the first kernel overwrites partial[0..grid) x 2h in
+  // full and the second reads exactly that range, so whatever an earlier call left behind is never seen.
   FX_LN_DISPATCH(ln_bwd_kernel, DY, X, gamma, mean, rstd, DR, DX, part, rows, h);
   FX_LAUNCH_CHECK();
   ln::ln_bwd_finish_kernel<<<ceil_div(2 * h, 32), dim3(32, 8), 0, st>>>(part, dgamma, dbeta, grid, h);

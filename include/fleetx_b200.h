@@ -64,6 +64,24 @@ int fx_layernorm_bwd(void* stream, const void* dy, const void* x, const float* g
                      const float* mean, const float* rstd, const void* dresidual, void* dx,
                      float* dgamma, float* dbeta, void* workspace, int rows, int h);
 
+/* No counterpart in the reference. LayerNorm backward for callers that cannot allocate device
+ * memory: a runtime that planned every buffer before the step and forbids cudaMalloc afterwards
+ * (it synchronises the device), a static-graph custom op that receives only its declared inputs
+ * and outputs, a latency-critical loop. Same arguments and results as fx_layernorm_bwd (up to fp32
+ * summation order of dgamma/dbeta) minus the workspace: the partial sums live in a fixed array
+ * inside the library's device image (148 x 2 x 4096 fp32 = 4,849,664 bytes, held by every GPU that
+ * loads the library until the process exits). It never calls cudaMalloc/cudaFree or any allocating
+ * routine.
+ *  - h must be <= 4096 (a multiple of 8); larger h is rejected with FX_ERR_INVALID_ARGUMENT.
+ *  - The first call on each device looks up the array's device address (with that device current);
+ *    make that first call before starting any stream capture.
+ *  - All calls on a device share the one array. Nothing in it needs clearing between calls, but
+ *    two calls whose kernels overlap on the GPU (different streams, no dependency) race on it:
+ *    keep calls on one stream or order them with events. */
+int fx_layernorm_bwd_noalloc(void* stream, const void* dy, const void* x, const float* gamma,
+                             const float* mean, const float* rstd, const void* dresidual, void* dx,
+                             float* dgamma, float* dbeta, int rows, int h);
+
 /* ---- bias + dropout + residual: hybrid_model.py:546-547 (dropout1) and :556-561 (dropout2) ---- */
 /* out = residual + dropout(y + bias, p, upscale_in_train). bias may be null. The keep mask is a
  * pure function of (seed, offset, element index) (Philox4x32-10) so backward and recompute
