@@ -1,0 +1,70 @@
+"""Tensor-parallel layer on 2 GPUs (NCCL) against the oracle's n=2 simulation. Needs 2 devices;
+skipped on a single-GPU box (the CPU/gloo version of the same logic is tests/test_dist_gloo.py)."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from oracle import decoder_layer as O
+
+pytestmark = pytest.mark.gpu
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, ret):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        from fleetx_b200.dist import TorchDistGroup
+        from fleetx_b200.rng import set_seed
+        from fleetx_b200.selfcheck import layer_from_oracle_params, rel_err
+
+        b, s = 2, 256
+        cfg = O.LayerConfig(d_model=512, nhead=8, dim_feedforward=2048, dropout=0.1, num_partitions=world)
+        params = {k: v.to(torch.bfloat16).float() for k, v in O.init_params(cfg, 1024).items()}
+        g = torch.Generator().manual_seed(3)
+        x = torch.randn(b, s, cfg.d_model, generator=g).to(torch.bfloat16)
+        dy = torch.randn(b, s, cfg.d_model, generator=g).to(torch.bfloat16)
+        set_seed(1024, mp_rank=rank)
+        layer = layer_from_oracle_params(cfg, params, group=TorchDistGroup(), device=f"cuda:{rank}")
+        layer.train()
+        xd = x.cuda().requires_grad_(True)
+        y = layer(xd)
+        y.backward(dy.cuda())
+        torch.cuda.synchronize()
+        masks = O.make_masks(cfg, b, s, 1024)
+        y_ref, dx_ref, g_ref = O.decoder_layer_fwd_bwd(x.float(), dy.float(), params, cfg, masks)
+        g_shard = O.shard_params(g_ref, cfg, rank)
+        errs = {"y": rel_err(y, y_ref), "dx": rel_err(xd.grad, dx_ref)}
+        for n, p in layer.named_parameters():
+            errs[n] = rel_err(p.grad, g_shard[n])
+        ret[rank] = max(errs.values())
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_tp2_layer_matches_oracle():
+    ctx = mp.get_context("spawn")
+    ret = ctx.Manager().dict()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, ret)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=300)
+    for p in procs:
+        if p.is_alive():
+            p.kill()
+            pytest.fail("TP worker hung")
+    assert len(ret) == 2 and all(v < 2e-2 for v in ret.values()), dict(ret)
