@@ -47,9 +47,10 @@ struct FwdParams {
   __nv_bfloat16* out;
   float* lse;
   int b, s, nh;
-  float scale, p_drop, inv_keep;
-  uint32_t thresh;
-  uint64_t seed, offset;
+  float scale, p_drop, inv_keep, log2_inv_keep;
+  uint32_t thresh2;         // threshold in both 16-bit lanes
+  uint32_t off_lo, off_hi;  // dropout call offset (Philox counter words 2, 3)
+  PhiloxKeys keys;          // round keys of the dropout seed
 };
 
 template <int HD>
@@ -234,9 +235,14 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FwdParams p) 
       if (lane == 0) mbar_arrive(&pv_empty[buf]);
     };
 
+    // Dropout's 1/(1-p) is folded into the exponent (p' = 2^(s·sl2 - m·sl2 + log2 inv_keep)), so the
+    // row sum below runs over p' too and is scaled back once at the end.
+    const float log2_inv_keep = p.log2_inv_keep;
+    const uint32_t thresh2 = p.thresh2;
+
     for (int j = 0; j < n_kv; ++j) {
       const int sb = j % C::NS;
-      const bool diag = (j == qt);
+      const bool diag = (j == qt);  // only the diagonal tile needs the causal predicate
       mbar_wait(&s_full[sb], (j / C::NS) & 1, 31);
       tc_fence_after();
       // sweep 1: row maximum of the raw scores
@@ -246,48 +252,52 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FwdParams p) 
         uint32_t r[32];
         tmem_ld_32x32(lane_base + sb * 128 + c * 32, r);
         tmem_ld_wait();
+        if (diag) {
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          const float v = __uint_as_float(r[i]);
-          const bool masked = diag && (c * 32 + i > row_local);
-          mx = fmaxf(mx, masked ? -INFINITY : v);
+          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, (c * 32 + i > row_local) ? -INFINITY : __uint_as_float(r[i]));
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; i += 2) mx = fmaxf(mx, fmaxf(__uint_as_float(r[i]), __uint_as_float(r[i + 1])));
         }
       }
       const float m_new = fmaxf(m, mx);
-      const float alpha = exp2f((m - m_new) * sl2);
-      const float m_sc = m_new * sl2;
+      const float alpha = ex2_approx((m - m_new) * sl2);
+      const float neg_m = log2_inv_keep - m_new * sl2;
       // P buffer must have been consumed by PV_{j-1}
       mbar_wait(p_empty, (j & 1) ^ 1, 32);
-      // sweep 2: probabilities -> bf16 P tile (dropout folded in), row sum of the undropped p
+      // sweep 2: probabilities -> bf16 P tile (dropout folded in), row sum of the undropped p'
       float rowsum = 0.f;
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
         uint32_t r[32];
         tmem_ld_32x32(lane_base + sb * 128 + c * 32, r);
         tmem_ld_wait();
-        float pr[32];
+        uint32_t pk[16];
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          const bool masked = diag && (c * 32 + i > row_local);
-          const float e = exp2f(__uint_as_float(r[i]) * sl2 - m_sc);
-          pr[i] = masked ? 0.f : e;
-          rowsum += pr[i];
+        for (int i = 0; i < 32; i += 2) {
+          float e0 = ex2_approx(fmaf(__uint_as_float(r[i]), sl2, neg_m));
+          float e1 = ex2_approx(fmaf(__uint_as_float(r[i + 1]), sl2, neg_m));
+          if (diag) {
+            e0 = (c * 32 + i > row_local) ? 0.f : e0;
+            e1 = (c * 32 + i + 1 > row_local) ? 0.f : e1;
+          }
+          rowsum += e0 + e1;
+          pk[i >> 1] = pack_bf16(e0, e1);
         }
         if (drop) {
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
-            const Philox8 rnd = philox4x32_10(p.seed, p.offset, grp_row + static_cast<uint64_t>(j * 16 + c * 4 + g));
+            const Philox8 rnd = philox4x32_10_rk(p.keys, p.off_lo, p.off_hi, grp_row + static_cast<uint64_t>(j * 16 + c * 4 + g));
 #pragma unroll
-            for (int e = 0; e < 8; ++e)
-              pr[g * 8 + e] = philox_keep(rnd, e, p.thresh) ? pr[g * 8 + e] * p.inv_keep : 0.f;
+            for (int w = 0; w < 4; ++w)  // flags at bits 15 / 31 -> 0xFFFF lane masks for the bf16 pair
+              pk[g * 4 + w] &= prmt(keep_flags2(rnd.lanes[w], thresh2), 0u, 0xBB99u);
           }
         }
         // columns [c*32, c*32+32) live in sub-tile c/2, 16-byte chunks (c&1)*4 .. +3
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
           const uint32_t addr = p_addr + (c >> 1) * C::SUB_BYTES + sw128_off(row_local, (c & 1) * 4 + g);
-          st_shared_v4(addr, pack_bf16(pr[g * 8 + 0], pr[g * 8 + 1]), pack_bf16(pr[g * 8 + 2], pr[g * 8 + 3]),
-                       pack_bf16(pr[g * 8 + 4], pr[g * 8 + 5]), pack_bf16(pr[g * 8 + 6], pr[g * 8 + 7]));
+          st_shared_v4(addr, pk[g * 4 + 0], pk[g * 4 + 1], pk[g * 4 + 2], pk[g * 4 + 3]);
         }
       }
       tc_fence_before();
@@ -305,7 +315,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FwdParams p) 
     o_update(n_kv - 1, alpha_prev);
 
     if (row < p.s) {
-      const float inv_l = 1.0f / l;
+      const float inv_l = p.inv_keep / l;  // l sums p' = p * inv_keep
       uint4* op = reinterpret_cast<uint4*>(p.out + (static_cast<size_t>(batch) * p.s + row) * (p.nh * HD) + head * HD);
 #pragma unroll
       for (int g = 0; g < HD / 8; ++g)
@@ -313,7 +323,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FwdParams p) 
                            pack_bf16(o[g * 8 + 2] * inv_l, o[g * 8 + 3] * inv_l),
                            pack_bf16(o[g * 8 + 4] * inv_l, o[g * 8 + 5] * inv_l),
                            pack_bf16(o[g * 8 + 6] * inv_l, o[g * 8 + 7] * inv_l));
-      p.lse[(static_cast<size_t>(batch) * p.nh + head) * p.s + row] = m * p.scale + __logf(l);
+      p.lse[(static_cast<size_t>(batch) * p.nh + head) * p.s + row] = m * p.scale + __logf(l) - __logf(p.inv_keep);
     }
   }
 
@@ -352,32 +362,45 @@ static int launch_fwd(cudaStream_t st, const CUtensorMap& map, const FwdParams& 
 constexpr int BWD_THREADS = 320;  // warp 0 TMA, warp 1 MMA, warps 2..9 elementwise (2 per TMEM lane quarter)
 
 struct BwdParams {
-  const float* lse;     // [b, nh, s]
-  const float* delta;   // [b, nh, s] rowsum(dO * O)
+  const float* lse2;    // [b, nh, s_pad]  lse·log2(e) − log2(inv_keep); +inf in the padding
+  const float* delta;   // [b, nh, s_pad]  rowsum(dO ∘ O) / inv_keep;     0 in the padding
   __nv_bfloat16* dqkv;  // [b, s, nh, 3, hd]
-  int b, s, nh;
+  int b, s, nh, s_pad;  // s_pad = s rounded up to 128
   float scale, p_drop, inv_keep;
-  uint32_t thresh;
-  uint64_t seed, offset;
+  uint32_t thresh2;
+  uint32_t off_lo, off_hi;
+  PhiloxKeys keys;
 };
 
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
-// delta[b, h, row] = sum_d dO[b, row, h, d] * O[b, row, h, d]
+// Row statistics the two backward kernels read per query row, padded so tiles never need a bound
+// check: with dropout folded in as p' = p·inv_keep,
+//   dS = p'·(keep·dP − delta'),  p' = 2^(s·scale·log2e − lse2),
+//   lse2 = lse·log2e − log2(inv_keep),  delta' = rowsum(dO ∘ O) / inv_keep.
+// Padding rows get lse2 = +inf (p' = 0) and delta' = 0.
 __global__ void __launch_bounds__(256)
 attn_delta_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16* __restrict__ out,
-                  float* __restrict__ delta, int b, int s, int nh, int hd) {
-  const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;  // over [b, s, nh]
-  const size_t total = (size_t)b * s * nh;
+                  const float* __restrict__ lse, float* __restrict__ lse2, float* __restrict__ delta, int b, int s,
+                  int nh, int hd, int s_pad, float log2_inv_keep, float keep) {
+  const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;  // over [b, s_pad, nh]
+  const size_t total = (size_t)b * s_pad * nh;
   if (idx >= total) return;
   const int head = (int)(idx % nh);
-  const size_t br = idx / nh;  // b * s + row
-  const int row = (int)(br % s);
-  const int batch = (int)(br / s);
-  const uint4* a = reinterpret_cast<const uint4*>(dout + idx * hd);
-  const uint4* o = reinterpret_cast<const uint4*>(out + idx * hd);
+  const size_t br = idx / nh;
+  const int row = (int)(br % s_pad);
+  const int batch = (int)(br / s_pad);
+  const size_t o_idx = ((size_t)batch * nh + head) * s_pad + row;
+  if (row >= s) {
+    lse2[o_idx] = INFINITY;
+    delta[o_idx] = 0.f;
+    return;
+  }
+  const size_t i_idx = (((size_t)batch * s + row) * nh + head) * hd;
+  const uint4* a = reinterpret_cast<const uint4*>(dout + i_idx);
+  const uint4* o = reinterpret_cast<const uint4*>(out + i_idx);
   float acc = 0.f;
   for (int v = 0; v < hd / 8; ++v) {
     const uint4 x = __ldg(a + v), y = __ldg(o + v);
@@ -385,7 +408,8 @@ attn_delta_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16* _
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc += bf16_lo(xs[j]) * bf16_lo(ys[j]) + bf16_hi(xs[j]) * bf16_hi(ys[j]);
   }
-  delta[((size_t)batch * nh + head) * s + row] = acc;
+  delta[o_idx] = acc * keep;
+  lse2[o_idx] = lse[((size_t)batch * nh + head) * s + row] * LOG2E - log2_inv_keep;
 }
 
 // ---------------------------------------------------------------------------- dQ kernel
@@ -539,14 +563,15 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tma_q,   // qkv, box rows
     const float sl2 = p.scale * LOG2E;
     const bool drop = p.p_drop > 0.f;
     const uint64_t s8 = static_cast<uint64_t>((p.s + 7) / 8);
-    const size_t stat_idx = (static_cast<size_t>(batch) * p.nh + head) * p.s + row;
-    const uint64_t grp_row = static_cast<uint64_t>(stat_idx) * s8;
-    const float lse_r = row < p.s ? p.lse[stat_idx] * LOG2E : 0.f;
-    const float delta_r = row < p.s ? p.delta[stat_idx] : 0.f;
+    const uint64_t grp_row = (static_cast<uint64_t>(batch * p.nh + head) * p.s + row) * s8;
+    const size_t stat_idx = (static_cast<size_t>(batch) * p.nh + head) * p.s_pad + row;  // row < s_pad always
+    const float neg_lse2 = -p.lse2[stat_idx];
+    const float delta_r = p.delta[stat_idx];
 
     for (int j = 0; j < n_kv; ++j) {
       const int buf = j & 1;
       const uint32_t ph = (j >> 1) & 1;
+      const bool diag = (j >= 2 * qt);  // the last two 64-wide KV tiles straddle the diagonal
       mbar_wait(&s_full[buf], ph, 45);
       tc_fence_after();
       uint32_t rs[32], rp[32];
@@ -557,28 +582,36 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tma_q,   // qkv, box rows
       __syncwarp();
       if (lane == 0) mbar_arrive(&s_empty[buf]);
       const int kv0 = j * 64 + half * 32;
-      float ds[32];
+      if (drop) {
+        // zero dP where the forward dropped P: AND the fp32 bits with an all-ones / all-zeros mask
 #pragma unroll
-      for (int g = 0; g < 4; ++g) {
-        Philox8 rnd;
-        if (drop) rnd = philox4x32_10(p.seed, p.offset, grp_row + static_cast<uint64_t>((kv0 >> 3) + g));
+        for (int g = 0; g < 4; ++g) {
+          const Philox8 rnd = philox4x32_10_rk(p.keys, p.off_lo, p.off_hi, grp_row + static_cast<uint64_t>((kv0 >> 3) + g));
 #pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          const int i = g * 8 + e;
-          const bool masked = (kv0 + i > row);
-          const float pr = masked ? 0.f : exp2f(__uint_as_float(rs[i]) * sl2 - lse_r);
-          float dp = __uint_as_float(rp[i]);
-          if (drop) dp = philox_keep(rnd, e, p.thresh) ? dp * p.inv_keep : 0.f;
-          ds[i] = pr * (dp - delta_r);
+          for (int w = 0; w < 4; ++w) {
+            const uint32_t f = keep_flags2(rnd.lanes[w], p.thresh2);
+            rp[g * 8 + 2 * w] &= prmt(f, 0u, 0x9999u);      // bit 15 replicated over the word
+            rp[g * 8 + 2 * w + 1] &= prmt(f, 0u, 0xBBBBu);  // bit 31
+          }
         }
+      }
+      uint32_t pk[16];
+#pragma unroll
+      for (int i = 0; i < 32; i += 2) {
+        float p0 = ex2_approx(fmaf(__uint_as_float(rs[i]), sl2, neg_lse2));
+        float p1 = ex2_approx(fmaf(__uint_as_float(rs[i + 1]), sl2, neg_lse2));
+        if (diag) {
+          p0 = (kv0 + i > row) ? 0.f : p0;
+          p1 = (kv0 + i + 1 > row) ? 0.f : p1;
+        }
+        pk[i >> 1] = pack_bf16(p0 * (__uint_as_float(rp[i]) - delta_r), p1 * (__uint_as_float(rp[i + 1]) - delta_r));
       }
       mbar_wait(&ds_empty[buf], ph ^ 1, 46);
       const uint32_t ds_addr = smem_u32(smem + C::OFF_DS + buf * C::DS_BYTES);
 #pragma unroll
       for (int g = 0; g < 4; ++g)
-        st_shared_v4(ds_addr + sw128_off(row_local, half * 4 + g), pack_bf16(ds[g * 8 + 0], ds[g * 8 + 1]),
-                     pack_bf16(ds[g * 8 + 2], ds[g * 8 + 3]), pack_bf16(ds[g * 8 + 4], ds[g * 8 + 5]),
-                     pack_bf16(ds[g * 8 + 6], ds[g * 8 + 7]));
+        st_shared_v4(ds_addr + sw128_off(row_local, half * 4 + g), pk[g * 4 + 0], pk[g * 4 + 1], pk[g * 4 + 2],
+                     pk[g * 4 + 3]);
       fence_async_smem();
       __syncwarp();
       if (lane == 0) mbar_arrive(&ds_full[buf]);
@@ -765,31 +798,42 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tma_kv,  // qkv, box row
     const int quarter = warp & 3, half = (warp - 2) >> 2;
     const int r_local = quarter * 32 + lane;  // kv row inside the tile
     const int kv = jt * 128 + r_local;
-    const int tid = threadIdx.x - 64;         // 0..255 among the elementwise warps
+    const int ew = warp - 2;                   // 0..7 among the elementwise warps
     const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16);
     const float sl2 = p.scale * LOG2E;
     const bool drop = p.p_drop > 0.f;
     const uint64_t s8 = static_cast<uint64_t>((p.s + 7) / 8);
-    const size_t stat_base = (static_cast<size_t>(batch) * p.nh + head) * p.s;
-    uint8_t* mask = smem + C::OFF_MASK;
+    const size_t bh = static_cast<size_t>(batch) * p.nh + head;
+    const float* lse2_row = p.lse2 + bh * p.s_pad;
+    const float* delta_row = p.delta + bh * p.s_pad;
+    // keep bits of the tile, transposed: maskT[buf][kv row][word] holds 32 consecutive query rows
+    uint32_t* maskT = reinterpret_cast<uint32_t*>(smem + C::OFF_MASK);
 
     for (int t = 0; t < n_q; ++t) {
       const int buf = t & 1;
       const uint32_t ph = (t >> 1) & 1;
       const int q0 = (i0 + t) * 64;
       if (drop) {
-        // keep bits are defined along kv (8 per Philox call, attention fwd draws them per query
-        // row); here a thread owns a kv row, so the 64x128 tile of bits is built cooperatively
+        // The forward draws keep bits 8 at a time along kv for one query row. Here a thread owns a
+        // kv row, so the warps rebuild the 64 x 128 tile of bits together: lane = query row, one
+        // Philox call = 8 kv columns, and 8 ballots turn those into 32-query words per kv row.
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-          const int idx = tid * 4 + k;  // 0..1023 = q_local * 16 + kv group
-          const int ql = idx >> 4, g = idx & 15;
-          const Philox8 rnd = philox4x32_10(p.seed, p.offset,
-                                            static_cast<uint64_t>(stat_base + q0 + ql) * s8 + static_cast<uint64_t>(jt * 16 + g));
-          uint32_t bits = 0;
+          const int qw = ew & 1;             // which 32-query word
+          const int g = (ew >> 1) + 4 * k;   // kv group of 8 inside the tile (0..15)
+          const Philox8 rnd = philox4x32_10_rk(p.keys, p.off_lo, p.off_hi,
+                                               (bh * p.s + static_cast<uint64_t>(q0 + qw * 32 + lane)) * s8 +
+                                                   static_cast<uint64_t>(jt * 16 + g));
+          uint32_t mine = 0;
 #pragma unroll
-          for (int e = 0; e < 8; ++e) bits |= (philox_keep(rnd, e, p.thresh) ? 1u : 0u) << e;
-          mask[buf * 1024 + idx] = static_cast<uint8_t>(bits);
+          for (int w = 0; w < 4; ++w) {
+            const uint32_t f = keep_flags2(rnd.lanes[w], p.thresh2);
+            const uint32_t b_lo = __ballot_sync(0xffffffffu, (f >> 15) & 1u);
+            const uint32_t b_hi = __ballot_sync(0xffffffffu, f >> 31);
+            if (lane == 2 * w) mine = b_lo;
+            if (lane == 2 * w + 1) mine = b_hi;
+          }
+          if (lane < 8) maskT[(buf * 128 + g * 8 + lane) * 2 + qw] = mine;
         }
         named_bar_sync(1, 256);
       }
@@ -803,24 +847,30 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tma_kv,  // qkv, box row
       __syncwarp();
       if (lane == 0) mbar_arrive(&st_empty[buf]);
 
-      float pd[32], ds[32];
+      const int qh = q0 + half * 32;  // first query column of this thread's 32
+      const bool diag = (t < 2);      // the first two 64-row query tiles straddle the diagonal
+      const uint32_t mword = drop ? maskT[(buf * 128 + r_local) * 2 + half] : 0xffffffffu;
+      uint32_t pk_p[16], pk_ds[16];
 #pragma unroll
-      for (int i = 0; i < 32; ++i) {
-        const int ql = half * 32 + i;
-        const int q = q0 + ql;
-        const bool valid = (q >= kv) && (q < p.s);
-        const float lse_q = valid ? __ldg(p.lse + stat_base + q) * LOG2E : 0.f;
-        const float delta_q = valid ? __ldg(p.delta + stat_base + q) : 0.f;
-        const float pr = valid ? exp2f(__uint_as_float(rs[i]) * sl2 - lse_q) : 0.f;
-        float dp = __uint_as_float(rp[i]);
-        float pk = pr;
-        if (drop) {
-          const bool keep = (mask[buf * 1024 + ql * 16 + (r_local >> 3)] >> (r_local & 7)) & 1;
-          dp = keep ? dp * p.inv_keep : 0.f;
-          pk = keep ? pr * p.inv_keep : 0.f;
+      for (int i = 0; i < 32; i += 2) {
+        const float2 l2 = __ldg(reinterpret_cast<const float2*>(lse2_row + qh + i));  // warp-uniform address
+        const float2 dl = __ldg(reinterpret_cast<const float2*>(delta_row + qh + i));
+        float p0 = ex2_approx(fmaf(__uint_as_float(rs[i]), sl2, -l2.x));
+        float p1 = ex2_approx(fmaf(__uint_as_float(rs[i + 1]), sl2, -l2.y));
+        if (diag) {
+          p0 = (qh + i < kv) ? 0.f : p0;
+          p1 = (qh + i + 1 < kv) ? 0.f : p1;
         }
-        pd[i] = pk;
-        ds[i] = pr * (dp - delta_q);
+        uint32_t d0 = rp[i], d1 = rp[i + 1], pp = pack_bf16(p0, p1);
+        if (drop) {
+          const uint32_t m0 = static_cast<uint32_t>(static_cast<int32_t>(mword << (31 - i)) >> 31);
+          const uint32_t m1 = static_cast<uint32_t>(static_cast<int32_t>(mword << (30 - i)) >> 31);
+          d0 &= m0;
+          d1 &= m1;
+          pp &= prmt(m0, m1, 0x5410u);
+        }
+        pk_p[i >> 1] = pp;
+        pk_ds[i >> 1] = pack_bf16(p0 * (__uint_as_float(d0) - dl.x), p1 * (__uint_as_float(d1) - dl.y));
       }
       mbar_wait(&pt_empty[buf], ph ^ 1, 56);
       const uint32_t pt_addr = smem_u32(smem + C::OFF_PT + buf * C::PT_BYTES);
@@ -828,10 +878,8 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tma_kv,  // qkv, box row
 #pragma unroll
       for (int g = 0; g < 4; ++g) {
         const uint32_t off = sw128_off(r_local, half * 4 + g);
-        st_shared_v4(pt_addr + off, pack_bf16(pd[g * 8 + 0], pd[g * 8 + 1]), pack_bf16(pd[g * 8 + 2], pd[g * 8 + 3]),
-                     pack_bf16(pd[g * 8 + 4], pd[g * 8 + 5]), pack_bf16(pd[g * 8 + 6], pd[g * 8 + 7]));
-        st_shared_v4(dst_addr + off, pack_bf16(ds[g * 8 + 0], ds[g * 8 + 1]), pack_bf16(ds[g * 8 + 2], ds[g * 8 + 3]),
-                     pack_bf16(ds[g * 8 + 4], ds[g * 8 + 5]), pack_bf16(ds[g * 8 + 6], ds[g * 8 + 7]));
+        st_shared_v4(pt_addr + off, pk_p[g * 4 + 0], pk_p[g * 4 + 1], pk_p[g * 4 + 2], pk_p[g * 4 + 3]);
+        st_shared_v4(dst_addr + off, pk_ds[g * 4 + 0], pk_ds[g * 4 + 1], pk_ds[g * 4 + 2], pk_ds[g * 4 + 3]);
       }
       fence_async_smem();
       __syncwarp();
@@ -882,8 +930,8 @@ static int make_out_map_rows(CUtensorMap* map, const void* out, int b, int s, in
 }
 
 template <int HD>
-static int launch_bwd(cudaStream_t st, const void* dout, const void* qkv, const void* out, const BwdParams& p,
-                      float* delta) {
+static int launch_bwd(cudaStream_t st, const void* dout, const void* qkv, const void* out, const float* lse,
+                      const BwdParams& p, float* lse2, float* delta) {
   static bool attr_set[64] = {false};
   int dev = 0;
   FX_CUDA(cudaGetDevice(&dev));
@@ -899,9 +947,10 @@ static int launch_bwd(cudaStream_t st, const void* dout, const void* qkv, const 
   if ((rc = make_out_map_rows(&do128, dout, p.b, p.s, p.nh, HD, 128))) return rc;
   if ((rc = make_out_map_rows(&do64, dout, p.b, p.s, p.nh, HD, 64))) return rc;
 
-  const size_t total = (size_t)p.b * p.s * p.nh;
+  const size_t total = (size_t)p.b * p.s_pad * p.nh;
   attn_delta_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(
-      static_cast<const __nv_bfloat16*>(dout), static_cast<const __nv_bfloat16*>(out), delta, p.b, p.s, p.nh, HD);
+      static_cast<const __nv_bfloat16*>(dout), static_cast<const __nv_bfloat16*>(out), lse, lse2, delta, p.b, p.s,
+      p.nh, HD, p.s_pad, p.p_drop > 0.f ? log2f(p.inv_keep) : 0.f, 1.0f - p.p_drop);
   FX_LAUNCH_CHECK();
   dim3 grid((p.s + 127) / 128, p.nh, p.b);
   attn_bwd_dkv_kernel<HD><<<grid, BWD_THREADS, DkvCfg<HD>::SMEM_BYTES, st>>>(qkv128, qkv64, do64, p);
@@ -933,8 +982,10 @@ extern "C" int fx_attn_causal_fwd(void* stream, const void* qkv, void* out, floa
   p.lse = lse;
   p.b = b; p.s = s; p.nh = nh;
   p.scale = scale; p.p_drop = p_drop; p.inv_keep = 1.0f / (1.0f - p_drop);
-  p.thresh = dropout_threshold(p_drop);
-  p.seed = seed; p.offset = offset;
+  p.log2_inv_keep = p_drop > 0.f ? log2f(p.inv_keep) : 0.f;
+  p.thresh2 = dropout_threshold(p_drop) * 0x10001u;
+  p.off_lo = static_cast<uint32_t>(offset); p.off_hi = static_cast<uint32_t>(offset >> 32);
+  p.keys = philox_round_keys(seed);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   return hd == 64 ? attn::launch_fwd<64>(st, map, p) : attn::launch_fwd<128>(st, map, p);
 }
@@ -942,7 +993,8 @@ extern "C" int fx_attn_causal_fwd(void* stream, const void* qkv, void* out, floa
 extern "C" size_t fx_attn_causal_bwd_workspace_bytes(int b, int s, int nh, int hd) {
   (void)hd;
   if (b <= 0 || s <= 0 || nh <= 0) return 0;
-  return (size_t)b * s * nh * sizeof(float);  // delta = rowsum(dO * O)
+  const size_t s_pad = ((size_t)s + 127) / 128 * 128;
+  return 2 * (size_t)b * nh * s_pad * sizeof(float);  // lse2 and delta', padded per (batch, head) row
 }
 
 extern "C" int fx_attn_causal_bwd(void* stream, const void* dout, const void* qkv, const void* out,
@@ -958,14 +1010,18 @@ extern "C" int fx_attn_causal_bwd(void* stream, const void* dout, const void* qk
   FX_CHECK_ARG(((uintptr_t)dout | (uintptr_t)qkv | (uintptr_t)out | (uintptr_t)dqkv | (uintptr_t)workspace) % 16 == 0,
                "fx_attn_causal_bwd: pointers must be 16-byte aligned");
   attn::BwdParams p{};
-  p.lse = lse;
-  p.delta = static_cast<const float*>(workspace);
+  p.s_pad = (s + 127) / 128 * 128;
+  float* lse2 = static_cast<float*>(workspace);
+  float* delta = lse2 + (size_t)b * nh * p.s_pad;
+  p.lse2 = lse2;
+  p.delta = delta;
   p.dqkv = static_cast<__nv_bfloat16*>(dqkv);
   p.b = b; p.s = s; p.nh = nh;
   p.scale = scale; p.p_drop = p_drop; p.inv_keep = 1.0f / (1.0f - p_drop);
-  p.thresh = dropout_threshold(p_drop);
-  p.seed = seed; p.offset = offset;
+  p.thresh2 = dropout_threshold(p_drop) * 0x10001u;
+  p.off_lo = static_cast<uint32_t>(offset); p.off_hi = static_cast<uint32_t>(offset >> 32);
+  p.keys = philox_round_keys(seed);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  float* delta = static_cast<float*>(workspace);
-  return hd == 64 ? attn::launch_bwd<64>(st, dout, qkv, out, p, delta) : attn::launch_bwd<128>(st, dout, qkv, out, p, delta);
+  return hd == 64 ? attn::launch_bwd<64>(st, dout, qkv, out, lse, p, lse2, delta)
+                  : attn::launch_bwd<128>(st, dout, qkv, out, lse, p, lse2, delta);
 }

@@ -46,8 +46,10 @@ __device__ __forceinline__ uint64_t global_ns() {
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
   return t;
 }
-// Blocking wait on a phase parity. A pipeline bug would otherwise hang the GPU for good, so
-// the wait carries a watchdog: after ~4 s it prints where it is stuck and traps the kernel.
+// Blocking wait on a phase parity. try_wait carries a suspend-time hint, so a waiting warp is
+// parked by the hardware instead of burning issue slots that the math warps need. A pipeline bug
+// would otherwise hang the GPU for good, so the loop carries a watchdog: every 64 failed tries it
+// looks at the global timer and, 4 s after the first look, reports where it is stuck and traps.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, int tag = 0) {
   const uint32_t addr = smem_u32(bar);
   uint32_t spins = 0;
@@ -56,17 +58,20 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, int ta
     uint32_t done;
     asm volatile(
         "{\n\t.reg .pred P;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 P, [%1], %2;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 P, [%1], %2, %3;\n\t"
         "selp.u32 %0, 1, 0, P;\n\t}\n"
         : "=r"(done)
-        : "r"(addr), "r"(parity)
+        : "r"(addr), "r"(parity), "r"(0x989680u)
         : "memory");
     if (done) break;
-    if (++spins == 4096) t0 = global_ns();
-    if (spins > 4096 && (spins & 1023) == 0 && global_ns() - t0 > 4000000000ull) {
-      printf("fleetx_b200: mbarrier watchdog: block %d thread %d tag %d parity %u\n", blockIdx.x,
-             threadIdx.x, tag, parity);
-      __trap();
+    if ((++spins & 63u) == 0) {
+      const uint64_t now = global_ns();
+      if (t0 == 0) t0 = now;
+      if (now - t0 > 4000000000ull) {
+        printf("fleetx_b200: mbarrier watchdog: block (%d,%d,%d) thread %d tag %d parity %u\n", blockIdx.x,
+               blockIdx.y, blockIdx.z, threadIdx.x, tag, parity);
+        __trap();
+      }
     }
   }
 }
@@ -190,6 +195,18 @@ __device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&r)[32])
 }
 __device__ __forceinline__ void tmem_ld_wait() {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// 2^x, one MUFU op, flush-to-zero (inputs here are <= 0 or bounded; no range fix-up needed)
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
+  uint32_t d;
+  asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(sel));
+  return d;
 }
 
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {

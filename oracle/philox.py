@@ -10,8 +10,8 @@ what is pinned is (seed, offset, index) -> mask between CUDA and this restatemen
 
   key     = (seed lo32, seed hi32)
   counter = (group lo32, group hi32, offset lo32, offset hi32)
-  Philox4x32-10 -> 4 words -> 8 x 16-bit draws (element 2i = low half of word i, 2i+1 = high)
-  keep    <=>  draw >= round(p * 65536)
+  Philox4x32-10 -> 4 words -> 8 x 16-bit lanes (element 2i = low half of word i, 2i+1 = high)
+  keep    <=>  (lane & 0x7fff) >= round(p * 32768)
 """
 from __future__ import annotations
 
@@ -47,14 +47,14 @@ def philox4x32_10(seed: int, offset: int, groups: np.ndarray) -> np.ndarray:
 
 
 def dropout_threshold(p: float) -> int:
-    t = np.float32(p) * np.float32(65536.0) + np.float32(0.5)
-    return int(min(max(float(t), 0.0), 65536.0))
+    t = np.float32(p) * np.float32(32768.0) + np.float32(0.5)
+    return int(min(max(float(t), 0.0), 32767.0))
 
 
 def _keep_from_words(words: np.ndarray, p: float) -> np.ndarray:
     """words uint32 [..., 4] -> keep uint8 [..., 8]."""
-    lo = (words & np.uint32(0xFFFF)).astype(np.uint32)
-    hi = (words >> np.uint32(16)).astype(np.uint32)
+    lo = (words & np.uint32(0x7FFF)).astype(np.uint32)
+    hi = ((words >> np.uint32(16)) & np.uint32(0x7FFF)).astype(np.uint32)
     draws = np.stack([lo, hi], axis=-1).reshape(*words.shape[:-1], 8)
     return (draws >= np.uint32(dropout_threshold(p))).astype(np.uint8)
 

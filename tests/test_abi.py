@@ -30,7 +30,7 @@ def test_host_side_helpers_and_argument_validation():
     assert lib.fx_layernorm_bwd_workspace_bytes(16384, 2048) == 592 * 2 * 2048 * 4
     assert lib.fx_layernorm_bwd_workspace_bytes(10, 128) == 10 * 2 * 128 * 4
     assert lib.fx_layernorm_bwd_workspace_bytes(0, 128) == 0
-    assert lib.fx_attn_causal_bwd_workspace_bytes(2, 100, 4, 64) == 2 * 100 * 4 * 4
+    assert lib.fx_attn_causal_bwd_workspace_bytes(2, 100, 4, 64) == 2 * (2 * 4 * 128 * 4)
     assert lib.fx_colsum_workspace_bytes(0, 8) == 0
     # bad arguments are rejected before any CUDA call, with a message
     rc = lib.fx_gemm_bf16(None, 0, 0, 12, 16, 16, None, 16, None, 16, None, 16, 0, 0, 0, None, None, 0)
