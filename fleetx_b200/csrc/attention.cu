@@ -359,7 +359,8 @@ static int launch_fwd(cudaStream_t st, const CUtensorMap& map, const FwdParams& 
 // =====================================================================================
 // Backward
 // =====================================================================================
-constexpr int BWD_THREADS = 320;  // warp 0 TMA, warp 1 MMA, warps 2..9 elementwise (2 per TMEM lane quarter)
+constexpr int BWD_EW_WARPS = 16;  // elementwise warps: 4 per TMEM lane quarter, 16 of a tile's 64 columns each
+constexpr int BWD_THREADS = 64 + BWD_EW_WARPS * 32;  // warp 0 TMA, warp 1 MMA, warps 2..17 elementwise
 
 struct BwdParams {
   const float* lse2;    // [b, nh, s_pad]  lse·log2(e) − log2(inv_keep); +inf in the padding
@@ -412,6 +413,25 @@ attn_delta_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16* _
   lse2[o_idx] = lse[((size_t)batch * nh + head) * s + row] * LOG2E - log2_inv_keep;
 }
 
+// TMEM accumulator columns [taddr, taddr + NCOLS) of this thread's row -> bf16, times `mul`, to dst.
+template <int NCOLS>
+__device__ __forceinline__ void drain_scaled(uint32_t taddr, __nv_bfloat16* dst, float mul, bool valid) {
+  static_assert(NCOLS == 16 || NCOLS == 32, "");
+  uint32_t r[NCOLS];
+  if constexpr (NCOLS == 16) tmem_ld_32x16(taddr, r);
+  else tmem_ld_32x32(taddr, r);
+  tmem_ld_wait();
+  if (valid) {
+    uint4* o = reinterpret_cast<uint4*>(dst);
+#pragma unroll
+    for (int g = 0; g < NCOLS / 8; ++g)
+      o[g] = make_uint4(pack_bf16(__uint_as_float(r[g * 8 + 0]) * mul, __uint_as_float(r[g * 8 + 1]) * mul),
+                        pack_bf16(__uint_as_float(r[g * 8 + 2]) * mul, __uint_as_float(r[g * 8 + 3]) * mul),
+                        pack_bf16(__uint_as_float(r[g * 8 + 4]) * mul, __uint_as_float(r[g * 8 + 5]) * mul),
+                        pack_bf16(__uint_as_float(r[g * 8 + 6]) * mul, __uint_as_float(r[g * 8 + 7]) * mul));
+  }
+}
+
 // ---------------------------------------------------------------------------- dQ kernel
 template <int HD>
 struct DqCfg {
@@ -419,11 +439,14 @@ struct DqCfg {
   static constexpr int KV_BYTES = 64 * HD * 2;    // K / V tile (64 rows)
   static constexpr int KV_SUB = 64 * 128;         // one 64-col sub-tile of a 64-row tile
   static constexpr int DS_BYTES = 128 * 64 * 2;
+  // K/V ring depth: a slot is only released when the dQ MMA that reads K retires, so the ring must
+  // be deep enough for the next loads to be in flight a few tiles ahead of their use
+  static constexpr int NKV = HD == 64 ? 4 : 3;
   static constexpr int OFF_Q = 0;
   static constexpr int OFF_DO = QT_BYTES;
   static constexpr int OFF_K = 2 * QT_BYTES;
-  static constexpr int OFF_V = OFF_K + 2 * KV_BYTES;
-  static constexpr int OFF_DS = OFF_V + 2 * KV_BYTES;
+  static constexpr int OFF_V = OFF_K + NKV * KV_BYTES;
+  static constexpr int OFF_DS = OFF_V + NKV * KV_BYTES;
   static constexpr int OFF_BAR = OFF_DS + 2 * DS_BYTES;
   static constexpr int SMEM_BYTES = OFF_BAR + 256;
   static constexpr int TM_S = 0, TM_DP = 128, TM_DQ = 256;
@@ -440,14 +463,14 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tma_q,   // qkv, box rows
   extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::OFF_BAR);
   uint64_t* qdo_full = bars;        // 1
-  uint64_t* kv_full = bars + 1;     // 2
-  uint64_t* kv_empty = bars + 3;    // 2
-  uint64_t* s_full = bars + 5;      // 2
-  uint64_t* s_empty = bars + 7;     // 2
-  uint64_t* ds_full = bars + 9;     // 2
-  uint64_t* ds_empty = bars + 11;   // 2
-  uint64_t* dq_full = bars + 13;    // 1
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 14);
+  uint64_t* kv_full = bars + 1;     // NKV (<= 4)
+  uint64_t* kv_empty = bars + 5;    // NKV
+  uint64_t* s_full = bars + 9;      // 2
+  uint64_t* s_empty = bars + 11;    // 2
+  uint64_t* ds_full = bars + 13;    // 2
+  uint64_t* ds_empty = bars + 15;   // 2
+  uint64_t* dq_full = bars + 17;    // 1
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 18);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int num_qt = (p.s + 127) / 128;
@@ -465,12 +488,14 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tma_q,   // qkv, box rows
     if (lane == 0) {
       mbar_init(qdo_full, 1);
       mbar_init(dq_full, 1);
-      for (int i = 0; i < 2; ++i) {
+      for (int i = 0; i < C::NKV; ++i) {
         mbar_init(&kv_full[i], 1);
         mbar_init(&kv_empty[i], 1);
+      }
+      for (int i = 0; i < 2; ++i) {
         mbar_init(&s_full[i], 1);
-        mbar_init(&s_empty[i], 8);
-        mbar_init(&ds_full[i], 8);
+        mbar_init(&s_empty[i], BWD_EW_WARPS);
+        mbar_init(&ds_full[i], BWD_EW_WARPS);
         mbar_init(&ds_empty[i], 1);
       }
       mbar_fence_init();
@@ -492,14 +517,14 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tma_q,   // qkv, box rows
         tma_load_4d(smem + C::OFF_DO + h2 * 16384, &tma_do, qdo_full, h2 * 64, head, qt * 128, batch);
       }
       for (int j = 0; j < n_kv; ++j) {
-        const int buf = j & 1;
-        mbar_wait(&kv_empty[buf], ((j >> 1) & 1) ^ 1, 40);
-        mbar_expect_tx(&kv_full[buf], 2 * C::KV_BYTES);
+        const int st = j % C::NKV;
+        mbar_wait(&kv_empty[st], ((j / C::NKV) & 1) ^ 1, 40);
+        mbar_expect_tx(&kv_full[st], 2 * C::KV_BYTES);
 #pragma unroll
         for (int h2 = 0; h2 < HD / 64; ++h2) {
-          tma_load_4d(smem + C::OFF_K + buf * C::KV_BYTES + h2 * C::KV_SUB, &tma_kv, &kv_full[buf], h2 * 64,
+          tma_load_4d(smem + C::OFF_K + st * C::KV_BYTES + h2 * C::KV_SUB, &tma_kv, &kv_full[st], h2 * 64,
                       head * 3 + 1, j * 64, batch);
-          tma_load_4d(smem + C::OFF_V + buf * C::KV_BYTES + h2 * C::KV_SUB, &tma_kv, &kv_full[buf], h2 * 64,
+          tma_load_4d(smem + C::OFF_V + st * C::KV_BYTES + h2 * C::KV_SUB, &tma_kv, &kv_full[st], h2 * 64,
                       head * 3 + 2, j * 64, batch);
         }
       }
@@ -510,14 +535,14 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tma_q,   // qkv, box rows
     const uint32_t q_addr = smem_u32(smem + C::OFF_Q), do_addr = smem_u32(smem + C::OFF_DO);
 
     auto issue_sdp = [&](int j) {
-      const int buf = j & 1;
+      const int buf = j & 1, st = j % C::NKV;
       const uint32_t ph = (j >> 1) & 1;
-      mbar_wait(&kv_full[buf], ph, 41);
+      mbar_wait(&kv_full[st], (j / C::NKV) & 1, 41);
       mbar_wait(&s_empty[buf], ph ^ 1, 42);
       tc_fence_after();
       if (lane == 0) {
-        const uint32_t k_addr = smem_u32(smem + C::OFF_K + buf * C::KV_BYTES);
-        const uint32_t v_addr = smem_u32(smem + C::OFF_V + buf * C::KV_BYTES);
+        const uint32_t k_addr = smem_u32(smem + C::OFF_K + st * C::KV_BYTES);
+        const uint32_t v_addr = smem_u32(smem + C::OFF_V + st * C::KV_BYTES);
 #pragma unroll
         for (int kk = 0; kk < HD / 16; ++kk) {
           const uint32_t offa = (kk >> 2) * 16384 + (kk & 3) * 32, offb = (kk >> 2) * C::KV_SUB + (kk & 3) * 32;
@@ -539,24 +564,24 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tma_q,   // qkv, box rows
     issue_sdp(0);
     for (int j = 0; j < n_kv; ++j) {
       if (j + 1 < n_kv) issue_sdp(j + 1);
-      const int buf = j & 1;
+      const int buf = j & 1, st = j % C::NKV;
       mbar_wait(&ds_full[buf], (j >> 1) & 1, 44);
       tc_fence_after();
       if (lane == 0) {
         const uint32_t ds_addr = smem_u32(smem + C::OFF_DS + buf * C::DS_BYTES);
-        const uint32_t k_addr = smem_u32(smem + C::OFF_K + buf * C::KV_BYTES);
+        const uint32_t k_addr = smem_u32(smem + C::OFF_K + st * C::KV_BYTES);
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)
           umma_ss(tmem_base + C::TM_DQ, smem_desc_sw128(ds_addr + kk * 32, 0, 1024),
                   smem_desc_sw128(k_addr + kk * 2048, C::KV_SUB, 1024), idesc_dq, (j | kk) != 0);
         umma_commit(&ds_empty[buf]);
-        umma_commit(&kv_empty[buf]);
+        umma_commit(&kv_empty[st]);
         if (j == n_kv - 1) umma_commit(dq_full);
       }
       __syncwarp();
     }
   } else {
-    const int quarter = warp & 3, half = (warp - 2) >> 2;
+    const int quarter = warp & 3, part = (warp - 2) >> 2;  // part: which 16 of the tile's 64 kv columns
     const int row_local = quarter * 32 + lane;
     const int row = qt * 128 + row_local;
     const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16);
@@ -574,18 +599,18 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tma_q,   // qkv, box rows
       const bool diag = (j >= 2 * qt);  // the last two 64-wide KV tiles straddle the diagonal
       mbar_wait(&s_full[buf], ph, 45);
       tc_fence_after();
-      uint32_t rs[32], rp[32];
-      tmem_ld_32x32(lane_base + C::TM_S + buf * 64 + half * 32, rs);
-      tmem_ld_32x32(lane_base + C::TM_DP + buf * 64 + half * 32, rp);
+      uint32_t rs[16], rp[16];
+      tmem_ld_32x16(lane_base + C::TM_S + buf * 64 + part * 16, rs);
+      tmem_ld_32x16(lane_base + C::TM_DP + buf * 64 + part * 16, rp);
       tmem_ld_wait();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&s_empty[buf]);
-      const int kv0 = j * 64 + half * 32;
+      const int kv0 = j * 64 + part * 16;
       if (drop) {
         // zero dP where the forward dropped P: AND the fp32 bits with an all-ones / all-zeros mask
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
+        for (int g = 0; g < 2; ++g) {
           const Philox8 rnd = philox4x32_10_rk(p.keys, p.off_lo, p.off_hi, grp_row + static_cast<uint64_t>((kv0 >> 3) + g));
 #pragma unroll
           for (int w = 0; w < 4; ++w) {
@@ -595,9 +620,9 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tma_q,   // qkv, box rows
           }
         }
       }
-      uint32_t pk[16];
+      uint32_t pk[8];
 #pragma unroll
-      for (int i = 0; i < 32; i += 2) {
+      for (int i = 0; i < 16; i += 2) {
         float p0 = ex2_approx(fmaf(__uint_as_float(rs[i]), sl2, neg_lse2));
         float p1 = ex2_approx(fmaf(__uint_as_float(rs[i + 1]), sl2, neg_lse2));
         if (diag) {
@@ -609,33 +634,19 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tma_q,   // qkv, box rows
       mbar_wait(&ds_empty[buf], ph ^ 1, 46);
       const uint32_t ds_addr = smem_u32(smem + C::OFF_DS + buf * C::DS_BYTES);
 #pragma unroll
-      for (int g = 0; g < 4; ++g)
-        st_shared_v4(ds_addr + sw128_off(row_local, half * 4 + g), pk[g * 4 + 0], pk[g * 4 + 1], pk[g * 4 + 2],
+      for (int g = 0; g < 2; ++g)
+        st_shared_v4(ds_addr + sw128_off(row_local, part * 2 + g), pk[g * 4 + 0], pk[g * 4 + 1], pk[g * 4 + 2],
                      pk[g * 4 + 3]);
       fence_async_smem();
       __syncwarp();
       if (lane == 0) mbar_arrive(&ds_full[buf]);
     }
 
-    // dQ = scale * (dS · K): this warp drains columns [half*HD/2, +HD/2) of its 32 rows
+    // dQ = scale * (dS · K): this warp drains columns [part*HD/4, +HD/4) of its 32 rows
     mbar_wait(dq_full, 0, 47);
     tc_fence_after();
-    __nv_bfloat16* dst = p.dqkv + ((static_cast<size_t>(batch) * p.s + row) * p.nh + head) * (3 * HD) + half * (HD / 2);
-#pragma unroll
-    for (int c = 0; c < HD / 64; ++c) {
-      uint32_t r[32];
-      tmem_ld_32x32(lane_base + C::TM_DQ + half * (HD / 2) + c * 32, r);
-      tmem_ld_wait();
-      if (row < p.s) {
-        uint4* o = reinterpret_cast<uint4*>(dst + c * 32);
-#pragma unroll
-        for (int g = 0; g < 4; ++g)
-          o[g] = make_uint4(pack_bf16(__uint_as_float(r[g * 8 + 0]) * p.scale, __uint_as_float(r[g * 8 + 1]) * p.scale),
-                            pack_bf16(__uint_as_float(r[g * 8 + 2]) * p.scale, __uint_as_float(r[g * 8 + 3]) * p.scale),
-                            pack_bf16(__uint_as_float(r[g * 8 + 4]) * p.scale, __uint_as_float(r[g * 8 + 5]) * p.scale),
-                            pack_bf16(__uint_as_float(r[g * 8 + 6]) * p.scale, __uint_as_float(r[g * 8 + 7]) * p.scale));
-      }
-    }
+    __nv_bfloat16* dst = p.dqkv + ((static_cast<size_t>(batch) * p.s + row) * p.nh + head) * (3 * HD) + part * (HD / 4);
+    drain_scaled<HD / 4>(lane_base + C::TM_DQ + part * (HD / 4), dst, p.scale, row < p.s);
   }
 
   tc_fence_before();
@@ -650,14 +661,18 @@ struct DkvCfg {
   static constexpr int Q_BYTES = 64 * HD * 2;    // Q / dO tile (64 rows), 2-deep ring
   static constexpr int Q_SUB = 64 * 128;
   static constexpr int PT_BYTES = 128 * 64 * 2;  // P^T / dS^T tile [128 kv x 64 q]
+  // Q/dO ring depth: a slot is only released when the dV/dK MMAs that read it retire, so the ring
+  // must be deep enough for the next loads to be in flight a few tiles ahead of their use
+  static constexpr int NQ = HD == 64 ? 4 : 2;
   static constexpr int OFF_K = 0;
   static constexpr int OFF_V = KV_BYTES;
   static constexpr int OFF_Q = 2 * KV_BYTES;
-  static constexpr int OFF_DO = OFF_Q + 2 * Q_BYTES;
-  static constexpr int OFF_PT = OFF_DO + 2 * Q_BYTES;
+  static constexpr int OFF_DO = OFF_Q + NQ * Q_BYTES;
+  static constexpr int OFF_PT = OFF_DO + NQ * Q_BYTES;
   static constexpr int OFF_DST = OFF_PT + 2 * PT_BYTES;
-  static constexpr int OFF_MASK = OFF_DST + 2 * PT_BYTES;  // [2][64 q][16 bytes]: keep bits of 128 kv
-  static constexpr int OFF_BAR = OFF_MASK + 2 * 1024;
+  static constexpr int OFF_MASK = OFF_DST + 2 * PT_BYTES;  // [2][128 kv][2 words]: keep bits, 32 queries per word
+  static constexpr int OFF_STAT = OFF_MASK + 2 * 1024;     // [NQ][lse2 | delta'][64 queries] fp32
+  static constexpr int OFF_BAR = OFF_STAT + NQ * 512;
   static constexpr int SMEM_BYTES = OFF_BAR + 256;
   static constexpr int TM_ST = 0, TM_DPT = 128, TM_DV = 256, TM_DK = 256 + HD;
   static constexpr int TMEM_COLS = 512;
@@ -673,14 +688,14 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tma_kv,  // qkv, box row
   extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::OFF_BAR);
   uint64_t* kv_full = bars;          // 1
-  uint64_t* q_full = bars + 1;       // 2
-  uint64_t* q_empty = bars + 3;      // 2
-  uint64_t* st_full = bars + 5;      // 2
-  uint64_t* st_empty = bars + 7;     // 2
-  uint64_t* pt_full = bars + 9;      // 2
-  uint64_t* pt_empty = bars + 11;    // 2
-  uint64_t* acc_full = bars + 13;    // 1
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 14);
+  uint64_t* q_full = bars + 1;       // NQ (<= 4)
+  uint64_t* q_empty = bars + 5;      // NQ
+  uint64_t* st_full = bars + 9;      // 2
+  uint64_t* st_empty = bars + 11;    // 2
+  uint64_t* pt_full = bars + 13;     // 2
+  uint64_t* pt_empty = bars + 15;    // 2
+  uint64_t* acc_full = bars + 17;    // 1
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 18);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int jt = blockIdx.x;  // KV tile; low tiles walk the most query tiles and start first
@@ -698,12 +713,14 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tma_kv,  // qkv, box row
     if (lane == 0) {
       mbar_init(kv_full, 1);
       mbar_init(acc_full, 1);
-      for (int i = 0; i < 2; ++i) {
+      for (int i = 0; i < C::NQ; ++i) {
         mbar_init(&q_full[i], 1);
         mbar_init(&q_empty[i], 1);
+      }
+      for (int i = 0; i < 2; ++i) {
         mbar_init(&st_full[i], 1);
-        mbar_init(&st_empty[i], 8);
-        mbar_init(&pt_full[i], 8);
+        mbar_init(&st_empty[i], BWD_EW_WARPS);
+        mbar_init(&pt_full[i], BWD_EW_WARPS);
         mbar_init(&pt_empty[i], 1);
       }
       mbar_fence_init();
@@ -725,14 +742,17 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tma_kv,  // qkv, box row
         tma_load_4d(smem + C::OFF_V + h2 * 16384, &tma_kv, kv_full, h2 * 64, head * 3 + 2, jt * 128, batch);
       }
       for (int t = 0; t < n_q; ++t) {
-        const int buf = t & 1;
-        mbar_wait(&q_empty[buf], ((t >> 1) & 1) ^ 1, 50);
-        mbar_expect_tx(&q_full[buf], 2 * C::Q_BYTES);
+        const int st = t % C::NQ;
+        mbar_wait(&q_empty[st], ((t / C::NQ) & 1) ^ 1, 50);
+        mbar_expect_tx(&q_full[st], 2 * C::Q_BYTES + 512);
+        const size_t stat_off = (static_cast<size_t>(batch) * p.nh + head) * p.s_pad + (i0 + t) * 64;
+        bulk_copy_g2s(smem + C::OFF_STAT + st * 512, p.lse2 + stat_off, 256, &q_full[st]);
+        bulk_copy_g2s(smem + C::OFF_STAT + st * 512 + 256, p.delta + stat_off, 256, &q_full[st]);
 #pragma unroll
         for (int h2 = 0; h2 < HD / 64; ++h2) {
-          tma_load_4d(smem + C::OFF_Q + buf * C::Q_BYTES + h2 * C::Q_SUB, &tma_q, &q_full[buf], h2 * 64, head * 3 + 0,
+          tma_load_4d(smem + C::OFF_Q + st * C::Q_BYTES + h2 * C::Q_SUB, &tma_q, &q_full[st], h2 * 64, head * 3 + 0,
                       (i0 + t) * 64, batch);
-          tma_load_4d(smem + C::OFF_DO + buf * C::Q_BYTES + h2 * C::Q_SUB, &tma_do, &q_full[buf], h2 * 64, head,
+          tma_load_4d(smem + C::OFF_DO + st * C::Q_BYTES + h2 * C::Q_SUB, &tma_do, &q_full[st], h2 * 64, head,
                       (i0 + t) * 64, batch);
         }
       }
@@ -743,14 +763,14 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tma_kv,  // qkv, box row
     const uint32_t k_addr = smem_u32(smem + C::OFF_K), v_addr = smem_u32(smem + C::OFF_V);
 
     auto issue_st = [&](int t) {
-      const int buf = t & 1;
+      const int buf = t & 1, st = t % C::NQ;
       const uint32_t ph = (t >> 1) & 1;
-      mbar_wait(&q_full[buf], ph, 51);
+      mbar_wait(&q_full[st], (t / C::NQ) & 1, 51);
       mbar_wait(&st_empty[buf], ph ^ 1, 52);
       tc_fence_after();
       if (lane == 0) {
-        const uint32_t q_addr = smem_u32(smem + C::OFF_Q + buf * C::Q_BYTES);
-        const uint32_t do_addr = smem_u32(smem + C::OFF_DO + buf * C::Q_BYTES);
+        const uint32_t q_addr = smem_u32(smem + C::OFF_Q + st * C::Q_BYTES);
+        const uint32_t do_addr = smem_u32(smem + C::OFF_DO + st * C::Q_BYTES);
 #pragma unroll
         for (int kk = 0; kk < HD / 16; ++kk) {
           const uint32_t offa = (kk >> 2) * 16384 + (kk & 3) * 32, offb = (kk >> 2) * C::Q_SUB + (kk & 3) * 32;
@@ -772,14 +792,14 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tma_kv,  // qkv, box row
     issue_st(0);
     for (int t = 0; t < n_q; ++t) {
       if (t + 1 < n_q) issue_st(t + 1);
-      const int buf = t & 1;
+      const int buf = t & 1, st = t % C::NQ;
       mbar_wait(&pt_full[buf], (t >> 1) & 1, 54);
       tc_fence_after();
       if (lane == 0) {
         const uint32_t pt_addr = smem_u32(smem + C::OFF_PT + buf * C::PT_BYTES);
         const uint32_t dst_addr = smem_u32(smem + C::OFF_DST + buf * C::PT_BYTES);
-        const uint32_t q_addr = smem_u32(smem + C::OFF_Q + buf * C::Q_BYTES);
-        const uint32_t do_addr = smem_u32(smem + C::OFF_DO + buf * C::Q_BYTES);
+        const uint32_t q_addr = smem_u32(smem + C::OFF_Q + st * C::Q_BYTES);
+        const uint32_t do_addr = smem_u32(smem + C::OFF_DO + st * C::Q_BYTES);
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)
           umma_ss(tmem_base + C::TM_DV, smem_desc_sw128(pt_addr + kk * 32, 0, 1024),
@@ -789,23 +809,21 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tma_kv,  // qkv, box row
           umma_ss(tmem_base + C::TM_DK, smem_desc_sw128(dst_addr + kk * 32, 0, 1024),
                   smem_desc_sw128(q_addr + kk * 2048, C::Q_SUB, 1024), idesc_acc, (t | kk) != 0);
         umma_commit(&pt_empty[buf]);
-        umma_commit(&q_empty[buf]);
+        umma_commit(&q_empty[st]);
         if (t == n_q - 1) umma_commit(acc_full);
       }
       __syncwarp();
     }
   } else {
-    const int quarter = warp & 3, half = (warp - 2) >> 2;
-    const int r_local = quarter * 32 + lane;  // kv row inside the tile
+    const int quarter = warp & 3, part = (warp - 2) >> 2;  // part: which 16 of the tile's 64 query columns
+    const int r_local = quarter * 32 + lane;                // kv row inside the tile
     const int kv = jt * 128 + r_local;
-    const int ew = warp - 2;                   // 0..7 among the elementwise warps
+    const int ew = warp - 2;                                 // 0..15 among the elementwise warps
     const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16);
     const float sl2 = p.scale * LOG2E;
     const bool drop = p.p_drop > 0.f;
     const uint64_t s8 = static_cast<uint64_t>((p.s + 7) / 8);
     const size_t bh = static_cast<size_t>(batch) * p.nh + head;
-    const float* lse2_row = p.lse2 + bh * p.s_pad;
-    const float* delta_row = p.delta + bh * p.s_pad;
     // keep bits of the tile, transposed: maskT[buf][kv row][word] holds 32 consecutive query rows
     uint32_t* maskT = reinterpret_cast<uint32_t*>(smem + C::OFF_MASK);
 
@@ -818,9 +836,9 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tma_kv,  // qkv, box row
         // kv row, so the warps rebuild the 64 x 128 tile of bits together: lane = query row, one
         // Philox call = 8 kv columns, and 8 ballots turn those into 32-query words per kv row.
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
+        for (int k = 0; k < 2; ++k) {
           const int qw = ew & 1;             // which 32-query word
-          const int g = (ew >> 1) + 4 * k;   // kv group of 8 inside the tile (0..15)
+          const int g = (ew >> 1) + 8 * k;   // kv group of 8 inside the tile (0..15)
           const Philox8 rnd = philox4x32_10_rk(p.keys, p.off_lo, p.off_hi,
                                                (bh * p.s + static_cast<uint64_t>(q0 + qw * 32 + lane)) * s8 +
                                                    static_cast<uint64_t>(jt * 16 + g));
@@ -835,49 +853,57 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tma_kv,  // qkv, box row
           }
           if (lane < 8) maskT[(buf * 128 + g * 8 + lane) * 2 + qw] = mine;
         }
-        named_bar_sync(1, 256);
+        named_bar_sync(1, BWD_EW_WARPS * 32);
       }
-      mbar_wait(&st_full[buf], ph, 55);
+      const int qst = t % C::NQ;
+      mbar_wait(&q_full[qst], (t / C::NQ) & 1, 58);  // the bulk-copied row statistics of this tile have landed
+      mbar_wait(&st_full[buf], ph, 55);  // S^T / dP^T are in TMEM
       tc_fence_after();
-      uint32_t rs[32], rp[32];
-      tmem_ld_32x32(lane_base + C::TM_ST + buf * 64 + half * 32, rs);
-      tmem_ld_32x32(lane_base + C::TM_DPT + buf * 64 + half * 32, rp);
+      uint32_t rs[16], rp[16];
+      tmem_ld_32x16(lane_base + C::TM_ST + buf * 64 + part * 16, rs);
+      tmem_ld_32x16(lane_base + C::TM_DPT + buf * 64 + part * 16, rp);
       tmem_ld_wait();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&st_empty[buf]);
 
-      const int qh = q0 + half * 32;  // first query column of this thread's 32
+      const int qh = q0 + part * 16;  // first query column of this thread's 16
       const bool diag = (t < 2);      // the first two 64-row query tiles straddle the diagonal
-      const uint32_t mword = drop ? maskT[(buf * 128 + r_local) * 2 + half] : 0xffffffffu;
-      uint32_t pk_p[16], pk_ds[16];
+      const float* stat = reinterpret_cast<const float*>(smem + C::OFF_STAT + qst * 512) + part * 16;
+      const uint32_t mbits = drop ? (maskT[(buf * 128 + r_local) * 2 + (part >> 1)] >> ((part & 1) * 16)) : 0xffffu;
+      uint32_t pk_p[8], pk_ds[8];
 #pragma unroll
-      for (int i = 0; i < 32; i += 2) {
-        const float2 l2 = __ldg(reinterpret_cast<const float2*>(lse2_row + qh + i));  // warp-uniform address
-        const float2 dl = __ldg(reinterpret_cast<const float2*>(delta_row + qh + i));
-        float p0 = ex2_approx(fmaf(__uint_as_float(rs[i]), sl2, -l2.x));
-        float p1 = ex2_approx(fmaf(__uint_as_float(rs[i + 1]), sl2, -l2.y));
-        if (diag) {
-          p0 = (qh + i < kv) ? 0.f : p0;
-          p1 = (qh + i + 1 < kv) ? 0.f : p1;
+      for (int i4 = 0; i4 < 16; i4 += 4) {
+        const float4 l2 = *reinterpret_cast<const float4*>(stat + i4);       // warp-uniform: broadcast
+        const float4 dl = *reinterpret_cast<const float4*>(stat + 64 + i4);
+        const float l2v[4] = {l2.x, l2.y, l2.z, l2.w}, dlv[4] = {dl.x, dl.y, dl.z, dl.w};
+#pragma unroll
+        for (int u = 0; u < 4; u += 2) {
+          const int i = i4 + u;
+          float p0 = ex2_approx(fmaf(__uint_as_float(rs[i]), sl2, -l2v[u]));
+          float p1 = ex2_approx(fmaf(__uint_as_float(rs[i + 1]), sl2, -l2v[u + 1]));
+          if (diag) {
+            p0 = (qh + i < kv) ? 0.f : p0;
+            p1 = (qh + i + 1 < kv) ? 0.f : p1;
+          }
+          uint32_t d0 = rp[i], d1 = rp[i + 1], pp = pack_bf16(p0, p1);
+          if (drop) {
+            const uint32_t m0 = static_cast<uint32_t>(static_cast<int32_t>(mbits << (31 - i)) >> 31);
+            const uint32_t m1 = static_cast<uint32_t>(static_cast<int32_t>(mbits << (30 - i)) >> 31);
+            d0 &= m0;
+            d1 &= m1;
+            pp &= prmt(m0, m1, 0x5410u);
+          }
+          pk_p[i >> 1] = pp;
+          pk_ds[i >> 1] = pack_bf16(p0 * (__uint_as_float(d0) - dlv[u]), p1 * (__uint_as_float(d1) - dlv[u + 1]));
         }
-        uint32_t d0 = rp[i], d1 = rp[i + 1], pp = pack_bf16(p0, p1);
-        if (drop) {
-          const uint32_t m0 = static_cast<uint32_t>(static_cast<int32_t>(mword << (31 - i)) >> 31);
-          const uint32_t m1 = static_cast<uint32_t>(static_cast<int32_t>(mword << (30 - i)) >> 31);
-          d0 &= m0;
-          d1 &= m1;
-          pp &= prmt(m0, m1, 0x5410u);
-        }
-        pk_p[i >> 1] = pp;
-        pk_ds[i >> 1] = pack_bf16(p0 * (__uint_as_float(d0) - dl.x), p1 * (__uint_as_float(d1) - dl.y));
       }
       mbar_wait(&pt_empty[buf], ph ^ 1, 56);
       const uint32_t pt_addr = smem_u32(smem + C::OFF_PT + buf * C::PT_BYTES);
       const uint32_t dst_addr = smem_u32(smem + C::OFF_DST + buf * C::PT_BYTES);
 #pragma unroll
-      for (int g = 0; g < 4; ++g) {
-        const uint32_t off = sw128_off(r_local, half * 4 + g);
+      for (int g = 0; g < 2; ++g) {
+        const uint32_t off = sw128_off(r_local, part * 2 + g);
         st_shared_v4(pt_addr + off, pk_p[g * 4 + 0], pk_p[g * 4 + 1], pk_p[g * 4 + 2], pk_p[g * 4 + 3]);
         st_shared_v4(dst_addr + off, pk_ds[g * 4 + 0], pk_ds[g * 4 + 1], pk_ds[g * 4 + 2], pk_ds[g * 4 + 3]);
       }
@@ -886,29 +912,12 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tma_kv,  // qkv, box row
       if (lane == 0) mbar_arrive(&pt_full[buf]);
     }
 
-    // dV = P_drop^T · dO, dK = scale * dS^T · Q; this warp drains columns [half*HD/2, +HD/2)
+    // dV = P_drop^T · dO, dK = scale * dS^T · Q; this warp drains columns [part*HD/4, +HD/4)
     mbar_wait(acc_full, 0, 57);
     tc_fence_after();
-    __nv_bfloat16* base = p.dqkv + ((static_cast<size_t>(batch) * p.s + kv) * p.nh + head) * (3 * HD) + half * (HD / 2);
-#pragma unroll
-    for (int which = 0; which < 2; ++which) {  // 0: dK, 1: dV
-      const float mul = which == 0 ? p.scale : 1.0f;
-#pragma unroll
-      for (int c = 0; c < HD / 64; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32(lane_base + (which == 0 ? C::TM_DK : C::TM_DV) + half * (HD / 2) + c * 32, r);
-        tmem_ld_wait();
-        if (kv < p.s) {
-          uint4* o = reinterpret_cast<uint4*>(base + (which + 1) * HD + c * 32);
-#pragma unroll
-          for (int g = 0; g < 4; ++g)
-            o[g] = make_uint4(pack_bf16(__uint_as_float(r[g * 8 + 0]) * mul, __uint_as_float(r[g * 8 + 1]) * mul),
-                              pack_bf16(__uint_as_float(r[g * 8 + 2]) * mul, __uint_as_float(r[g * 8 + 3]) * mul),
-                              pack_bf16(__uint_as_float(r[g * 8 + 4]) * mul, __uint_as_float(r[g * 8 + 5]) * mul),
-                              pack_bf16(__uint_as_float(r[g * 8 + 6]) * mul, __uint_as_float(r[g * 8 + 7]) * mul));
-        }
-      }
-    }
+    __nv_bfloat16* base = p.dqkv + ((static_cast<size_t>(batch) * p.s + kv) * p.nh + head) * (3 * HD) + part * (HD / 4);
+    drain_scaled<HD / 4>(lane_base + C::TM_DK + part * (HD / 4), base + HD, p.scale, kv < p.s);
+    drain_scaled<HD / 4>(lane_base + C::TM_DV + part * (HD / 4), base + 2 * HD, 1.0f, kv < p.s);
   }
 
   tc_fence_before();
