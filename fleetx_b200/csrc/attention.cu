@@ -362,6 +362,24 @@ static int launch_fwd(cudaStream_t st, const CUtensorMap& map, const FwdParams& 
 constexpr int BWD_EW_WARPS = 16;  // elementwise warps: 4 per TMEM lane quarter, 16 of a tile's 64 columns each
 constexpr int BWD_THREADS = 64 + BWD_EW_WARPS * 32;  // warp 0 TMA, warp 1 MMA, warps 2..17 elementwise
 
+#ifdef FX_TRACE
+// Debug-only phase timing (tools/micro/trace_attn.py builds a private copy of this file with
+// -DFX_TRACE). g_trace[i] accumulates clock64 deltas of phase i for one elementwise warp per CTA.
+__device__ unsigned long long g_trace[16];
+#define FX_T0() long long t_trace = clock64()
+#define FX_T(i)                                                                       \
+  do {                                                                                \
+    if (warp == 2 && lane == 0) {                                                     \
+      const long long n_ = clock64();                                                 \
+      atomicAdd(&g_trace[i], static_cast<unsigned long long>(n_ - t_trace));          \
+      t_trace = n_;                                                                   \
+    }                                                                                 \
+  } while (0)
+#else
+#define FX_T0() do {} while (0)
+#define FX_T(i) do {} while (0)
+#endif
+
 struct BwdParams {
   const float* lse2;    // [b, nh, s_pad]  lse·log2(e) − log2(inv_keep); +inf in the padding
   const float* delta;   // [b, nh, s_pad]  rowsum(dO ∘ O) / inv_keep;     0 in the padding
@@ -438,7 +456,6 @@ struct DqCfg {
   static constexpr int QT_BYTES = 128 * HD * 2;   // Q / dO tile (128 rows)
   static constexpr int KV_BYTES = 64 * HD * 2;    // K / V tile (64 rows)
   static constexpr int KV_SUB = 64 * 128;         // one 64-col sub-tile of a 64-row tile
-  static constexpr int DS_BYTES = 128 * 64 * 2;
   // K/V ring depth: a slot is only released when the dQ MMA that reads K retires, so the ring must
   // be deep enough for the next loads to be in flight a few tiles ahead of their use
   static constexpr int NKV = HD == 64 ? 4 : 3;
@@ -446,9 +463,10 @@ struct DqCfg {
   static constexpr int OFF_DO = QT_BYTES;
   static constexpr int OFF_K = 2 * QT_BYTES;
   static constexpr int OFF_V = OFF_K + NKV * KV_BYTES;
-  static constexpr int OFF_DS = OFF_V + NKV * KV_BYTES;
-  static constexpr int OFF_BAR = OFF_DS + 2 * DS_BYTES;
+  static constexpr int OFF_BAR = OFF_V + NKV * KV_BYTES;
   static constexpr int SMEM_BYTES = OFF_BAR + 256;
+  // TMEM: S[2] | dP[2] | dQ. dS (bf16) is written back over the dP columns it came from and is
+  // the A operand of the dQ MMA straight from TMEM.
   static constexpr int TM_S = 0, TM_DP = 128, TM_DQ = 256;
   static constexpr int TMEM_COLS = 512;
 };
@@ -466,9 +484,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tma_q,   // qkv, box rows
   uint64_t* kv_full = bars + 1;     // NKV (<= 4)
   uint64_t* kv_empty = bars + 5;    // NKV
   uint64_t* s_full = bars + 9;      // 2
-  uint64_t* s_empty = bars + 11;    // 2
   uint64_t* ds_full = bars + 13;    // 2
-  uint64_t* ds_empty = bars + 15;   // 2
   uint64_t* dq_full = bars + 17;    // 1
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 18);
 
@@ -494,9 +510,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tma_q,   // qkv, box rows
       }
       for (int i = 0; i < 2; ++i) {
         mbar_init(&s_full[i], 1);
-        mbar_init(&s_empty[i], BWD_EW_WARPS);
         mbar_init(&ds_full[i], BWD_EW_WARPS);
-        mbar_init(&ds_empty[i], 1);
       }
       mbar_fence_init();
     }
@@ -535,10 +549,10 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tma_q,   // qkv, box rows
     const uint32_t q_addr = smem_u32(smem + C::OFF_Q), do_addr = smem_u32(smem + C::OFF_DO);
 
     auto issue_sdp = [&](int j) {
+      // S/dP buffer (j & 1) was last used by tile j-2, whose dQ MMA has been issued already (the
+      // tensor pipe runs MMAs in issue order), after every elementwise warp had finished with it.
       const int buf = j & 1, st = j % C::NKV;
-      const uint32_t ph = (j >> 1) & 1;
       mbar_wait(&kv_full[st], (j / C::NKV) & 1, 41);
-      mbar_wait(&s_empty[buf], ph ^ 1, 42);
       tc_fence_after();
       if (lane == 0) {
         const uint32_t k_addr = smem_u32(smem + C::OFF_K + st * C::KV_BYTES);
@@ -568,13 +582,11 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tma_q,   // qkv, box rows
       mbar_wait(&ds_full[buf], (j >> 1) & 1, 44);
       tc_fence_after();
       if (lane == 0) {
-        const uint32_t ds_addr = smem_u32(smem + C::OFF_DS + buf * C::DS_BYTES);
         const uint32_t k_addr = smem_u32(smem + C::OFF_K + st * C::KV_BYTES);
 #pragma unroll
-        for (int kk = 0; kk < 4; ++kk)
-          umma_ss(tmem_base + C::TM_DQ, smem_desc_sw128(ds_addr + kk * 32, 0, 1024),
+        for (int kk = 0; kk < 4; ++kk)  // k-step kk = the 16 kv columns of elementwise part kk
+          umma_ts(tmem_base + C::TM_DQ, tmem_base + C::TM_DP + buf * 64 + kk * 16,
                   smem_desc_sw128(k_addr + kk * 2048, C::KV_SUB, 1024), idesc_dq, (j | kk) != 0);
-        umma_commit(&ds_empty[buf]);
         umma_commit(&kv_empty[st]);
         if (j == n_kv - 1) umma_commit(dq_full);
       }
@@ -603,9 +615,6 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tma_q,   // qkv, box rows
       tmem_ld_32x16(lane_base + C::TM_S + buf * 64 + part * 16, rs);
       tmem_ld_32x16(lane_base + C::TM_DP + buf * 64 + part * 16, rp);
       tmem_ld_wait();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&s_empty[buf]);
       const int kv0 = j * 64 + part * 16;
       if (drop) {
         // zero dP where the forward dropped P: AND the fp32 bits with an all-ones / all-zeros mask
@@ -631,13 +640,10 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tma_q,   // qkv, box rows
         }
         pk[i >> 1] = pack_bf16(p0 * (__uint_as_float(rp[i]) - delta_r), p1 * (__uint_as_float(rp[i + 1]) - delta_r));
       }
-      mbar_wait(&ds_empty[buf], ph ^ 1, 46);
-      const uint32_t ds_addr = smem_u32(smem + C::OFF_DS + buf * C::DS_BYTES);
-#pragma unroll
-      for (int g = 0; g < 2; ++g)
-        st_shared_v4(ds_addr + sw128_off(row_local, part * 2 + g), pk[g * 4 + 0], pk[g * 4 + 1], pk[g * 4 + 2],
-                     pk[g * 4 + 3]);
-      fence_async_smem();
+      // dS (bf16 pairs) goes back into the first 8 of this thread's own 16 dP columns
+      tmem_st_32x8(lane_base + C::TM_DP + buf * 64 + part * 16, pk);
+      tmem_st_wait();
+      tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&ds_full[buf]);
     }
@@ -660,20 +666,19 @@ struct DkvCfg {
   static constexpr int KV_BYTES = 128 * HD * 2;  // K / V tile (128 rows), persistent
   static constexpr int Q_BYTES = 64 * HD * 2;    // Q / dO tile (64 rows), 2-deep ring
   static constexpr int Q_SUB = 64 * 128;
-  static constexpr int PT_BYTES = 128 * 64 * 2;  // P^T / dS^T tile [128 kv x 64 q]
   // Q/dO ring depth: a slot is only released when the dV/dK MMAs that read it retire, so the ring
   // must be deep enough for the next loads to be in flight a few tiles ahead of their use
-  static constexpr int NQ = HD == 64 ? 4 : 2;
+  static constexpr int NQ = 4;
   static constexpr int OFF_K = 0;
   static constexpr int OFF_V = KV_BYTES;
   static constexpr int OFF_Q = 2 * KV_BYTES;
   static constexpr int OFF_DO = OFF_Q + NQ * Q_BYTES;
-  static constexpr int OFF_PT = OFF_DO + NQ * Q_BYTES;
-  static constexpr int OFF_DST = OFF_PT + 2 * PT_BYTES;
-  static constexpr int OFF_MASK = OFF_DST + 2 * PT_BYTES;  // [2][128 kv][2 words]: keep bits, 32 queries per word
+  static constexpr int OFF_MASK = OFF_DO + NQ * Q_BYTES;   // [2][128 kv][2 words]: keep bits, 32 queries per word
   static constexpr int OFF_STAT = OFF_MASK + 2 * 1024;     // [NQ][lse2 | delta'][64 queries] fp32
   static constexpr int OFF_BAR = OFF_STAT + NQ * 512;
   static constexpr int SMEM_BYTES = OFF_BAR + 256;
+  // TMEM: S^T[2] | dP^T[2] | dV | dK. P^T and dS^T (bf16) are written back over the S^T / dP^T
+  // columns they came from and feed the dV / dK MMAs as A operands straight from TMEM.
   static constexpr int TM_ST = 0, TM_DPT = 128, TM_DV = 256, TM_DK = 256 + HD;
   static constexpr int TMEM_COLS = 512;
 };
@@ -691,9 +696,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tma_kv,  // qkv, box row
   uint64_t* q_full = bars + 1;       // NQ (<= 4)
   uint64_t* q_empty = bars + 5;      // NQ
   uint64_t* st_full = bars + 9;      // 2
-  uint64_t* st_empty = bars + 11;    // 2
   uint64_t* pt_full = bars + 13;     // 2
-  uint64_t* pt_empty = bars + 15;    // 2
   uint64_t* acc_full = bars + 17;    // 1
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 18);
 
@@ -719,9 +722,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tma_kv,  // qkv, box row
       }
       for (int i = 0; i < 2; ++i) {
         mbar_init(&st_full[i], 1);
-        mbar_init(&st_empty[i], BWD_EW_WARPS);
         mbar_init(&pt_full[i], BWD_EW_WARPS);
-        mbar_init(&pt_empty[i], 1);
       }
       mbar_fence_init();
     }
@@ -763,10 +764,10 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tma_kv,  // qkv, box row
     const uint32_t k_addr = smem_u32(smem + C::OFF_K), v_addr = smem_u32(smem + C::OFF_V);
 
     auto issue_st = [&](int t) {
+      // S^T/dP^T buffer (t & 1) was last used by tile t-2, whose dV/dK MMAs have been issued already
+      // (the tensor pipe runs MMAs in issue order), after every elementwise warp had finished with it.
       const int buf = t & 1, st = t % C::NQ;
-      const uint32_t ph = (t >> 1) & 1;
       mbar_wait(&q_full[st], (t / C::NQ) & 1, 51);
-      mbar_wait(&st_empty[buf], ph ^ 1, 52);
       tc_fence_after();
       if (lane == 0) {
         const uint32_t q_addr = smem_u32(smem + C::OFF_Q + st * C::Q_BYTES);
@@ -796,19 +797,16 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tma_kv,  // qkv, box row
       mbar_wait(&pt_full[buf], (t >> 1) & 1, 54);
       tc_fence_after();
       if (lane == 0) {
-        const uint32_t pt_addr = smem_u32(smem + C::OFF_PT + buf * C::PT_BYTES);
-        const uint32_t dst_addr = smem_u32(smem + C::OFF_DST + buf * C::PT_BYTES);
         const uint32_t q_addr = smem_u32(smem + C::OFF_Q + st * C::Q_BYTES);
         const uint32_t do_addr = smem_u32(smem + C::OFF_DO + st * C::Q_BYTES);
 #pragma unroll
-        for (int kk = 0; kk < 4; ++kk)
-          umma_ss(tmem_base + C::TM_DV, smem_desc_sw128(pt_addr + kk * 32, 0, 1024),
+        for (int kk = 0; kk < 4; ++kk)  // k-step kk = the 16 query columns of elementwise part kk
+          umma_ts(tmem_base + C::TM_DV, tmem_base + C::TM_ST + buf * 64 + kk * 16,
                   smem_desc_sw128(do_addr + kk * 2048, C::Q_SUB, 1024), idesc_acc, (t | kk) != 0);
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)
-          umma_ss(tmem_base + C::TM_DK, smem_desc_sw128(dst_addr + kk * 32, 0, 1024),
+          umma_ts(tmem_base + C::TM_DK, tmem_base + C::TM_DPT + buf * 64 + kk * 16,
                   smem_desc_sw128(q_addr + kk * 2048, C::Q_SUB, 1024), idesc_acc, (t | kk) != 0);
-        umma_commit(&pt_empty[buf]);
         umma_commit(&q_empty[st]);
         if (t == n_q - 1) umma_commit(acc_full);
       }
@@ -827,6 +825,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tma_kv,  // qkv, box row
     // keep bits of the tile, transposed: maskT[buf][kv row][word] holds 32 consecutive query rows
     uint32_t* maskT = reinterpret_cast<uint32_t*>(smem + C::OFF_MASK);
 
+    FX_T0();
     for (int t = 0; t < n_q; ++t) {
       const int buf = t & 1;
       const uint32_t ph = (t >> 1) & 1;
@@ -855,17 +854,17 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tma_kv,  // qkv, box row
         }
         named_bar_sync(1, BWD_EW_WARPS * 32);
       }
+      FX_T(0);
       const int qst = t % C::NQ;
       mbar_wait(&q_full[qst], (t / C::NQ) & 1, 58);  // the bulk-copied row statistics of this tile have landed
       mbar_wait(&st_full[buf], ph, 55);  // S^T / dP^T are in TMEM
+      FX_T(1);
       tc_fence_after();
       uint32_t rs[16], rp[16];
       tmem_ld_32x16(lane_base + C::TM_ST + buf * 64 + part * 16, rs);
       tmem_ld_32x16(lane_base + C::TM_DPT + buf * 64 + part * 16, rp);
       tmem_ld_wait();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&st_empty[buf]);
+      FX_T(2);
 
       const int qh = q0 + part * 16;  // first query column of this thread's 16
       const bool diag = (t < 2);      // the first two 64-row query tiles straddle the diagonal
@@ -898,18 +897,15 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tma_kv,  // qkv, box row
           pk_ds[i >> 1] = pack_bf16(p0 * (__uint_as_float(d0) - dlv[u]), p1 * (__uint_as_float(d1) - dlv[u + 1]));
         }
       }
-      mbar_wait(&pt_empty[buf], ph ^ 1, 56);
-      const uint32_t pt_addr = smem_u32(smem + C::OFF_PT + buf * C::PT_BYTES);
-      const uint32_t dst_addr = smem_u32(smem + C::OFF_DST + buf * C::PT_BYTES);
-#pragma unroll
-      for (int g = 0; g < 2; ++g) {
-        const uint32_t off = sw128_off(r_local, part * 2 + g);
-        st_shared_v4(pt_addr + off, pk_p[g * 4 + 0], pk_p[g * 4 + 1], pk_p[g * 4 + 2], pk_p[g * 4 + 3]);
-        st_shared_v4(dst_addr + off, pk_ds[g * 4 + 0], pk_ds[g * 4 + 1], pk_ds[g * 4 + 2], pk_ds[g * 4 + 3]);
-      }
-      fence_async_smem();
+      FX_T(3);
+      // P^T and dS^T (bf16 pairs) go back into the first 8 of this thread's own 16 S^T / dP^T columns
+      tmem_st_32x8(lane_base + C::TM_ST + buf * 64 + part * 16, pk_p);
+      tmem_st_32x8(lane_base + C::TM_DPT + buf * 64 + part * 16, pk_ds);
+      tmem_st_wait();
+      tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&pt_full[buf]);
+      FX_T(5);
     }
 
     // dV = P_drop^T · dO, dK = scale * dS^T · Q; this warp drains columns [part*HD/4, +HD/4)
@@ -998,6 +994,16 @@ extern "C" int fx_attn_causal_fwd(void* stream, const void* qkv, void* out, floa
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   return hd == 64 ? attn::launch_fwd<64>(st, map, p) : attn::launch_fwd<128>(st, map, p);
 }
+
+#ifdef FX_TRACE
+extern "C" int fx_debug_trace(unsigned long long* host16, int reset) {
+  if (reset) {
+    unsigned long long z[16] = {0};
+    return cudaMemcpyToSymbol(fx::attn::g_trace, z, sizeof(z)) == cudaSuccess ? 0 : -2;
+  }
+  return cudaMemcpyFromSymbol(host16, fx::attn::g_trace, 16 * sizeof(unsigned long long)) == cudaSuccess ? 0 : -2;
+}
+#endif
 
 extern "C" size_t fx_attn_causal_bwd_workspace_bytes(int b, int s, int nh, int hd) {
   (void)hd;
