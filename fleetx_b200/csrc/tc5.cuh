@@ -166,6 +166,42 @@ __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t smem_addr, uint32_t
   return d;
 }
 
+// The MMA-issuing thread is a single thread running a dependent instruction stream at ~5 cycles
+// per instruction, so every instruction per tcgen05.mma counts (a 128x64x16 MMA is 32 cycles of
+// tensor work). The *_lo forms keep the descriptor's constant high word (SBO = 1024, version 1,
+// 128B swizzle) out of the loop: the caller precomputes desc_lo() once per operand buffer and adds
+// compile-time byte offsets >> 4 per k-step.
+constexpr uint32_t DESC_HI_SW128 = (1024u >> 4) | (1u << 14) | (2u << 29);
+__device__ __forceinline__ uint32_t desc_lo(uint32_t smem_addr, uint32_t lbo_bytes) {
+  return ((smem_addr & 0x3FFFFu) >> 4) | ((lbo_bytes >> 4) << 16);
+}
+// ACC: 0 = overwrite D, 1 = accumulate, 2 = take the runtime flag `acc_rt`
+template <int ACC>
+__device__ __forceinline__ void umma_ss_lo(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t idesc,
+                                           uint32_t acc_rt = 1) {
+  const uint32_t acc = ACC == 2 ? acc_rt : static_cast<uint32_t>(ACC);
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+      "mov.b64 da, {%1, %5};\n\t"
+      "mov.b64 db, {%2, %5};\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %3, p;\n\t}\n" ::"r"(tmem_d),
+      "r"(a_lo), "r"(b_lo), "r"(idesc), "r"(acc), "r"(DESC_HI_SW128)
+      : "memory");
+}
+template <int ACC>
+__device__ __forceinline__ void umma_ts_lo(uint32_t tmem_d, uint32_t tmem_a, uint32_t b_lo, uint32_t idesc,
+                                           uint32_t acc_rt = 1) {
+  const uint32_t acc = ACC == 2 ? acc_rt : static_cast<uint32_t>(ACC);
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t.reg .b64 db;\n\t"
+      "mov.b64 db, {%2, %5};\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], db, %3, p;\n\t}\n" ::"r"(tmem_d),
+      "r"(tmem_a), "r"(b_lo), "r"(idesc), "r"(acc), "r"(DESC_HI_SW128)
+      : "memory");
+}
+
 // Instruction descriptor for kind::f16, bf16 x bf16 -> fp32.
 //   [4,6) D fmt (1 = f32)  [7,10) A fmt (1 = bf16)  [10,13) B fmt  [15] A major  [16] B major
 //   [17,23) N >> 3   [24,29) M >> 4        major: 0 = K-major, 1 = MN-major

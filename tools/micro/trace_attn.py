@@ -28,3 +28,5 @@ for i, n in enumerate(names):
     print(f"{n:18s} {buf[i] / tiles:9.1f} cycles/tile")
     tot += buf[i] / tiles
 print("sum", tot)
+for i, n in ((12, "mma: loop/other"), (8, "mma: wait q_full"), (9, "mma: issue ST/DPT"), (10, "mma: wait pt_full"), (11, "mma: issue dV/dK")):
+    print(f"{n:18s} {buf[i] / tiles:9.1f} cycles/tile")
