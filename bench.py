@@ -178,7 +178,7 @@ def run_gpu(args):
     import torch.distributed as dist
 
     from fleetx_b200 import _lib, functional as Fn, ops
-    from fleetx_b200.dist import SingleGroup, TorchDistGroup, shard_columns, shard_rows
+    from fleetx_b200.dist import SingleGroup, SymmetricTPGroup, TorchDistGroup
     from fleetx_b200.layers import TransformerDecoderLayer
     from fleetx_b200.rng import get_rng_state_tracker, set_seed
 
@@ -194,9 +194,19 @@ def run_gpu(args):
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
-        group = TorchDistGroup()
+        collective = "fused allreduce kernel over NVSwitch peer memory (csrc/comm.cu)"
+        if args.collective == "nccl":
+            group = TorchDistGroup()
+            collective = "NCCL allreduce (torch.distributed)"
+        else:
+            try:
+                group = SymmetricTPGroup(max_elems=args.batch * SEQ * H)
+            except Exception as e:  # noqa: BLE001  (no multicast on this box: fall back to NCCL, and say so)
+                group = TorchDistGroup()
+                collective = f"NCCL allreduce (symmetric memory unavailable: {str(e)[:80]})"
     else:
         group = SingleGroup()
+        collective = "none (1 GPU)"
     n = world
     b, s = args.batch, SEQ
     T = b * s
@@ -316,7 +326,7 @@ def run_gpu(args):
             "metric": METRIC, "value": tokens_per_s, "unit": "tokens/s", "n_gpus": n, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": workload_config(args, n),
+            "config": dict(workload_config(args, n), collective=collective),
             "e2e": {"value": e2e_tokens_per_s, "unit": "tokens/s", "h2d_bytes_per_step": 2 * T * H * 2,
                     "d2h_bytes_per_step": T * H * 2, "steps": e2e_steps},
             "gpu_launches": int(launches),
@@ -343,6 +353,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--batch", type=int, default=8)
     ap.add_argument("--impl", default="fleetx_b200", choices=["fleetx_b200", "reference"])
+    ap.add_argument("--collective", default="fused", choices=["fused", "nccl"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--profile-mode", action="store_true",
                     help="device-timed steps only (no e2e / CPU legs): the command ncu wraps")

@@ -1,0 +1,270 @@
+// comm.cu — K7: the model-parallel allreduce of the row-parallel linears, as our own kernel over
+// NVLink 5 / NVSwitch peer memory, fused with the elementwise op that follows it.
+//
+// Reference semantics (fleet.meta_parallel.RowParallelLinear, call sites hybrid_model.py:157-163,
+// 505-511): y = allreduce_sum_mp(x_shard · W_shard), then + bias ONCE, then (in the decoder layer,
+// :546-547 / :556-561) dropout under the shared 'global_seed' stream and the residual add. The
+// backward of ColumnParallelLinear's `_c_identity` is the same allreduce on dX.
+//
+// The GEMM writes its partial result straight into a SYMMETRIC buffer (same virtual layout on every
+// rank, mapped into every peer and into one NVSwitch multicast address). One kernel then does
+//
+//   phase 0  flag handshake: every rank's partial is complete (stream order on each GPU)
+//   phase 1  reduce-scatter + all-gather through the switch: rank r owns rows [r·T/n, (r+1)·T/n);
+//            it reads them with multimem.ld_reduce (the switch sums the n replicas, fp32
+//            accumulation) and writes the sum back with multimem.st, which the switch replicates
+//            into every rank's copy of the buffer
+//   phase 2  counter barrier across all blocks of all ranks
+//   phase 3  epilogue: every rank reads the now complete sum from its own copy and applies
+//            out = residual + dropout(sum + bias)  (or just copies, for the backward allreduces)
+//            into an ordinary local tensor
+//   phase 4  counter barrier: nobody overwrites the symmetric buffer while a peer still reads it
+//
+// so each byte crosses NVLink once in each direction, and the bias/dropout/residual pass costs no
+// extra trip through HBM. Flags and counters are monotonic (epoch-stamped), never reset.
+#include <stdlib.h>
+
+#include "common.cuh"
+#include "philox.cuh"
+#include "tc5.cuh"
+
+namespace fx {
+namespace comm {
+
+using tc5::bf16_hi;
+using tc5::bf16_lo;
+using tc5::pack_bf16;
+
+constexpr int MAX_RANKS = 8;
+constexpr int THREADS = 512;
+// u32 slots inside each rank's signal pad (byte offset 4096 keeps clear of torch's own use)
+constexpr int SLOT_BASE = 1024;            // in u32 units
+constexpr int SLOT_READY = SLOT_BASE;      // [MAX_RANKS] epoch flag written by each source rank
+constexpr int SLOT_RS_DONE = SLOT_BASE + 16;
+constexpr int SLOT_AG_DONE = SLOT_BASE + 17;
+
+struct Params {
+  uint64_t sig[MAX_RANKS];   // signal pad of every rank, as mapped on this GPU
+  uint64_t buf[MAX_RANKS];   // symmetric buffer of every rank, as mapped on this GPU
+  uint64_t mc;               // multicast address of the symmetric buffer
+  int rank, world;
+  int rows, h;               // logical [rows, h] bf16
+  uint32_t epoch;            // 1, 2, 3, ... identical on all ranks for the same call
+  __nv_bfloat16* out;        // local result [rows, h]
+  // epilogue (null bias / residual => plain allreduce)
+  const __nv_bfloat16* bias;
+  const __nv_bfloat16* residual;
+  float p_drop, scale;
+  uint32_t thresh;
+  uint64_t seed, offset;
+  const uint8_t* mask_in;
+  int variant;               // 0: reduced slices are multicast to every rank (multimem.st), phase 3 reads locally
+                             // 1: reduced slices stay with their owner, phase 3 pulls them with peer loads
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void red_release_sys_add(uint32_t* p, uint32_t v) {
+  asm volatile("red.release.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// Wait until *p has reached `target` (wrap-safe). A peer that never arrives would hang the GPU, so
+// the spin carries a 5 s watchdog.
+__device__ __forceinline__ void spin_until(const uint32_t* p, uint32_t target, int tag) {
+  uint32_t spins = 0;
+  uint64_t t0 = 0;
+  while (static_cast<int32_t>(ld_acquire_sys(p) - target) < 0) {
+    if ((++spins & 1023u) == 0) {
+      const uint64_t now = tc5::global_ns();
+      if (t0 == 0) t0 = now;
+      if (now - t0 > 5000000000ull) {
+        printf("fleetx_b200: tp allreduce watchdog: block %d tag %d target %u have %u\n", blockIdx.x, tag, target,
+               ld_acquire_sys(p));
+        __trap();
+      }
+    }
+  }
+}
+__device__ __forceinline__ uint4 ld_relaxed_sys_v4(const uint4* ptr) {
+  uint4 v;
+  asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(ptr)
+               : "memory");
+  return v;
+}
+// plain (weak) 16-byte load that does not allocate in L1: the data was published by the barrier
+__device__ __forceinline__ uint4 ld_weak_v4(const uint4* ptr) {
+  uint4 v;
+  asm volatile("ld.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(ptr)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st_v4(uint64_t mc_addr, const uint4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc_addr), "r"(v.x), "r"(v.y),
+               "r"(v.z), "r"(v.w)
+               : "memory");
+}
+// 8 bf16 summed over all replicas by the switch, fp32 accumulation
+__device__ __forceinline__ uint4 multimem_ld_reduce_bf16x8(uint64_t mc_addr) {
+  uint4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(mc_addr)
+               : "memory");
+  return v;
+}
+
+__device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
+  f[0] = bf16_lo(u.x); f[1] = bf16_hi(u.x); f[2] = bf16_lo(u.y); f[3] = bf16_hi(u.y);
+  f[4] = bf16_lo(u.z); f[5] = bf16_hi(u.z); f[6] = bf16_lo(u.w); f[7] = bf16_hi(u.w);
+}
+__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
+  return make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+}
+
+__global__ void __launch_bounds__(THREADS)
+tp_allreduce_kernel(const Params p) {
+  const int tid = threadIdx.x;
+  uint32_t* my_sig = reinterpret_cast<uint32_t*>(p.sig[p.rank]);
+  const uint32_t nblk = gridDim.x;
+
+  // ---- phase 0: everyone's partial result is in place
+  if (blockIdx.x == 0 && tid < p.world)
+    st_release_sys(reinterpret_cast<uint32_t*>(p.sig[tid]) + SLOT_READY + p.rank, p.epoch);
+  if (tid < p.world) spin_until(my_sig + SLOT_READY + tid, p.epoch, 0);
+  __syncthreads();
+
+  // ---- phase 1: reduce-scatter my row slice through the switch, result into my own copy
+  const int hv = p.h >> 3;                                   // 16-byte vectors per row
+  const int rows_per = (p.rows + p.world - 1) / p.world;
+  const int r0 = p.rank * rows_per;
+  const int r1 = min(p.rows, r0 + rows_per);
+  const size_t v0 = static_cast<size_t>(r0) * hv, v1 = static_cast<size_t>(max(r1, r0)) * hv;
+  uint4* mine = reinterpret_cast<uint4*>(p.buf[p.rank]);
+  const size_t stride = static_cast<size_t>(nblk) * THREADS;
+  for (size_t v = v0 + static_cast<size_t>(blockIdx.x) * THREADS + tid; v < v1; v += 4 * stride) {
+    uint4 t[4];  // four switch reductions in flight per thread: NVLink round trips are microseconds
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (v + u * stride < v1) t[u] = multimem_ld_reduce_bf16x8(p.mc + (v + u * stride) * 16);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      if (v + u * stride >= v1) continue;
+      if (p.variant == 0) multimem_st_v4(p.mc + (v + u * stride) * 16, t[u]);  // the switch writes every replica
+      else mine[v + u * stride] = t[u];
+    }
+  }
+
+  // ---- phase 2: all blocks of all ranks have stored their reduced slices
+  __threadfence_system();
+  __syncthreads();
+  if (tid < p.world) red_release_sys_add(reinterpret_cast<uint32_t*>(p.sig[tid]) + SLOT_RS_DONE, 1u);
+  if (tid == 0) spin_until(my_sig + SLOT_RS_DONE, p.epoch * nblk * p.world, 1);
+  __syncthreads();
+
+  // ---- phase 3: epilogue over the complete sum; fused bias + dropout + residual.
+  // Plain allreduce with out = NULL (multicast variant): the sum is already in every rank's copy, so
+  // the symmetric buffer itself is the result and there is nothing to do here.
+  const size_t total = p.out == nullptr ? 0 : static_cast<size_t>(p.rows) * hv;
+  const size_t slice_v = static_cast<size_t>(rows_per) * hv;
+  for (size_t vb = static_cast<size_t>(blockIdx.x) * THREADS + tid; vb < total; vb += 4 * stride) {
+    uint4 raws[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const size_t v = vb + u * stride;
+      if (v < total)
+        raws[u] = p.variant == 0 ? ld_weak_v4(mine + v) : ld_weak_v4(reinterpret_cast<const uint4*>(p.buf[v / slice_v]) + v);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const size_t v = vb + u * stride;
+      if (v >= total) continue;
+      uint4 res = raws[u];
+      if (p.residual != nullptr) {
+        float y[8], r[8];
+        unpack8(raws[u], y);
+        unpack8(__ldg(reinterpret_cast<const uint4*>(p.residual) + v), r);
+        if (p.bias != nullptr) {
+          float b[8];
+          unpack8(__ldg(reinterpret_cast<const uint4*>(p.bias) + (v % hv)), b);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) y[j] += b[j];
+        }
+        float o[8];
+        if (p.mask_in != nullptr) {
+          const uint2 m = __ldg(reinterpret_cast<const uint2*>(p.mask_in) + v);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            o[j] = r[j] + (((m.x >> (8 * j)) & 0xFFu) ? y[j] * p.scale : 0.f);
+            o[4 + j] = r[4 + j] + (((m.y >> (8 * j)) & 0xFFu) ? y[4 + j] * p.scale : 0.f);
+          }
+        } else if (p.p_drop > 0.f) {
+          const Philox8 rnd = philox4x32_10(p.seed, p.offset, v);  // group index = vector index of [rows, h]
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] = r[j] + (philox_keep(rnd, j, p.thresh) ? y[j] * p.scale : 0.f);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] = r[j] + y[j];
+        }
+        res = pack8(o);
+      }
+      reinterpret_cast<uint4*>(p.out)[v] = res;
+    }
+  }
+
+  // ---- phase 4: every rank has finished reading every copy
+  __syncthreads();
+  if (tid < p.world) red_release_sys_add(reinterpret_cast<uint32_t*>(p.sig[tid]) + SLOT_AG_DONE, 1u);
+  if (blockIdx.x == 0 && tid == 0) spin_until(my_sig + SLOT_AG_DONE, p.epoch * nblk * p.world, 2);
+}
+
+}  // namespace comm
+}  // namespace fx
+
+extern "C" int fx_tp_allreduce_bdr(void* stream, const uint64_t* peer_bufs, const uint64_t* peer_signal_pads,
+                                   uint64_t multicast_ptr, int rank, int world, uint32_t epoch, int num_blocks,
+                                   void* out, int rows, int h, const void* bias, const void* residual, float p,
+                                   uint64_t seed, uint64_t offset, const uint8_t* mask_in) {
+  using namespace fx;
+  FX_CHECK_ARG(world >= 2 && world <= comm::MAX_RANKS && rank >= 0 && rank < world,
+               "fx_tp_allreduce_bdr: bad rank/world (%d/%d)", rank, world);
+  FX_CHECK_ARG(rows > 0 && h > 0 && h % 8 == 0, "fx_tp_allreduce_bdr: rows %d, h %d (h must be a multiple of 8)", rows, h);
+  FX_CHECK_ARG(peer_bufs && peer_signal_pads && multicast_ptr, "fx_tp_allreduce_bdr: null pointer");
+  FX_CHECK_ARG(out != nullptr || residual == nullptr, "fx_tp_allreduce_bdr: out may only be null for a plain allreduce");
+  FX_CHECK_ARG(p >= 0.f && p < 1.f, "fx_tp_allreduce_bdr: dropout p must be in [0,1) (got %f)", p);
+  FX_CHECK_ARG(epoch > 0, "fx_tp_allreduce_bdr: epoch must start at 1");
+  FX_CHECK_ARG(num_blocks > 0 && num_blocks <= num_sms(), "fx_tp_allreduce_bdr: num_blocks must be in [1, #SMs] "
+               "(all blocks of all ranks wait on each other, so they must be co-resident)");
+  FX_CHECK_ARG((bias == nullptr && mask_in == nullptr && p == 0.f) || residual != nullptr,
+               "fx_tp_allreduce_bdr: bias / dropout need a residual");
+  comm::Params q{};
+  for (int i = 0; i < world; ++i) {
+    q.sig[i] = peer_signal_pads[i];
+    q.buf[i] = peer_bufs[i];
+  }
+  q.mc = multicast_ptr;
+  q.rank = rank; q.world = world;
+  q.rows = rows; q.h = h;
+  q.epoch = epoch;
+  q.out = static_cast<__nv_bfloat16*>(out);
+  q.bias = static_cast<const __nv_bfloat16*>(bias);
+  q.residual = static_cast<const __nv_bfloat16*>(residual);
+  q.p_drop = p; q.scale = 1.0f / (1.0f - p);
+  q.thresh = dropout_threshold(p);
+  q.seed = seed; q.offset = offset;
+  q.mask_in = mask_in;
+  q.variant = 0;
+  if (const char* e = getenv("FX_COMM_VARIANT")) q.variant = atoi(e);  // tuning knob
+  FX_CHECK_ARG(out != nullptr || q.variant == 0, "fx_tp_allreduce_bdr: in-place result needs the multicast variant");
+  comm::tp_allreduce_kernel<<<num_blocks, comm::THREADS, 0, static_cast<cudaStream_t>(stream)>>>(q);
+  FX_LAUNCH_CHECK();
+  return FX_OK;
+}

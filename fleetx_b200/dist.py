@@ -19,7 +19,25 @@ from typing import Optional
 import torch
 
 
-class SingleGroup:
+class _GroupOps:
+    """What the layer needs from a model-parallel group beyond all_reduce_(): where a row-parallel
+    GEMM should write its partial result, and the allreduce fused with what follows it. The base
+    versions compose all_reduce_() with the library's elementwise kernels."""
+
+    def partial_buffer(self, rows: int, cols: int, device) -> torch.Tensor:
+        return torch.empty(rows, cols, dtype=torch.bfloat16, device=device)
+
+    def all_reduce(self, t: torch.Tensor) -> torch.Tensor:
+        return self.all_reduce_(t)
+
+    def all_reduce_bias_dropout_residual(self, y, bias, residual, p, seed, offset, mask_in=None):
+        from . import ops
+
+        self.all_reduce_(y)
+        return ops.bias_dropout_residual_fwd(y, bias, residual, p, seed, offset, mask_in=mask_in)
+
+
+class SingleGroup(_GroupOps):
     rank = 0
     nranks = 1
 
@@ -30,7 +48,7 @@ class SingleGroup:
         return None
 
 
-class TorchDistGroup:
+class TorchDistGroup(_GroupOps):
     """Wraps a torch.distributed process group (default: WORLD)."""
 
     def __init__(self, process_group=None):
@@ -50,6 +68,78 @@ class TorchDistGroup:
 
     def barrier(self):
         self._dist.barrier(group=self.pg)
+
+
+class SymmetricTPGroup(TorchDistGroup):
+    """Model-parallel group whose allreduces are this library's own kernel over NVLink/NVSwitch peer
+    memory (csrc/comm.cu: switch-side reduce-scatter with multimem.ld_reduce, peer-load all-gather,
+    bias + dropout + residual fused in). torch.distributed only does the plumbing: it allocates the
+    symmetric buffer, exchanges the mappings and gives us the raw peer / multicast / flag addresses.
+
+    One symmetric buffer of `max_elems` bf16 is reused by every allreduce of the layer: the GEMM
+    writes its partial result into it and the kernel leaves the reduced tensor in ordinary memory."""
+
+    def __init__(self, process_group=None, max_elems: int = 1 << 26, num_blocks: int = 148):
+        super().__init__(process_group)
+        import ctypes
+
+        import torch.distributed._symmetric_memory as symm_mem
+
+        from . import _lib
+
+        dev = torch.device("cuda", torch.cuda.current_device())
+        pg = self.pg if self.pg is not None else self._dist.group.WORLD
+        self._buf = symm_mem.empty(max_elems, dtype=torch.bfloat16, device=dev)
+        self._hdl = symm_mem.rendezvous(self._buf, pg.group_name)
+        if not self._hdl.multicast_ptr:
+            raise RuntimeError("NVSwitch multicast is not available for this group")
+        n = self.nranks
+        self._peer_bufs = (ctypes.c_uint64 * n)(*[int(p) for p in self._hdl.buffer_ptrs])
+        self._peer_sigs = (ctypes.c_uint64 * n)(*[int(p) for p in self._hdl.signal_pad_ptrs])
+        self._mc = int(self._hdl.multicast_ptr)
+        self._lib = _lib
+        self._epoch = 0
+        self.num_blocks = num_blocks
+        self.max_elems = max_elems
+        # the flag page must start at zero on every rank before the first call
+        pad = self._hdl.get_signal_pad(self.rank, (self._hdl.signal_pad_size // 4,), torch.int32)
+        pad.zero_()
+        torch.cuda.synchronize(dev)
+        self._dist.barrier(group=self.pg)
+
+    def partial_buffer(self, rows: int, cols: int, device) -> torch.Tensor:
+        if rows * cols > self.max_elems:
+            return super().partial_buffer(rows, cols, device)
+        return self._buf[: rows * cols].view(rows, cols)
+
+    def _is_symmetric(self, t: torch.Tensor) -> bool:
+        return t.data_ptr() == self._buf.data_ptr() and t.is_contiguous() and t.dtype == torch.bfloat16
+
+    def _launch(self, y, out, bias, residual, p, seed, offset, mask_in):
+        rows, h = y.shape[0], y.shape[1]
+        self._epoch += 1
+        lib = self._lib.lib()
+        self._lib.check(lib.fx_tp_allreduce_bdr(
+            torch.cuda.current_stream().cuda_stream, self._peer_bufs, self._peer_sigs, self._mc, self.rank, self.nranks,
+            self._epoch, self.num_blocks, None if out is None else out.data_ptr(), rows, h,
+            None if bias is None else bias.data_ptr(), None if residual is None else residual.data_ptr(),
+            float(p), int(seed), int(offset), None if mask_in is None else mask_in.data_ptr()), "fx_tp_allreduce_bdr")
+        return out
+
+    def all_reduce(self, t: torch.Tensor) -> torch.Tensor:
+        if not self._is_symmetric(t):
+            return self.all_reduce_(t)
+        # in place: the switch writes the sum into every rank's copy of the symmetric buffer, which the
+        # caller consumes before the next row-parallel GEMM of this rank overwrites it (stream order)
+        self._launch(t.view(-1, t.shape[-1]), None, None, None, 0.0, 0, 0, None)
+        return t
+
+    def all_reduce_bias_dropout_residual(self, y, bias, residual, p, seed, offset, mask_in=None):
+        if not self._is_symmetric(y):
+            return super().all_reduce_bias_dropout_residual(y, bias, residual, p, seed, offset, mask_in)
+        y2 = y.view(-1, y.shape[-1])
+        out = torch.empty_like(y2)
+        return self._launch(y2, out, bias, residual.view_as(y2), p, seed, offset, mask_in).view(y.shape)
 
 
 _DEFAULT_GROUP = None

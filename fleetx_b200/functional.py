@@ -77,9 +77,9 @@ def decoder_layer_fwd(x: torch.Tensor, P: LayerParams, M: LayerMeta, group):
     qkv = ops.gemm(attn_in, P.qkv_w, epilogue=FX_EPI_BIAS, bias=P.qkv_b)            # :166
     ctx, lse = ops.attn_causal_fwd(qkv.view(b, s, -1), M.nh_local, M.hd, scale, M.p_attn, *M.rng_attn)  # :167-173, :268-298
     ctx2 = ctx.view(T, -1)
-    attn_out = ops.gemm(ctx2, P.out_w)                                              # :340 local matmul
-    group.all_reduce_(attn_out)                                                     # _mp_allreduce
-    r1 = ops.bias_dropout_residual_fwd(attn_out, P.out_b, x2, M.p_hidden1, *M.rng_h1, mask_in=M.mask_h1)  # :546-547
+    attn_out = ops.gemm(ctx2, P.out_w, out=group.partial_buffer(T, h, x.device))    # :340 local matmul
+    # _mp_allreduce, + bias, dropout1 + residual (:546-547) — one fused kernel on a symmetric-memory group
+    r1 = group.all_reduce_bias_dropout_residual(attn_out, P.out_b, x2, M.p_hidden1, *M.rng_h1, mask_in=M.mask_h1)
     del attn_out
     if M.normalize_before:
         x1 = r1
@@ -91,9 +91,9 @@ def decoder_layer_fwd(x: torch.Tensor, P: LayerParams, M: LayerMeta, group):
         ffn_in = x1
     z = torch.empty(T, P.lin1_w.shape[1], dtype=torch.bfloat16, device=x.device)
     act = ops.gemm(ffn_in, P.lin1_w, epilogue=FX_EPI_BIAS_GELU, bias=P.lin1_b, aux=z)  # :558-559
-    y2 = ops.gemm(act, P.lin2_w)                                                    # :558 local matmul
-    group.all_reduce_(y2)                                                           # _mp_allreduce
-    r2 = ops.bias_dropout_residual_fwd(y2, P.lin2_b, x1, M.p_hidden2, *M.rng_h2, mask_in=M.mask_h2)  # :556-561
+    y2 = ops.gemm(act, P.lin2_w, out=group.partial_buffer(T, h, x.device))          # :558 local matmul
+    # _mp_allreduce, + bias, dropout2 + residual (:556-561)
+    r2 = group.all_reduce_bias_dropout_residual(y2, P.lin2_b, x1, M.p_hidden2, *M.rng_h2, mask_in=M.mask_h2)
     del y2
     if M.normalize_before:
         out = r2
@@ -126,9 +126,9 @@ def decoder_layer_bwd(dout: torch.Tensor, saved: dict, P: LayerParams, M: LayerM
     g["lin1_b"] = ops.colsum(d_z)
     ffn_in = saved["ln2"] if M.normalize_before else saved["x1"]
     g["lin1_w"] = ops.gemm(ffn_in, d_z, trans_a=True)
-    d_ffn_in = ops.gemm(d_z, P.lin1_w, trans_b=True)
+    d_ffn_in = ops.gemm(d_z, P.lin1_w, trans_b=True, out=group.partial_buffer(T, h, d.device))
     del d_z
-    group.all_reduce_(d_ffn_in)                                                     # backward of _c_identity
+    d_ffn_in = group.all_reduce(d_ffn_in)                                           # backward of _c_identity
     if M.normalize_before:
         # x1 feeds LN2 and the skip: d(x1) = LN2'(d_ffn_in) + d
         d_x1, g["norm2_w"], g["norm2_b"] = ops.layernorm_bwd(d_ffn_in, saved["x1"], P.norm2_w, saved["mean2"],
@@ -151,9 +151,9 @@ def decoder_layer_bwd(dout: torch.Tensor, saved: dict, P: LayerParams, M: LayerM
     g["qkv_b"] = ops.colsum(d_qkv)
     attn_in = saved["ln1"] if M.normalize_before else saved["x"]
     g["qkv_w"] = ops.gemm(attn_in, d_qkv, trans_a=True)
-    d_attn_in = ops.gemm(d_qkv, P.qkv_w, trans_b=True)
+    d_attn_in = ops.gemm(d_qkv, P.qkv_w, trans_b=True, out=group.partial_buffer(T, h, d.device))
     del d_qkv
-    group.all_reduce_(d_attn_in)                                                    # backward of _c_identity
+    d_attn_in = group.all_reduce(d_attn_in)                                         # backward of _c_identity
     if M.normalize_before:
         dx, g["norm1_w"], g["norm1_b"] = ops.layernorm_bwd(d_attn_in, saved["x"], P.norm1_w, saved["mean1"],
                                                            saved["rstd1"], dresidual=d_r1)

@@ -130,6 +130,26 @@ int fx_attn_causal_bwd(void* stream, const void* dout, const void* qkv, const vo
                        const float* lse, void* dqkv, void* workspace, int b, int s, int nh, int hd,
                        float scale, float p_drop, uint64_t seed, uint64_t offset);
 
+/* ---- model-parallel allreduce over NVLink/NVSwitch peer memory, fused with what follows it ------
+ * Replaces `_mp_allreduce` of fleet.meta_parallel.RowParallelLinear (call sites hybrid_model.py:
+ * 157-163, 505-511) together with the bias add and the dropout + residual of :546-547 / :556-561,
+ * and (with bias = residual = NULL, p = 0) the allreduce that is the backward of `_c_identity`
+ * in front of ColumnParallelLinear.
+ *
+ * The partial result of this rank (bf16 [rows,h]) must sit in a SYMMETRIC buffer: allocated by the
+ * host on every rank, mapped into every peer (peer_bufs[i] = rank i's copy as addressed from this
+ * GPU) and into one NVSwitch multicast address (multicast_ptr). peer_signal_pads[i] is rank i's
+ * zero-initialised flag page (>= 8 KiB), mapped likewise. All ranks call with the same rows, h,
+ * num_blocks and epoch; epoch counts the calls on this set of buffers: 1, 2, 3, ...
+ * out (ordinary local memory) = residual + dropout(sum + bias), or just the sum; with out = NULL
+ * (plain allreduce only) the sum is left in every rank's copy of the symmetric buffer.
+ * num_blocks <= #SMs: the blocks of all ranks wait on each other and must be co-resident. One
+ * process per GPU. */
+int fx_tp_allreduce_bdr(void* stream, const uint64_t* peer_bufs, const uint64_t* peer_signal_pads,
+                        uint64_t multicast_ptr, int rank, int world, uint32_t epoch, int num_blocks,
+                        void* out, int rows, int h, const void* bias, const void* residual, float p,
+                        uint64_t seed, uint64_t offset, const uint8_t* mask_in);
+
 #ifdef __cplusplus
 }
 #endif
