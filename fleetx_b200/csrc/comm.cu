@@ -60,6 +60,7 @@ struct Params {
   const uint8_t* mask_in;
   int variant;               // 0: reduced slices are multicast to every rank (multimem.st), phase 3 reads locally
                              // 1: reduced slices stay with their owner, phase 3 pulls them with peer loads
+                             // 2: one shot (2 ranks): phase 3 adds the peer copy to the local one; no phases 1-2
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -142,14 +143,15 @@ tp_allreduce_kernel(const Params p) {
   if (tid < p.world) spin_until(my_sig + SLOT_READY + tid, p.epoch, 0);
   __syncthreads();
 
-  // ---- phase 1: reduce-scatter my row slice through the switch, result into my own copy
   const int hv = p.h >> 3;                                   // 16-byte vectors per row
+  const size_t stride = static_cast<size_t>(gridDim.x) * THREADS;
+  if (p.variant != 2) {
+  // ---- phase 1: reduce-scatter my row slice through the switch, result into my own copy
   const int rows_per = (p.rows + p.world - 1) / p.world;
   const int r0 = p.rank * rows_per;
   const int r1 = min(p.rows, r0 + rows_per);
   const size_t v0 = static_cast<size_t>(r0) * hv, v1 = static_cast<size_t>(max(r1, r0)) * hv;
   uint4* mine = reinterpret_cast<uint4*>(p.buf[p.rank]);
-  const size_t stride = static_cast<size_t>(nblk) * THREADS;
   for (size_t v = v0 + static_cast<size_t>(blockIdx.x) * THREADS + tid; v < v1; v += 4 * stride) {
     uint4 t[4];  // four switch reductions in flight per thread: NVLink round trips are microseconds
 #pragma unroll
@@ -169,19 +171,34 @@ tp_allreduce_kernel(const Params p) {
   if (tid < p.world) red_release_sys_add(reinterpret_cast<uint32_t*>(p.sig[tid]) + SLOT_RS_DONE, 1u);
   if (tid == 0) spin_until(my_sig + SLOT_RS_DONE, p.epoch * nblk * p.world, 1);
   __syncthreads();
+  }
 
   // ---- phase 3: epilogue over the complete sum; fused bias + dropout + residual.
   // Plain allreduce with out = NULL (multicast variant): the sum is already in every rank's copy, so
   // the symmetric buffer itself is the result and there is nothing to do here.
   const size_t total = p.out == nullptr ? 0 : static_cast<size_t>(p.rows) * hv;
-  const size_t slice_v = static_cast<size_t>(rows_per) * hv;
+  const size_t slice_v = static_cast<size_t>((p.rows + p.world - 1) / p.world) * hv;
+  uint4* mine = reinterpret_cast<uint4*>(p.buf[p.rank]);
   for (size_t vb = static_cast<size_t>(blockIdx.x) * THREADS + tid; vb < total; vb += 4 * stride) {
     uint4 raws[4];
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       const size_t v = vb + u * stride;
-      if (v < total)
-        raws[u] = p.variant == 0 ? ld_weak_v4(mine + v) : ld_weak_v4(reinterpret_cast<const uint4*>(p.buf[v / slice_v]) + v);
+      if (v >= total) continue;
+      if (p.variant == 0) {
+        raws[u] = ld_weak_v4(mine + v);
+      } else if (p.variant == 1) {
+        raws[u] = ld_weak_v4(reinterpret_cast<const uint4*>(p.buf[v / slice_v]) + v);
+      } else {  // two ranks, one shot: local + peer, added in fp32
+        const uint4 a = ld_weak_v4(mine + v);
+        const uint4 b = ld_weak_v4(reinterpret_cast<const uint4*>(p.buf[p.rank ^ 1]) + v);
+        float fa[8], fb[8];
+        unpack8(a, fa);
+        unpack8(b, fb);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) fa[j] += fb[j];
+        raws[u] = pack8(fa);
+      }
     }
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
@@ -261,9 +278,11 @@ extern "C" int fx_tp_allreduce_bdr(void* stream, const uint64_t* peer_bufs, cons
   q.thresh = dropout_threshold(p);
   q.seed = seed; q.offset = offset;
   q.mask_in = mask_in;
-  q.variant = 0;
+  // two ranks: one-shot peer loads beat a trip through the switch; otherwise reduce + multicast in the switch
+  q.variant = (world == 2 && out != nullptr) ? 2 : 0;
   if (const char* e = getenv("FX_COMM_VARIANT")) q.variant = atoi(e);  // tuning knob
   FX_CHECK_ARG(out != nullptr || q.variant == 0, "fx_tp_allreduce_bdr: in-place result needs the multicast variant");
+  FX_CHECK_ARG(q.variant != 2 || world == 2, "fx_tp_allreduce_bdr: the one-shot variant is for 2 ranks");
   comm::tp_allreduce_kernel<<<num_blocks, comm::THREADS, 0, static_cast<cudaStream_t>(stream)>>>(q);
   FX_LAUNCH_CHECK();
   return FX_OK;

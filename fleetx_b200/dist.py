@@ -129,9 +129,12 @@ class SymmetricTPGroup(TorchDistGroup):
     def all_reduce(self, t: torch.Tensor) -> torch.Tensor:
         if not self._is_symmetric(t):
             return self.all_reduce_(t)
+        t2 = t.view(-1, t.shape[-1])
+        if self.nranks == 2:  # one-shot peer-load variant: the peer still reads my copy, so the sum goes elsewhere
+            return self._launch(t2, torch.empty_like(t2), None, None, 0.0, 0, 0, None).view(t.shape)
         # in place: the switch writes the sum into every rank's copy of the symmetric buffer, which the
         # caller consumes before the next row-parallel GEMM of this rank overwrites it (stream order)
-        self._launch(t.view(-1, t.shape[-1]), None, None, None, 0.0, 0, 0, None)
+        self._launch(t2, None, None, None, 0.0, 0, 0, None)
         return t
 
     def all_reduce_bias_dropout_residual(self, y, bias, residual, p, seed, offset, mask_in=None):
