@@ -53,10 +53,52 @@ struct FwdParams {
   float* lse;
   int b, s, nh;
   float scale, p_drop, inv_keep, log2_inv_keep;
-  uint32_t thresh2;         // threshold in both 16-bit lanes
-  uint32_t off_lo, off_hi;  // dropout call offset (Philox counter words 2, 3)
-  PhiloxKeys keys;          // round keys of the dropout seed
+  const uint32_t* mask;     // dropout keep bits [b, nh, s, wpr] (see attn_dropout_mask_kernel), or null
+  int wpr;                  // 32-bit mask words per query row = ceil(s / 128) * 4
 };
+
+// ---------------------------------------------------------------------------- dropout keep bits
+// The keep bits of attention dropout are drawn ONCE per layer call by this kernel and read by the
+// forward and both backward kernels (Philox inside those kernels cost more issue slots than the
+// softmax itself). Definition unchanged (philox.cuh): query row q, 8 consecutive kv per Philox call,
+// group index ((batch·nh + head)·s + q)·ceil(s/8) + kv/8.
+//
+// Layout: word w of row q covers kv in [32w, 32w+32). Element e = 4k + 2u + t of the word (k < 8,
+// u, t < 2) sits at bit 8·(2u + t) + 7 − k: after `word << k` the four elements 4k..4k+3 are the sign
+// bits of bytes 0..3, so one PRMT (sign-replicate mode) turns them into bf16x2 or fp32 AND-masks.
+struct MaskParams {
+  uint32_t* mask;
+  int b, s, nh, wpr;
+  uint32_t thresh2, off_lo, off_hi;
+  PhiloxKeys keys;
+};
+
+__global__ void __launch_bounds__(256)
+attn_dropout_mask_kernel(const MaskParams p) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int q = blockIdx.x * 32 + lane;
+  const int w = blockIdx.y * 8 + warp;                 // word index along kv
+  const int tile_end = (blockIdx.x * 32 / 128 + 1) * 128;  // causal: kv tiles beyond the diagonal tile are never read
+  if (w * 32 >= tile_end || w >= p.wpr || q >= p.s) return;
+  const uint64_t bh = blockIdx.z;
+  const uint64_t s8 = static_cast<uint64_t>((p.s + 7) / 8);
+  const uint64_t grp = (bh * p.s + q) * s8 + static_cast<uint64_t>(w) * 4;
+  uint32_t word = 0;
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    const Philox8 rnd = philox4x32_10_rk(p.keys, p.off_lo, p.off_hi, grp + c);
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {  // k = 2c + half: lanes[2·half] holds u = 0, lanes[2·half + 1] holds u = 1
+      const uint32_t f0 = keep_flags2(rnd.lanes[2 * half], p.thresh2);
+      const uint32_t f1 = keep_flags2(rnd.lanes[2 * half + 1], p.thresh2);
+      // bytes [f0.b1, f0.b3, f1.b1, f1.b3]: their sign bits are the keep flags of elements 4k .. 4k+3
+      const uint32_t t = prmt(f0, f1, 0x7531u) & 0x80808080u;
+      word |= t >> (2 * c + half);
+    }
+  }
+  p.mask[(bh * p.s + q) * p.wpr + w] = word;
+}
+
 
 template <int HD>
 struct FwdCfg {
@@ -222,8 +264,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FwdParams p) 
     const uint32_t p_addr = smem_u32(smem + C::OFF_P);
     const float sl2 = p.scale * LOG2E;
     const bool drop = p.p_drop > 0.f;
-    const uint64_t s8 = static_cast<uint64_t>((p.s + 7) / 8);
-    const uint64_t grp_row = (static_cast<uint64_t>(batch * p.nh + head) * p.s + row) * s8;
+    // this query row's dropout keep bits: 4 words per 128-wide kv tile
+    const uint4* mask_row = reinterpret_cast<const uint4*>(
+        p.mask + (static_cast<size_t>(batch * p.nh + head) * p.s + min(row, p.s - 1)) * p.wpr);
 
     float o[HD];
 #pragma unroll
@@ -250,11 +293,12 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FwdParams p) 
     // Dropout's 1/(1-p) is folded into the exponent (p' = 2^(s·sl2 - m·sl2 + log2 inv_keep)), so the
     // row sum below runs over p' too and is scaled back once at the end.
     const float log2_inv_keep = p.log2_inv_keep;
-    const uint32_t thresh2 = p.thresh2;
 
     for (int j = 0; j < n_kv; ++j) {
       const int sb = j % C::NS;
       const bool diag = (j == qt);  // only the diagonal tile needs the causal predicate
+      uint4 mw = make_uint4(0, 0, 0, 0);
+      if (drop) mw = __ldg(mask_row + j);  // issued before the wait: the load overlaps sweep 1
       mbar_wait(&s_full[sb], (j / C::NS) & 1, 31);
       tc_fence_after();
       // sweep 1: row maximum of the raw scores
@@ -297,12 +341,12 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FwdParams p) 
           pk[i >> 1] = pack_bf16(e0, e1);
         }
         if (drop) {
+          const uint32_t word = c == 0 ? mw.x : c == 1 ? mw.y : c == 2 ? mw.z : mw.w;
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            const Philox8 rnd = philox4x32_10_rk(p.keys, p.off_lo, p.off_hi, grp_row + static_cast<uint64_t>(j * 16 + c * 4 + g));
-#pragma unroll
-            for (int w = 0; w < 4; ++w)  // flags at bits 15 / 31 -> 0xFFFF lane masks for the bf16 pair
-              pk[g * 4 + w] &= prmt(keep_flags2(rnd.lanes[w], thresh2), 0u, 0xBB99u);
+          for (int k = 0; k < 8; ++k) {  // sign bits of bytes 0..3 of (word << k) = elements 4k .. 4k+3
+            const uint32_t x = word << k;
+            pk[2 * k] &= prmt(x, 0u, 0x9988u);
+            pk[2 * k + 1] &= prmt(x, 0u, 0xBBAAu);
           }
         }
         // columns [c*32, c*32+32) live in sub-tile c/2, 16-byte chunks (c&1)*4 .. +3
@@ -408,9 +452,8 @@ struct BwdParams {
   __nv_bfloat16* dqkv;  // [b, s, nh, 3, hd]
   int b, s, nh, s_pad;  // s_pad = s rounded up to 128
   float scale, p_drop, inv_keep;
-  uint32_t thresh2;
-  uint32_t off_lo, off_hi;
-  PhiloxKeys keys;
+  const uint32_t* mask;  // dropout keep bits [b, nh, s, wpr], or null
+  int wpr;
 };
 
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
@@ -626,8 +669,9 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tma_q,   // qkv, box rows
     const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16);
     const float sl2 = p.scale * LOG2E;
     const bool drop = p.p_drop > 0.f;
-    const uint64_t s8 = static_cast<uint64_t>((p.s + 7) / 8);
-    const uint64_t grp_row = (static_cast<uint64_t>(batch * p.nh + head) * p.s + row) * s8;
+    // keep bits of this query row; this thread's 16 kv columns are half of word 2j + part/2 of tile j
+    const uint32_t* mask_row = p.mask + (static_cast<size_t>(batch * p.nh + head) * p.s + min(row, p.s - 1)) * p.wpr + (part >> 1);
+    const int mshift = (part & 1) * 4;
     const size_t stat_idx = (static_cast<size_t>(batch) * p.nh + head) * p.s_pad + row;  // row < s_pad always
     const float neg_lse2 = -p.lse2[stat_idx];
     const float delta_r = p.delta[stat_idx];
@@ -637,6 +681,8 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tma_q,   // qkv, box rows
     auto tile = [&](int j, auto diag_c, auto drop_c) {
       constexpr bool DIAG = decltype(diag_c)::value, DROP = decltype(drop_c)::value;
       const int buf = j % C::NB;
+      uint32_t mword = 0;
+      if constexpr (DROP) mword = __ldg(mask_row + 2 * j);
       mbar_wait(&s_full[buf], (j / C::NB) & 1, 45);
       tc_fence_after();
       uint32_t rs[16], rp[16];
@@ -647,14 +693,12 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tma_q,   // qkv, box rows
       if constexpr (DROP) {
         // zero dP where the forward dropped P: AND the fp32 bits with an all-ones / all-zeros mask
 #pragma unroll
-        for (int g = 0; g < 2; ++g) {
-          const Philox8 rnd = philox4x32_10_rk(p.keys, p.off_lo, p.off_hi, grp_row + static_cast<uint64_t>((kv0 >> 3) + g));
-#pragma unroll
-          for (int w = 0; w < 4; ++w) {
-            const uint32_t f = keep_flags2(rnd.lanes[w], p.thresh2);
-            rp[g * 8 + 2 * w] &= prmt(f, 0u, 0x9999u);      // bit 15 replicated over the word
-            rp[g * 8 + 2 * w + 1] &= prmt(f, 0u, 0xBBBBu);  // bit 31
-          }
+        for (int k = 0; k < 4; ++k) {  // elements 4k .. 4k+3 of this thread's 16 = sign bits of (word << (mshift + k))
+          const uint32_t x = mword << (mshift + k);
+          rp[4 * k + 0] &= prmt(x, 0u, 0x8888u);
+          rp[4 * k + 1] &= prmt(x, 0u, 0x9999u);
+          rp[4 * k + 2] &= prmt(x, 0u, 0xAAAAu);
+          rp[4 * k + 3] &= prmt(x, 0u, 0xBBBBu);
         }
       }
       uint32_t pk[8];
@@ -712,8 +756,8 @@ struct DkvCfg {
   static constexpr int OFF_V = KV_BYTES;
   static constexpr int OFF_Q = 2 * KV_BYTES;
   static constexpr int OFF_DO = OFF_Q + NQ * Q_BYTES;
-  static constexpr int OFF_MASK = OFF_DO + NQ * Q_BYTES;   // [2][128 kv][2 words]: keep bits, 32 queries per word
-  static constexpr int OFF_STAT = OFF_MASK + 2 * 1024;     // [NQ][lse2 | delta'][64 queries] fp32
+  static constexpr int OFF_MASK = OFF_DO + NQ * Q_BYTES;   // [NQ][64 queries][4 words]: dropout keep bits of the tile
+  static constexpr int OFF_STAT = OFF_MASK + NQ * 1024;    // [NQ][lse2 | delta'][64 queries] fp32
   static constexpr int OFF_BAR = OFF_STAT + NQ * 512;
   static constexpr int SMEM_BYTES = OFF_BAR + 256;
   // TMEM: S^T[NB] | dP^T[NB] | dV | dK. P^T and dS^T (bf16) are written back over the S^T / dP^T
@@ -729,6 +773,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1)
 attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tma_kv,  // qkv, box rows 128
                     const __grid_constant__ CUtensorMap tma_q,   // qkv, box rows 64
                     const __grid_constant__ CUtensorMap tma_do,  // dout, box rows 64
+                    const __grid_constant__ CUtensorMap tma_mask,  // keep bits as u32 [b·nh·s, wpr], box 4 x 64
                     const BwdParams p) {
   using C = DkvCfg<HD>;
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -786,7 +831,11 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tma_kv,  // qkv, box row
       for (int t = 0; t < n_q; ++t) {
         const int st = t % C::NQ;
         mbar_wait(&q_empty[st], ((t / C::NQ) & 1) ^ 1, 50);
-        mbar_expect_tx(&q_full[st], 2 * C::Q_BYTES + 512);
+        const bool drop = p.p_drop > 0.f;
+        mbar_expect_tx(&q_full[st], 2 * C::Q_BYTES + 512 + (drop ? 1024 : 0));
+        if (drop)  // keep bits of query rows q0 .. q0+63 for this CTA's 128 kv columns (4 words per row)
+          tma_load_2d(smem + C::OFF_MASK + st * 1024, &tma_mask, &q_full[st], 4 * jt,
+                      (batch * p.nh + head) * p.s + (i0 + t) * 64);
         const size_t stat_off = (static_cast<size_t>(batch) * p.nh + head) * p.s_pad + (i0 + t) * 64;
         bulk_copy_g2s(smem + C::OFF_STAT + st * 512, p.lse2 + stat_off, 256, &q_full[st]);
         bulk_copy_g2s(smem + C::OFF_STAT + st * 512 + 256, p.delta + stat_off, 256, &q_full[st]);
@@ -866,46 +915,21 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tma_kv,  // qkv, box row
     const int quarter = warp & 3, part = warp >> 2;  // part: which 16 of the tile's 64 query columns
     const int r_local = quarter * 32 + lane;                // kv row inside the tile
     const int kv = jt * 128 + r_local;
-    const int ew = warp;                                     // 0..15 among the elementwise warps
     const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16);
     const float sl2 = p.scale * LOG2E;
     const bool drop = p.p_drop > 0.f;
-    const uint64_t s8 = static_cast<uint64_t>((p.s + 7) / 8);
-    const size_t bh = static_cast<size_t>(batch) * p.nh + head;
-    // keep bits of the tile, transposed: maskT[buf][kv row][word] holds 32 consecutive query rows
-    uint32_t* maskT = reinterpret_cast<uint32_t*>(smem + C::OFF_MASK);
+    // This kv row's position inside a keep-bit word (layout: attn_dropout_mask_kernel): word r/32 of the
+    // query's 4 words, element e = r % 32 at bit 8·(e & 3) + 7 − e/4; mask_sh moves that bit to bit 31.
+    const int mask_word = r_local >> 5;
+    const int mask_sh = 31 - (8 * (r_local & 3) + 7 - ((r_local & 31) >> 2));
 
     FX_T0();
     // One 128 x 64 tile: p' = 2^(s·sl2 − lse2), P^T = keep·p', dS^T = p'·(keep·dP^T − delta'). DIAG / DROP
     // are compile-time so that the common tile carries no predicate or select per element.
     auto tile = [&](int t, auto diag_c, auto drop_c) {
       constexpr bool DIAG = decltype(diag_c)::value, DROP = decltype(drop_c)::value;
-      const int buf = t % C::NB, mb = t & 1;
+      const int buf = t % C::NB;
       const int q0 = (i0 + t) * 64;
-      if constexpr (DROP) {
-        // The forward draws keep bits 8 at a time along kv for one query row. Here a thread owns a
-        // kv row, so the warps rebuild the 64 x 128 tile of bits together: lane = query row, one
-        // Philox call = 8 kv columns, and 8 ballots turn those into 32-query words per kv row.
-#pragma unroll
-        for (int k = 0; k < 2; ++k) {
-          const int qw = ew & 1;             // which 32-query word
-          const int g = (ew >> 1) + 8 * k;   // kv group of 8 inside the tile (0..15)
-          const Philox8 rnd = philox4x32_10_rk(p.keys, p.off_lo, p.off_hi,
-                                               (bh * p.s + static_cast<uint64_t>(q0 + qw * 32 + lane)) * s8 +
-                                                   static_cast<uint64_t>(jt * 16 + g));
-          uint32_t mine = 0;
-#pragma unroll
-          for (int w = 0; w < 4; ++w) {
-            const uint32_t f = keep_flags2(rnd.lanes[w], p.thresh2);
-            const uint32_t b_lo = __ballot_sync(0xffffffffu, (f >> 15) & 1u);
-            const uint32_t b_hi = __ballot_sync(0xffffffffu, f >> 31);
-            if (lane == 2 * w) mine = b_lo;
-            if (lane == 2 * w + 1) mine = b_hi;
-          }
-          if (lane < 8) maskT[(mb * 128 + g * 8 + lane) * 2 + qw] = mine;
-        }
-        named_bar_sync(1, BWD_EW_WARPS * 32);
-      }
       FX_T(0);
       const int qst = t % C::NQ;
       mbar_wait(&q_full[qst], (t / C::NQ) & 1, 58);  // the bulk-copied row statistics of this tile have landed
@@ -920,8 +944,9 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tma_kv,  // qkv, box row
 
       const int qh = q0 + part * 16;  // first query column of this thread's 16
       const float* stat = reinterpret_cast<const float*>(smem + C::OFF_STAT + qst * 512) + part * 16;
-      uint32_t mbits = 0;
-      if constexpr (DROP) mbits = maskT[(mb * 128 + r_local) * 2 + (part >> 1)] >> ((part & 1) * 16);
+      // keep bits of the tile as the producer's TMA left them: [64 queries][4 words]; all lanes of a warp
+      // share mask_word, so every read below is a broadcast
+      const uint32_t* mtile = reinterpret_cast<const uint32_t*>(smem + C::OFF_MASK + qst * 1024) + part * 16 * 4 + mask_word;
       uint32_t pk_p[8], pk_ds[8];
 #pragma unroll
       for (int i4 = 0; i4 < 16; i4 += 4) {
@@ -939,8 +964,8 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tma_kv,  // qkv, box row
           }
           uint32_t d0 = rp[i], d1 = rp[i + 1], pp = pack_bf16(p0, p1);
           if constexpr (DROP) {
-            const uint32_t m0 = static_cast<uint32_t>(static_cast<int32_t>(mbits << (31 - i)) >> 31);
-            const uint32_t m1 = static_cast<uint32_t>(static_cast<int32_t>(mbits << (30 - i)) >> 31);
+            const uint32_t m0 = static_cast<uint32_t>(static_cast<int32_t>(mtile[i * 4] << mask_sh) >> 31);
+            const uint32_t m1 = static_cast<uint32_t>(static_cast<int32_t>(mtile[(i + 1) * 4] << mask_sh) >> 31);
             d0 &= m0;
             d1 &= m1;
             pp &= prmt(m0, m1, 0x5410u);
@@ -1008,8 +1033,13 @@ static int launch_bwd(cudaStream_t st, const void* dout, const void* qkv, const 
     FX_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, DkvCfg<HD>::SMEM_BYTES));
     attr_set[dev] = true;
   }
-  CUtensorMap qkv128, qkv64, do128, do64;
+  CUtensorMap qkv128, qkv64, do128, do64, mmap;
   int rc;
+  if (p.p_drop > 0.f) {
+    if ((rc = make_tma_u32_2d(&mmap, p.mask, (uint64_t)p.wpr, (uint64_t)p.b * p.nh * p.s, (uint64_t)p.wpr * 4, 4, 64))) return rc;
+  } else {
+    mmap = CUtensorMap{};
+  }
   if ((rc = make_qkv_map_rows(&qkv128, qkv, p.b, p.s, p.nh, HD, 128))) return rc;
   if ((rc = make_qkv_map_rows(&qkv64, qkv, p.b, p.s, p.nh, HD, 64))) return rc;
   if ((rc = make_out_map_rows(&do128, dout, p.b, p.s, p.nh, HD, 128))) return rc;
@@ -1021,7 +1051,7 @@ static int launch_bwd(cudaStream_t st, const void* dout, const void* qkv, const 
       p.nh, HD, p.s_pad, p.p_drop > 0.f ? log2f(p.inv_keep) : 0.f, 1.0f - p.p_drop);
   FX_LAUNCH_CHECK();
   dim3 grid((p.s + 127) / 128, p.nh, p.b);
-  attn_bwd_dkv_kernel<HD><<<grid, BWD_THREADS, DkvCfg<HD>::SMEM_BYTES, st>>>(qkv128, qkv64, do64, p);
+  attn_bwd_dkv_kernel<HD><<<grid, BWD_THREADS, DkvCfg<HD>::SMEM_BYTES, st>>>(qkv128, qkv64, do64, mmap, p);
   FX_LAUNCH_CHECK();
   attn_bwd_dq_kernel<HD><<<grid, BWD_THREADS, DqCfg<HD>::SMEM_BYTES, st>>>(qkv128, qkv64, do128, p);
   FX_LAUNCH_CHECK();
@@ -1031,17 +1061,37 @@ static int launch_bwd(cudaStream_t st, const void* dout, const void* qkv, const 
 }  // namespace attn
 }  // namespace fx
 
-extern "C" int fx_attn_causal_fwd(void* stream, const void* qkv, void* out, float* lse, int b, int s,
-                                  int nh, int hd, float scale, float p_drop, uint64_t seed,
-                                  uint64_t offset) {
+extern "C" size_t fx_attn_dropout_mask_bytes(int b, int s, int nh) {
+  if (b <= 0 || s <= 0 || nh <= 0) return 0;
+  const size_t wpr = ((size_t)s + 127) / 128 * 4;
+  return (size_t)b * nh * s * wpr * sizeof(uint32_t);
+}
+
+extern "C" int fx_attn_causal_fwd(void* stream, const void* qkv, void* out, float* lse, void* dropout_mask, int b,
+                                  int s, int nh, int hd, float scale, float p_drop, uint64_t seed, uint64_t offset) {
   using namespace fx;
   FX_CHECK_ARG(b > 0 && s > 0 && nh > 0, "fx_attn_causal_fwd: empty input (b %d, s %d, nh %d)", b, s, nh);
   FX_CHECK_ARG(hd == 64 || hd == 128, "fx_attn_causal_fwd: head_dim must be 64 or 128 (got %d)", hd);
-  FX_CHECK_ARG(nh <= 65535 && b <= 65535, "fx_attn_causal_fwd: nh and b must be <= 65535");
+  FX_CHECK_ARG(nh <= 65535 && b * nh <= 65535, "fx_attn_causal_fwd: nh and b*nh must be <= 65535");
   FX_CHECK_ARG(p_drop >= 0.f && p_drop < 1.f, "fx_attn_causal_fwd: dropout p must be in [0,1) (got %f)", p_drop);
   FX_CHECK_ARG(scale > 0.f, "fx_attn_causal_fwd: scale must be positive");
   FX_CHECK_ARG(qkv && out && lse, "fx_attn_causal_fwd: null pointer");
-  FX_CHECK_ARG(((uintptr_t)qkv | (uintptr_t)out) % 16 == 0, "fx_attn_causal_fwd: pointers must be 16-byte aligned");
+  FX_CHECK_ARG(p_drop == 0.f || dropout_mask, "fx_attn_causal_fwd: dropout needs the keep-bit buffer (fx_attn_dropout_mask_bytes)");
+  FX_CHECK_ARG(((uintptr_t)qkv | (uintptr_t)out | (uintptr_t)dropout_mask) % 16 == 0,
+               "fx_attn_causal_fwd: pointers must be 16-byte aligned");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int wpr = (s + 127) / 128 * 4;
+  if (p_drop > 0.f) {
+    attn::MaskParams m{};
+    m.mask = static_cast<uint32_t*>(dropout_mask);
+    m.b = b; m.s = s; m.nh = nh; m.wpr = wpr;
+    m.thresh2 = dropout_threshold(p_drop) * 0x10001u;
+    m.off_lo = static_cast<uint32_t>(offset); m.off_hi = static_cast<uint32_t>(offset >> 32);
+    m.keys = philox_round_keys(seed);
+    dim3 grid((s + 31) / 32, (wpr + 7) / 8, b * nh);
+    attn::attn_dropout_mask_kernel<<<grid, 256, 0, st>>>(m);
+    FX_LAUNCH_CHECK();
+  }
   CUtensorMap map;
   int rc = attn::make_qkv_map(&map, qkv, b, s, nh, hd);
   if (rc) return rc;
@@ -1051,10 +1101,8 @@ extern "C" int fx_attn_causal_fwd(void* stream, const void* qkv, void* out, floa
   p.b = b; p.s = s; p.nh = nh;
   p.scale = scale; p.p_drop = p_drop; p.inv_keep = 1.0f / (1.0f - p_drop);
   p.log2_inv_keep = p_drop > 0.f ? log2f(p.inv_keep) : 0.f;
-  p.thresh2 = dropout_threshold(p_drop) * 0x10001u;
-  p.off_lo = static_cast<uint32_t>(offset); p.off_hi = static_cast<uint32_t>(offset >> 32);
-  p.keys = philox_round_keys(seed);
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  p.mask = static_cast<const uint32_t*>(dropout_mask);
+  p.wpr = wpr;
   return hd == 64 ? attn::launch_fwd<64>(st, map, p) : attn::launch_fwd<128>(st, map, p);
 }
 
@@ -1076,12 +1124,13 @@ extern "C" size_t fx_attn_causal_bwd_workspace_bytes(int b, int s, int nh, int h
 }
 
 extern "C" int fx_attn_causal_bwd(void* stream, const void* dout, const void* qkv, const void* out,
-                                  const float* lse, void* dqkv, void* workspace, int b, int s, int nh,
-                                  int hd, float scale, float p_drop, uint64_t seed, uint64_t offset) {
+                                  const float* lse, const void* dropout_mask, void* dqkv, void* workspace, int b,
+                                  int s, int nh, int hd, float scale, float p_drop) {
   using namespace fx;
   FX_CHECK_ARG(b > 0 && s > 0 && nh > 0, "fx_attn_causal_bwd: empty input (b %d, s %d, nh %d)", b, s, nh);
   FX_CHECK_ARG(hd == 64 || hd == 128, "fx_attn_causal_bwd: head_dim must be 64 or 128 (got %d)", hd);
   FX_CHECK_ARG(nh <= 65535 && b <= 65535, "fx_attn_causal_bwd: nh and b must be <= 65535");
+  FX_CHECK_ARG(p_drop == 0.f || dropout_mask, "fx_attn_causal_bwd: dropout needs the keep bits the forward call wrote");
   FX_CHECK_ARG(p_drop >= 0.f && p_drop < 1.f, "fx_attn_causal_bwd: dropout p must be in [0,1) (got %f)", p_drop);
   FX_CHECK_ARG(scale > 0.f, "fx_attn_causal_bwd: scale must be positive");
   FX_CHECK_ARG(dout && qkv && out && lse && dqkv && workspace, "fx_attn_causal_bwd: null pointer");
@@ -1096,9 +1145,8 @@ extern "C" int fx_attn_causal_bwd(void* stream, const void* dout, const void* qk
   p.dqkv = static_cast<__nv_bfloat16*>(dqkv);
   p.b = b; p.s = s; p.nh = nh;
   p.scale = scale; p.p_drop = p_drop; p.inv_keep = 1.0f / (1.0f - p_drop);
-  p.thresh2 = dropout_threshold(p_drop) * 0x10001u;
-  p.off_lo = static_cast<uint32_t>(offset); p.off_hi = static_cast<uint32_t>(offset >> 32);
-  p.keys = philox_round_keys(seed);
+  p.mask = static_cast<const uint32_t*>(dropout_mask);
+  p.wpr = (s + 127) / 128 * 4;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   return hd == 64 ? attn::launch_bwd<64>(st, dout, qkv, out, lse, p, lse2, delta)
                   : attn::launch_bwd<128>(st, dout, qkv, out, lse, p, lse2, delta);

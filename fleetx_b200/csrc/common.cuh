@@ -60,6 +60,10 @@ inline int make_tma_bf16_2d(CUtensorMap* map, const void* base, uint64_t inner, 
   return make_tma_bf16(map, base, 2, dims, strides, box);
 }
 
+// uint32 2-D map without swizzle (dropout bit masks)
+int make_tma_u32_2d(CUtensorMap* map, const void* base, uint64_t inner, uint64_t outer, uint64_t outer_stride_bytes,
+                    uint32_t box_inner, uint32_t box_outer);
+
 static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 
 }  // namespace fx

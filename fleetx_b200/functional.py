@@ -75,7 +75,7 @@ def decoder_layer_fwd(x: torch.Tensor, P: LayerParams, M: LayerMeta, group):
         ln1 = mean1 = rstd1 = None
         attn_in = x2
     qkv = ops.gemm(attn_in, P.qkv_w, epilogue=FX_EPI_BIAS, bias=P.qkv_b)            # :166
-    ctx, lse = ops.attn_causal_fwd(qkv.view(b, s, -1), M.nh_local, M.hd, scale, M.p_attn, *M.rng_attn)  # :167-173, :268-298
+    ctx, lse, attn_mask = ops.attn_causal_fwd(qkv.view(b, s, -1), M.nh_local, M.hd, scale, M.p_attn, *M.rng_attn)  # :167-173, :268-298
     ctx2 = ctx.view(T, -1)
     attn_out = ops.gemm(ctx2, P.out_w, out=group.partial_buffer(T, h, x.device))    # :340 local matmul
     # _mp_allreduce, + bias, dropout1 + residual (:546-547) — one fused kernel on a symmetric-memory group
@@ -100,7 +100,7 @@ def decoder_layer_fwd(x: torch.Tensor, P: LayerParams, M: LayerMeta, group):
         mean3 = rstd3 = None
     else:
         out, mean3, rstd3 = ops.layernorm_fwd(r2, P.norm2_w, P.norm2_b, M.eps)      # :564
-    saved = dict(x=x2, ln1=ln1, mean1=mean1, rstd1=rstd1, qkv=qkv, ctx=ctx2, lse=lse, r1=r1, x1=x1,
+    saved = dict(x=x2, ln1=ln1, mean1=mean1, rstd1=rstd1, qkv=qkv, ctx=ctx2, lse=lse, attn_mask=attn_mask, r1=r1, x1=x1,
                  ln2=ln2, mean2=mean2, rstd2=rstd2, z=z, act=act, r2=r2, mean3=mean3, rstd3=rstd3,
                  shape=(b, s, h))
     return out.view(b, s, h), saved
@@ -146,7 +146,7 @@ def decoder_layer_bwd(dout: torch.Tensor, saved: dict, P: LayerParams, M: LayerM
     d_ctx = ops.gemm(d_ao, P.out_w, trans_b=True)
     del d_ao
     d_qkv = ops.attn_causal_bwd(d_ctx.view(b, s, -1), saved["qkv"].view(b, s, -1), saved["ctx"].view(b, s, -1),
-                                saved["lse"], M.nh_local, M.hd, scale, M.p_attn, *M.rng_attn).view(T, -1)
+                                saved["lse"], saved["attn_mask"], M.nh_local, M.hd, scale, M.p_attn).view(T, -1)
     del d_ctx
     g["qkv_b"] = ops.colsum(d_qkv)
     attn_in = saved["ln1"] if M.normalize_before else saved["x"]
@@ -256,14 +256,15 @@ class CausalSelfAttentionFunction(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, qkv, nh_local, hd, p_drop, seed, offset):
-        out, lse = ops.attn_causal_fwd(qkv, nh_local, hd, hd ** -0.5, p_drop, seed, offset)
+        out, lse, mask = ops.attn_causal_fwd(qkv, nh_local, hd, hd ** -0.5, p_drop, seed, offset)
         ctx.save_for_backward(qkv, out, lse)
-        ctx.cfg = (nh_local, hd, p_drop, seed, offset)
+        ctx.mask = mask
+        ctx.cfg = (nh_local, hd, p_drop)
         return out
 
     @staticmethod
     def backward(ctx, dout):
         qkv, out, lse = ctx.saved_tensors
-        nh_local, hd, p_drop, seed, offset = ctx.cfg
-        dqkv = ops.attn_causal_bwd(dout.contiguous(), qkv, out, lse, nh_local, hd, hd ** -0.5, p_drop, seed, offset)
+        nh_local, hd, p_drop = ctx.cfg
+        dqkv = ops.attn_causal_bwd(dout.contiguous(), qkv, out, lse, ctx.mask, nh_local, hd, hd ** -0.5, p_drop)
         return dqkv, None, None, None, None, None

@@ -120,15 +120,18 @@ int fx_gemm_bf16(void* stream, int trans_a, int trans_b, int M, int N, int K, co
  * reshape/transpose/split at :167-173 reads it); out is bf16 [b, s, nh_local*hd], i.e. already
  * in the merged-head layout of :293-296. softmax(scale·QK^T + causal) is computed online, the
  * s×s matrix never reaches HBM; lse fp32 [b, nh_local, s] is saved for backward. Dropout on the
- * probabilities (:279-285, 'local_seed' stream) uses Philox keyed on (seed, offset, b, head,
- * row, col). hd is 64 or 128. */
-int fx_attn_causal_fwd(void* stream, const void* qkv, void* out, float* lse, int b, int s, int nh,
-                       int hd, float scale, float p_drop, uint64_t seed, uint64_t offset);
+ * probabilities (:279-285, 'local_seed' stream): keep bits are a pure function of (seed, offset,
+ * batch, head, row, col) (Philox4x32-10); the forward call draws them once into dropout_mask
+ * (fx_attn_dropout_mask_bytes bytes, 1 bit per (row, col); may be NULL when p_drop == 0) and the
+ * backward call reads the same buffer. hd is 64 or 128. */
+size_t fx_attn_dropout_mask_bytes(int b, int s, int nh);
+int fx_attn_causal_fwd(void* stream, const void* qkv, void* out, float* lse, void* dropout_mask, int b,
+                       int s, int nh, int hd, float scale, float p_drop, uint64_t seed, uint64_t offset);
 size_t fx_attn_causal_bwd_workspace_bytes(int b, int s, int nh, int hd);
-/* dqkv bf16, same packed layout as qkv, fully overwritten. */
+/* dqkv bf16, same packed layout as qkv, fully overwritten. dropout_mask: what the forward wrote. */
 int fx_attn_causal_bwd(void* stream, const void* dout, const void* qkv, const void* out,
-                       const float* lse, void* dqkv, void* workspace, int b, int s, int nh, int hd,
-                       float scale, float p_drop, uint64_t seed, uint64_t offset);
+                       const float* lse, const void* dropout_mask, void* dqkv, void* workspace, int b,
+                       int s, int nh, int hd, float scale, float p_drop);
 
 /* ---- model-parallel allreduce over NVLink/NVSwitch peer memory, fused with what follows it ------
  * Replaces `_mp_allreduce` of fleet.meta_parallel.RowParallelLinear (call sites hybrid_model.py:

@@ -46,7 +46,7 @@ def test_attn_fwd(b, s, nh, hd, p):
     seed, offset = 1147, 5
     keep = torch.from_numpy(OP.attn_dropout_mask(seed, offset, b, nh, s, p)) if p > 0 else None
     ref, _ = _oracle(qkv, nh, hd, p, keep)
-    out, lse = ops.attn_causal_fwd(qkv.cuda(), nh, hd, hd ** -0.5, p, seed, offset)
+    out, lse, amask = ops.attn_causal_fwd(qkv.cuda(), nh, hd, hd ** -0.5, p, seed, offset)
     torch.cuda.synchronize()
     assert rel_err(out, ref) < FWD_TOL
     # lse against the oracle's scores
@@ -62,10 +62,10 @@ def test_attn_causality():
 
     b, s, nh, hd = 1, 256, 2, 64
     qkv = _qkv(b, s, nh, hd, seed=3)
-    out1, _ = ops.attn_causal_fwd(qkv.cuda(), nh, hd, hd ** -0.5)
+    out1, _, _ = ops.attn_causal_fwd(qkv.cuda(), nh, hd, hd ** -0.5)
     qkv2 = qkv.clone()
     qkv2[:, 150:] = _qkv(b, s - 150, nh, hd, seed=4)
-    out2, _ = ops.attn_causal_fwd(qkv2.cuda(), nh, hd, hd ** -0.5)
+    out2, _, _ = ops.attn_causal_fwd(qkv2.cuda(), nh, hd, hd ** -0.5)
     assert torch.equal(out1[:, :150], out2[:, :150])
     assert not torch.equal(out1[:, 150:], out2[:, 150:])
 
@@ -81,8 +81,8 @@ def test_attn_bwd(b, s, nh, hd, p):
     keep = torch.from_numpy(OP.attn_dropout_mask(seed, offset, b, nh, s, p)) if p > 0 else None
     _, dref = _oracle(qkv, nh, hd, p, keep, dout)
     qd = qkv.cuda()
-    out, lse = ops.attn_causal_fwd(qd, nh, hd, hd ** -0.5, p, seed, offset)
-    dqkv = ops.attn_causal_bwd(dout.cuda(), qd, out, lse, nh, hd, hd ** -0.5, p, seed, offset)
+    out, lse, amask = ops.attn_causal_fwd(qd, nh, hd, hd ** -0.5, p, seed, offset)
+    dqkv = ops.attn_causal_bwd(dout.cuda(), qd, out, lse, amask, nh, hd, hd ** -0.5, p)
     torch.cuda.synchronize()
     d = dqkv.float().cpu().reshape(b, s, nh, 3, hd)
     r = dref.reshape(b, s, nh, 3, hd)

@@ -104,8 +104,8 @@ def main():
                 fl = 2.0 * b * nh * s * s * hd  # causal half of 4·b·nh·s²·hd
                 print(json.dumps({"op": "attn_fwd", "b": b, "s": s, "nh": nh, "hd": hd, "p": pd, "ms": round(med, 4),
                                   "tflops": round(fl / med / 1e9, 1)}), flush=True)
-                out, lse = ops.attn_causal_fwd(qkv, nh, hd, hd ** -0.5, pd, 1, 0)
-                med, _ = timeit(lambda: ops.attn_causal_bwd(out, qkv, out, lse, nh, hd, hd ** -0.5, pd, 1, 0), flush=flush, reps=2)
+                out, lse, amask = ops.attn_causal_fwd(qkv, nh, hd, hd ** -0.5, pd, 1, 0)
+                med, _ = timeit(lambda: ops.attn_causal_bwd(out, qkv, out, lse, amask, nh, hd, hd ** -0.5, pd), flush=flush, reps=2)
                 print(json.dumps({"op": "attn_bwd", "b": b, "s": s, "nh": nh, "hd": hd, "p": pd, "ms": round(med, 4),
                                   "tflops": round(2.5 * fl / med / 1e9, 1)}), flush=True)
             except Exception as e:  # noqa: BLE001

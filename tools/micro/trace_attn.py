@@ -12,12 +12,12 @@ lib.fx_debug_trace.argtypes = [ctypes.c_void_p, ctypes.c_int]
 p = float(sys.argv[1]) if len(sys.argv) > 1 else 0.0
 b, s, nh, hd = 8, 2048, 32, 64
 qkv = torch.randn(b, s, nh * 3 * hd, device="cuda").to(torch.bfloat16)
-out, lse = ops.attn_causal_fwd(qkv, nh, hd, hd ** -0.5, p, 1, 0)
+out, lse, amask = ops.attn_causal_fwd(qkv, nh, hd, hd ** -0.5, p, 1, 0)
 for _ in range(2):
-    ops.attn_causal_bwd(out, qkv, out, lse, nh, hd, hd ** -0.5, p, 1, 0)
+    ops.attn_causal_bwd(out, qkv, out, lse, amask, nh, hd, hd ** -0.5, p)
 torch.cuda.synchronize()
 lib.fx_debug_trace(None, 1)
-ops.attn_causal_bwd(out, qkv, out, lse, nh, hd, hd ** -0.5, p, 1, 0)
+ops.attn_causal_bwd(out, qkv, out, lse, amask, nh, hd, hd ** -0.5, p)
 torch.cuda.synchronize()
 buf = (ctypes.c_ulonglong * 16)()
 lib.fx_debug_trace(buf, 0)

@@ -9,7 +9,7 @@ hd = int(sys.argv[2]) if len(sys.argv) > 2 else 64
 b, s, nh = 2, 2048, 16
 qkv = torch.randn(b, s, nh * 3 * hd, device="cuda").to(torch.bfloat16)
 for _ in range(3):
-    out, lse = ops.attn_causal_fwd(qkv, nh, hd, hd ** -0.5, p, 1, 0)
-    dq = ops.attn_causal_bwd(out, qkv, out, lse, nh, hd, hd ** -0.5, p, 1, 0)
+    out, lse, amask = ops.attn_causal_fwd(qkv, nh, hd, hd ** -0.5, p, 1, 0)
+    dq = ops.attn_causal_bwd(out, qkv, out, lse, amask, nh, hd, hd ** -0.5, p)
 torch.cuda.synchronize()
 print("ok")
