@@ -137,9 +137,18 @@ class ClockSampler:
         self.p = None
         try:
             self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits",
-                                       "-lms", "100", "-i", str(index)], stdout=self.f, stderr=subprocess.DEVNULL)
+                                       "-lms", "20", "-i", str(index)], stdout=self.f, stderr=subprocess.DEVNULL)
         except Exception:  # noqa: BLE001
             self.p = None
+        self.marks = []
+
+    def mark(self):
+        """Remember how many samples exist now (start / end of the timed region)."""
+        try:
+            self.f.flush()
+            self.marks.append(sum(1 for _ in open(self.f.name)))
+        except Exception:  # noqa: BLE001
+            self.marks.append(0)
 
     def stop(self):
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
@@ -153,6 +162,11 @@ class ClockSampler:
         self.f.flush()
         rows = [r.strip().split(",") for r in open(self.f.name).read().strip().splitlines() if r.strip()]
         os.unlink(self.f.name)
+        window = "warm-up + timed region"
+        if len(self.marks) == 2 and self.marks[1] - self.marks[0] >= 3:
+            rows = rows[self.marks[0]:self.marks[1]]
+            window = "timed region"
+        out["window"] = window
         sm, smax, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for r in rows:
@@ -166,7 +180,7 @@ class ClockSampler:
                     reasons.add(name)
         if sm:
             sm.sort()
-            out["sm_mhz"] = sm[len(sm) // 2]  # median over the timed region
+            out["sm_mhz"] = sm[len(sm) // 2]  # median over the window named in "window"
             out["sm_max_mhz"] = max(smax)
             out["samples"] = len(sm)
         out["reasons"] = sorted(reasons)
@@ -243,12 +257,25 @@ def run_gpu(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    # nvidia-smi takes a moment to start: launch it before the warm-up so it is sampling (every 20 ms)
+    # by the time the timed region begins
+    sampler = ClockSampler(local) if rank == 0 else None
     for _ in range(max(args.warmup, 3)):
+        step_device()
+    barrier()
+    if sampler is not None:
+        # wait (host only: the other ranks sit in the barrier below) until the sampler prints its first line
+        t_wait = time.time()
+        while time.time() - t_wait < 3.0 and os.path.getsize(sampler.f.name) == 0:
+            time.sleep(0.02)
+    barrier()
+    for _ in range(3):  # bring clocks back up after the wait; still warm-up
         step_device()
     barrier()
 
     # ---- timed region: K steps, CUDA events per step on the launching stream, L2 flushed between steps
-    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler is not None:
+        sampler.mark()
     ops.profile_gemm(True)
     launches0 = _lib.launch_count()
     evs = []
@@ -263,6 +290,8 @@ def run_gpu(args):
     barrier()
     launches = _lib.launch_count() - launches0
     gemm_records = ops.profile_gemm(False)
+    if sampler is not None:
+        sampler.mark()
     clocks = sampler.stop() if sampler else None
     total_ms = sum(a.elapsed_time(c) for a, c in evs)
     t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
