@@ -9,11 +9,12 @@
 // are cut out of it by ONE 4-D TMA tensor map (dims hd | 3·nh | s | b), so the head split costs
 // no copy; out / dout are [b, s, nh·hd] (heads merged), dqkv has the qkv layout again.
 //
-// Forward (one CTA = 128 query rows of one head; 192 threads):
-//   warp 4     TMA: Q once, then K_j / V_j through a 2-deep ring
-//   warp 5     MMA: S_j = Q·K_j^T (128x128, K = hd) and PV_j = P_j·V_j (128 x hd, K = 128) into
+// Forward (one CTA = 128 query rows of one head; 320 threads):
+//   warp 8     TMA: Q once, then K_j / V_j through a 2-deep ring
+//   warp 9     MMA: S_j = Q·K_j^T (128x128, K = hd) and PV_j = P_j·V_j (128 x hd, K = 128) into
 //              TMEM; V is consumed as an MN-major operand straight from the same TMA box
-//   warps 0-3  softmax: one query row per thread; two sweeps over S in TMEM (max, then exp2),
+//   warps 0-7  softmax: two threads per query row (64 kv columns each; the row maximum is exchanged
+//              through shared memory); two sweeps over S in TMEM (max, then exp2),
 //              P_j (with dropout folded in) goes back to shared memory as bf16 in the
 //              128B-swizzled K-major layout the PV MMA reads; O is kept in registers and updated
 //              as O = alpha·O + PV_j one step behind, so the tensor core always has work queued
@@ -33,10 +34,11 @@ namespace attn {
 
 using namespace tc5;
 
-constexpr int NUM_THREADS = 192;
+constexpr int FWD_SM_WARPS = 8;  // softmax warps: two per TMEM lane quarter, 64 of a tile's 128 kv columns each
+constexpr int NUM_THREADS = 64 + FWD_SM_WARPS * 32;
 // Warp roles. The single-thread TMA / MMA issuers sit in the HIGHEST warp ids: the SM's warp arbiter
 // favours higher ids, and an MMA issuer starved of issue slots by the math warps stalls the tensor pipe.
-constexpr int FWD_TMA_WARP = 4, FWD_MMA_WARP = 5;  // warps 0..3: softmax, one TMEM lane quarter each
+constexpr int FWD_TMA_WARP = FWD_SM_WARPS, FWD_MMA_WARP = FWD_SM_WARPS + 1;  // warps 0..7: softmax
 constexpr float LOG2E = 1.4426950408889634f;
 
 // byte offset of 16-byte chunk `c16` of row `r` inside a [rows x 64 bf16] 128B-swizzled tile
@@ -44,6 +46,9 @@ __device__ __forceinline__ uint32_t sw128_off(int r, int c16) {
   return static_cast<uint32_t>(r * 128 + ((c16 ^ (r & 7)) << 4));
 }
 
+__device__ __forceinline__ void named_bar_sync_fwd(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
 __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
@@ -110,8 +115,10 @@ struct FwdCfg {
   static constexpr int OFF_K = TILE_BYTES;
   static constexpr int OFF_V = 3 * TILE_BYTES;
   static constexpr int OFF_P = 5 * TILE_BYTES;
-  static constexpr int OFF_BAR = OFF_P + P_BYTES;
-  static constexpr int SMEM_BYTES = OFF_BAR + 256;
+  static constexpr int OFF_BAR = OFF_P + P_BYTES;   // 19 mbarriers + TMEM slot: 160 bytes
+  static constexpr int OFF_XCH = OFF_BAR + 160;     // [2 halves][128 rows] bf16: row-max exchange between the
+                                                    // two threads of a row (bf16 keeps 2 CTAs/SM within smem)
+  static constexpr int SMEM_BYTES = OFF_XCH + 512;
   static constexpr int TMEM_PV = NS * 128;         // column of the first PV accumulator
   static constexpr int TMEM_COLS = HD == 64 ? 256 : 512;
   static constexpr int MIN_CTAS = HD == 64 ? 2 : 1;
@@ -158,11 +165,11 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FwdParams p) 
         mbar_init(&v_full[i], 1);
         mbar_init(&v_empty[i], 1);
         mbar_init(&s_full[i], 1);
-        mbar_init(&s_empty[i], 4);
+        mbar_init(&s_empty[i], FWD_SM_WARPS);
         mbar_init(&pv_full[i], 1);
-        mbar_init(&pv_empty[i], 4);
+        mbar_init(&pv_empty[i], FWD_SM_WARPS);
       }
-      mbar_init(p_full, 4);
+      mbar_init(p_full, FWD_SM_WARPS);
       mbar_init(p_empty, 1);
       mbar_fence_init();
     }
@@ -257,20 +264,24 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FwdParams p) 
     }
   } else {
     // ------------------------------------------------------------------ softmax / output
-    const int quarter = warp & 3;
+    // Thread pair (warp w, warp w+4; same lane) shares a query row: each takes 64 of the tile's 128 kv
+    // columns and half of the row's output columns.
+    const int quarter = warp & 3, half = warp >> 2;
     const int row_local = quarter * 32 + lane;
     const int row = qt * 128 + row_local;
     const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16);
-    const uint32_t p_addr = smem_u32(smem + C::OFF_P);
+    const uint32_t p_addr = smem_u32(smem + C::OFF_P) + half * C::SUB_BYTES;  // sub-tile `half` = my 64 columns
     const float sl2 = p.scale * LOG2E;
     const bool drop = p.p_drop > 0.f;
-    // this query row's dropout keep bits: 4 words per 128-wide kv tile
-    const uint4* mask_row = reinterpret_cast<const uint4*>(
-        p.mask + (static_cast<size_t>(batch * p.nh + head) * p.s + min(row, p.s - 1)) * p.wpr);
+    // this query row's dropout keep bits: 4 words per 128-wide kv tile, two of them mine
+    const uint2* mask_row = reinterpret_cast<const uint2*>(
+        p.mask + (static_cast<size_t>(batch * p.nh + head) * p.s + min(row, p.s - 1)) * p.wpr) + half;
+    __nv_bfloat16* xch = reinterpret_cast<__nv_bfloat16*>(smem + C::OFF_XCH);
+    constexpr int OC = HD / 2;  // output columns per thread
 
-    float o[HD];
+    float o[OC];
 #pragma unroll
-    for (int i = 0; i < HD; ++i) o[i] = 0.f;
+    for (int i = 0; i < OC; ++i) o[i] = 0.f;
     float m = -INFINITY, l = 0.f, alpha_prev = 0.f;
 
     auto o_update = [&](int j, float alpha) {
@@ -278,9 +289,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FwdParams p) 
       mbar_wait(&pv_full[buf], (j >> 1) & 1, 30);
       tc_fence_after();
 #pragma unroll
-      for (int c = 0; c < HD / 32; ++c) {
+      for (int c = 0; c < OC / 32; ++c) {
         uint32_t r[32];
-        tmem_ld_32x32(lane_base + C::TMEM_PV + buf * HD + c * 32, r);
+        tmem_ld_32x32(lane_base + C::TMEM_PV + buf * HD + half * OC + c * 32, r);
         tmem_ld_wait();
 #pragma unroll
         for (int i = 0; i < 32; ++i) o[c * 32 + i] = o[c * 32 + i] * alpha + __uint_as_float(r[i]);
@@ -297,26 +308,34 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FwdParams p) 
     for (int j = 0; j < n_kv; ++j) {
       const int sb = j % C::NS;
       const bool diag = (j == qt);  // only the diagonal tile needs the causal predicate
-      uint4 mw = make_uint4(0, 0, 0, 0);
-      if (drop) mw = __ldg(mask_row + j);  // issued before the wait: the load overlaps sweep 1
+      uint2 mw = make_uint2(0, 0);
+      if (drop) mw = __ldg(mask_row + 2 * j);  // issued before the wait: the load overlaps sweep 1
       mbar_wait(&s_full[sb], (j / C::NS) & 1, 31);
       tc_fence_after();
-      // sweep 1: row maximum of the raw scores
+      // sweep 1: maximum of my 64 raw scores
       float mx = -INFINITY;
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
+      for (int c = 0; c < 2; ++c) {
         uint32_t r[32];
-        tmem_ld_32x32(lane_base + sb * 128 + c * 32, r);
+        tmem_ld_32x32(lane_base + sb * 128 + half * 64 + c * 32, r);
         tmem_ld_wait();
         if (diag) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, (c * 32 + i > row_local) ? -INFINITY : __uint_as_float(r[i]));
+          for (int i = 0; i < 32; ++i)
+            mx = fmaxf(mx, (half * 64 + c * 32 + i > row_local) ? -INFINITY : __uint_as_float(r[i]));
         } else {
 #pragma unroll
           for (int i = 0; i < 32; i += 2) mx = fmaxf(mx, fmaxf(__uint_as_float(r[i]), __uint_as_float(r[i + 1])));
         }
       }
-      const float m_new = fmaxf(m, mx);
+      // Both threads of the row must scale with the SAME maximum. Each publishes its own, rounded UP to
+      // bf16 (any bound >= the true maximum is a valid stabiliser), and both take the max of the two.
+      const __nv_bfloat16 mine_up = __float2bfloat16_ru(mx);
+      xch[half * 128 + row_local] = mine_up;
+      named_bar_sync_fwd(1 + quarter, 64);
+      const float other = __bfloat162float(xch[(half ^ 1) * 128 + row_local]);
+      named_bar_sync_fwd(1 + quarter, 64);  // partner has read before the next tile overwrites
+      const float m_new = fmaxf(m, fmaxf(__bfloat162float(mine_up), other));
       const float alpha = ex2_approx((m - m_new) * sl2);
       const float neg_m = log2_inv_keep - m_new * sl2;
       // P buffer must have been consumed by PV_{j-1}
@@ -324,9 +343,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FwdParams p) 
       // sweep 2: probabilities -> bf16 P tile (dropout folded in), row sum of the undropped p'
       float rowsum = 0.f;
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
+      for (int c = 0; c < 2; ++c) {
         uint32_t r[32];
-        tmem_ld_32x32(lane_base + sb * 128 + c * 32, r);
+        tmem_ld_32x32(lane_base + sb * 128 + half * 64 + c * 32, r);
         tmem_ld_wait();
         uint32_t pk[16];
 #pragma unroll
@@ -334,14 +353,14 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FwdParams p) 
           float e0 = ex2_approx(fmaf(__uint_as_float(r[i]), sl2, neg_m));
           float e1 = ex2_approx(fmaf(__uint_as_float(r[i + 1]), sl2, neg_m));
           if (diag) {
-            e0 = (c * 32 + i > row_local) ? 0.f : e0;
-            e1 = (c * 32 + i + 1 > row_local) ? 0.f : e1;
+            e0 = (half * 64 + c * 32 + i > row_local) ? 0.f : e0;
+            e1 = (half * 64 + c * 32 + i + 1 > row_local) ? 0.f : e1;
           }
           rowsum += e0 + e1;
           pk[i >> 1] = pack_bf16(e0, e1);
         }
         if (drop) {
-          const uint32_t word = c == 0 ? mw.x : c == 1 ? mw.y : c == 2 ? mw.z : mw.w;
+          const uint32_t word = c == 0 ? mw.x : mw.y;
 #pragma unroll
           for (int k = 0; k < 8; ++k) {  // sign bits of bytes 0..3 of (word << k) = elements 4k .. 4k+3
             const uint32_t x = word << k;
@@ -349,12 +368,11 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FwdParams p) 
             pk[2 * k + 1] &= prmt(x, 0u, 0xBBAAu);
           }
         }
-        // columns [c*32, c*32+32) live in sub-tile c/2, 16-byte chunks (c&1)*4 .. +3
+        // my columns [c*32, c*32+32) of sub-tile `half`: 16-byte chunks c*4 .. c*4+3
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          const uint32_t addr = p_addr + (c >> 1) * C::SUB_BYTES + sw128_off(row_local, (c & 1) * 4 + g);
-          st_shared_v4(addr, pk[g * 4 + 0], pk[g * 4 + 1], pk[g * 4 + 2], pk[g * 4 + 3]);
-        }
+        for (int g = 0; g < 4; ++g)
+          st_shared_v4(p_addr + sw128_off(row_local, c * 4 + g), pk[g * 4 + 0], pk[g * 4 + 1], pk[g * 4 + 2],
+                       pk[g * 4 + 3]);
       }
       tc_fence_before();
       fence_async_smem();
@@ -370,16 +388,25 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FwdParams p) 
     }
     o_update(n_kv - 1, alpha_prev);
 
+    // the two partial row sums share every rescale, so they simply add; exchange them in fp32 through
+    // the P tile, which nothing reads any more (PV of the last tile has completed: o_update waited)
+    float* lx = reinterpret_cast<float*>(smem + C::OFF_P);
+    lx[half * 128 + row_local] = l;
+    named_bar_sync_fwd(1 + quarter, 64);
+    l += lx[(half ^ 1) * 128 + row_local];
+
     if (row < p.s) {
       const float inv_l = p.inv_keep / l;  // l sums p' = p * inv_keep
-      uint4* op = reinterpret_cast<uint4*>(p.out + (static_cast<size_t>(batch) * p.s + row) * (p.nh * HD) + head * HD);
+      uint4* op = reinterpret_cast<uint4*>(p.out + (static_cast<size_t>(batch) * p.s + row) * (p.nh * HD) + head * HD +
+                                           half * OC);
 #pragma unroll
-      for (int g = 0; g < HD / 8; ++g)
+      for (int g = 0; g < OC / 8; ++g)
         op[g] = make_uint4(pack_bf16(o[g * 8 + 0] * inv_l, o[g * 8 + 1] * inv_l),
                            pack_bf16(o[g * 8 + 2] * inv_l, o[g * 8 + 3] * inv_l),
                            pack_bf16(o[g * 8 + 4] * inv_l, o[g * 8 + 5] * inv_l),
                            pack_bf16(o[g * 8 + 6] * inv_l, o[g * 8 + 7] * inv_l));
-      p.lse[(static_cast<size_t>(batch) * p.nh + head) * p.s + row] = m * p.scale + __logf(l) - __logf(p.inv_keep);
+      if (half == 0)
+        p.lse[(static_cast<size_t>(batch) * p.nh + head) * p.s + row] = m * p.scale + __logf(l) - __logf(p.inv_keep);
     }
   }
 

@@ -101,6 +101,16 @@ __device__ __forceinline__ void epilogue_block(const Params& p, const float* stg
     const uint2 b = __ldg(reinterpret_cast<const uint2*>(p.bias + col));
     bias[0] = bf16_lo(b.x); bias[1] = bf16_hi(b.x); bias[2] = bf16_lo(b.y); bias[3] = bf16_hi(b.y);
   }
+  // Loads the epilogue depends on (saved pre-activation for GELU', old C for accumulate) are all
+  // issued up front: one exposed HBM round trip per 32x32 block instead of one per row group.
+  uint2 zpre[8];
+  if (p.epi == FX_EPI_DGELU) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int row = row0 + i * 4 + (lane >> 3);
+      zpre[i] = row < p.M ? __ldg(reinterpret_cast<const uint2*>(p.aux + (size_t)row * p.ldaux + col)) : make_uint2(0, 0);
+    }
+  }
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     const int rl = i * 4 + (lane >> 3);
@@ -119,7 +129,7 @@ __device__ __forceinline__ void epilogue_block(const Params& p, const float* stg
 #pragma unroll
       for (int j = 0; j < 4; ++j) v[j] = gelu_tanh(__bfloat162float(__float2bfloat16_rn(v[j])));
     } else if (p.epi == FX_EPI_DGELU) {
-      const uint2 z = __ldg(reinterpret_cast<const uint2*>(p.aux + (size_t)row * p.ldaux + col));
+      const uint2 z = zpre[i];
       v[0] *= gelu_tanh_grad(bf16_lo(z.x)); v[1] *= gelu_tanh_grad(bf16_hi(z.x));
       v[2] *= gelu_tanh_grad(bf16_lo(z.y)); v[3] *= gelu_tanh_grad(bf16_hi(z.y));
     }
