@@ -80,30 +80,33 @@ struct MaskParams {
 
 __global__ void __launch_bounds__(256)
 attn_dropout_mask_kernel(const MaskParams p) {
+  // CTA = 32 query rows (lane = row) of one (batch, head); its 8 warps walk the kv words 8 at a time up
+  // to the end of the diagonal 128-tile (tiles beyond it are never read: causal).
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int q = blockIdx.x * 32 + lane;
-  const int w = blockIdx.y * 8 + warp;                 // word index along kv
-  const int tile_end = (blockIdx.x * 32 / 128 + 1) * 128;  // causal: kv tiles beyond the diagonal tile are never read
-  if (w * 32 >= tile_end || w >= p.wpr || q >= p.s) return;
-  const uint64_t bh = blockIdx.z;
+  if (q >= p.s) return;
+  const int n_words = min(p.wpr, (blockIdx.x * 32 / 128 + 1) * 4);
+  const uint64_t bh = blockIdx.y;
   const uint64_t s8 = static_cast<uint64_t>((p.s + 7) / 8);
-  const uint64_t grp = (bh * p.s + q) * s8 + static_cast<uint64_t>(w) * 4;
-  uint32_t word = 0;
+  const uint64_t grp_row = (bh * p.s + q) * s8;
+  uint32_t* out_row = p.mask + (bh * p.s + q) * p.wpr;
+  for (int w = warp; w < n_words; w += 8) {
+    uint32_t word = 0;
 #pragma unroll
-  for (int c = 0; c < 4; ++c) {
-    const Philox8 rnd = philox4x32_10_rk(p.keys, p.off_lo, p.off_hi, grp + c);
+    for (int c = 0; c < 4; ++c) {
+      const Philox8 rnd = philox4x32_10_rk(p.keys, p.off_lo, p.off_hi, grp_row + static_cast<uint64_t>(w * 4 + c));
 #pragma unroll
-    for (int half = 0; half < 2; ++half) {  // k = 2c + half: lanes[2·half] holds u = 0, lanes[2·half + 1] holds u = 1
-      const uint32_t f0 = keep_flags2(rnd.lanes[2 * half], p.thresh2);
-      const uint32_t f1 = keep_flags2(rnd.lanes[2 * half + 1], p.thresh2);
-      // bytes [f0.b1, f0.b3, f1.b1, f1.b3]: their sign bits are the keep flags of elements 4k .. 4k+3
-      const uint32_t t = prmt(f0, f1, 0x7531u) & 0x80808080u;
-      word |= t >> (2 * c + half);
+      for (int half = 0; half < 2; ++half) {  // k = 2c + half: lanes[2·half] holds u = 0, lanes[2·half + 1] holds u = 1
+        const uint32_t f0 = keep_flags2(rnd.lanes[2 * half], p.thresh2);
+        const uint32_t f1 = keep_flags2(rnd.lanes[2 * half + 1], p.thresh2);
+        // bytes [f0.b1, f0.b3, f1.b1, f1.b3]: their sign bits are the keep flags of elements 4k .. 4k+3
+        const uint32_t t = prmt(f0, f1, 0x7531u) & 0x80808080u;
+        word |= t >> (2 * c + half);
+      }
     }
+    out_row[w] = word;
   }
-  p.mask[(bh * p.s + q) * p.wpr + w] = word;
 }
-
 
 template <int HD>
 struct FwdCfg {
@@ -1115,7 +1118,7 @@ extern "C" int fx_attn_causal_fwd(void* stream, const void* qkv, void* out, floa
     m.thresh2 = dropout_threshold(p_drop) * 0x10001u;
     m.off_lo = static_cast<uint32_t>(offset); m.off_hi = static_cast<uint32_t>(offset >> 32);
     m.keys = philox_round_keys(seed);
-    dim3 grid((s + 31) / 32, (wpr + 7) / 8, b * nh);
+    dim3 grid((s + 31) / 32, b * nh);
     attn::attn_dropout_mask_kernel<<<grid, 256, 0, st>>>(m);
     FX_LAUNCH_CHECK();
   }
