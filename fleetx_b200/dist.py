@@ -30,6 +30,14 @@ class _GroupOps:
     def all_reduce(self, t: torch.Tensor) -> torch.Tensor:
         return self.all_reduce_(t)
 
+    # Split form, so the caller can put independent work (the weight-gradient GEMMs) between the two
+    # halves and have it overlap the transfer. The base version is simply synchronous.
+    def all_reduce_start(self, t: torch.Tensor):
+        return self.all_reduce(t)
+
+    def all_reduce_finish(self, handle) -> torch.Tensor:
+        return handle
+
     def all_reduce_bias_dropout_residual(self, y, bias, residual, p, seed, offset, mask_in=None):
         from . import ops
 
@@ -69,6 +77,17 @@ class TorchDistGroup(_GroupOps):
     def barrier(self):
         self._dist.barrier(group=self.pg)
 
+    def all_reduce_start(self, t: torch.Tensor):
+        if self.nranks == 1:
+            return (t, None)
+        return (t, self._dist.all_reduce(t, op=self._dist.ReduceOp.SUM, group=self.pg, async_op=True))
+
+    def all_reduce_finish(self, handle) -> torch.Tensor:
+        t, work = handle
+        if work is not None:
+            work.wait()  # the current stream waits for the collective
+        return t
+
 
 class SymmetricTPGroup(TorchDistGroup):
     """Model-parallel group whose allreduces are this library's own kernel over NVLink/NVSwitch peer
@@ -99,6 +118,7 @@ class SymmetricTPGroup(TorchDistGroup):
         self._mc = int(self._hdl.multicast_ptr)
         self._lib = _lib
         self._epoch = 0
+        self._comm_stream = torch.cuda.Stream(device=dev, priority=-1)  # high priority: its blocks go first
         self.num_blocks = num_blocks
         self.max_elems = max_elems
         # the flag page must start at zero on every rank before the first call
@@ -136,6 +156,27 @@ class SymmetricTPGroup(TorchDistGroup):
         # caller consumes before the next row-parallel GEMM of this rank overwrites it (stream order)
         self._launch(t2, None, None, None, 0.0, 0, 0, None)
         return t
+
+    def all_reduce_start(self, t: torch.Tensor):
+        if not self._is_symmetric(t):
+            return super().all_reduce_start(t)
+        t2 = t.view(-1, t.shape[-1])
+        out = torch.empty_like(t2) if self.nranks == 2 else None  # allocated on the caller's stream
+        main = torch.cuda.current_stream()
+        ready = torch.cuda.Event()
+        ready.record(main)
+        with torch.cuda.stream(self._comm_stream):
+            self._comm_stream.wait_event(ready)
+            self._launch(t2, out, None, None, 0.0, 0, 0, None)
+            done = torch.cuda.Event()
+            done.record(self._comm_stream)
+        return ("symm", (out.view(t.shape) if out is not None else t), done)
+
+    def all_reduce_finish(self, handle) -> torch.Tensor:
+        if isinstance(handle, tuple) and len(handle) == 3 and handle[0] == "symm":
+            torch.cuda.current_stream().wait_event(handle[2])
+            return handle[1]
+        return super().all_reduce_finish(handle)
 
     def all_reduce_bias_dropout_residual(self, y, bias, residual, p, seed, offset, mask_in=None):
         if not self._is_symmetric(y):

@@ -119,16 +119,19 @@ def decoder_layer_bwd(dout: torch.Tensor, saved: dict, P: LayerParams, M: LayerM
         d, g["norm2_w"], g["norm2_b"] = ops.layernorm_bwd(d, saved["r2"], P.norm2_w, saved["mean3"], saved["rstd3"])
     # r2 = x1 + dropout2(y2 + b2): d is d(r2); the skip-path share d(x1) += d is folded in later
     d_y2 = ops.bias_dropout_residual_bwd(d, M.p_hidden2, *M.rng_h2, mask_in=M.mask_h2)
+    d_z = ops.gemm(d_y2, P.lin2_w, trans_b=True, epilogue=FX_EPI_DGELU, aux=saved["z"])  # (dY · W2^T) ∘ gelu'(z)
+    d_ffn_in = ops.gemm(d_z, P.lin1_w, trans_b=True, out=group.partial_buffer(T, h, d.device))
+    # backward of _c_identity: allreduce of dX. Nothing on the weight-gradient side depends on it, so the
+    # transfer runs on the group's own stream underneath those GEMMs.
+    pending = group.all_reduce_start(d_ffn_in)
     g["lin2_b"] = ops.colsum(d_y2)
     g["lin2_w"] = ops.gemm(saved["act"], d_y2, trans_a=True)                       # dW2 = act^T · dY
-    d_z = ops.gemm(d_y2, P.lin2_w, trans_b=True, epilogue=FX_EPI_DGELU, aux=saved["z"])  # (dY · W2^T) ∘ gelu'(z)
     del d_y2
     g["lin1_b"] = ops.colsum(d_z)
     ffn_in = saved["ln2"] if M.normalize_before else saved["x1"]
     g["lin1_w"] = ops.gemm(ffn_in, d_z, trans_a=True)
-    d_ffn_in = ops.gemm(d_z, P.lin1_w, trans_b=True, out=group.partial_buffer(T, h, d.device))
     del d_z
-    d_ffn_in = group.all_reduce(d_ffn_in)                                           # backward of _c_identity
+    d_ffn_in = group.all_reduce_finish(pending)
     if M.normalize_before:
         # x1 feeds LN2 and the skip: d(x1) = LN2'(d_ffn_in) + d
         d_x1, g["norm2_w"], g["norm2_b"] = ops.layernorm_bwd(d_ffn_in, saved["x1"], P.norm2_w, saved["mean2"],
@@ -141,19 +144,20 @@ def decoder_layer_bwd(dout: torch.Tensor, saved: dict, P: LayerParams, M: LayerM
     del d_ffn_in
     # r1 = x + dropout1(attn_out + bo)
     d_ao = ops.bias_dropout_residual_bwd(d_r1, M.p_hidden1, *M.rng_h1, mask_in=M.mask_h1)
-    g["out_b"] = ops.colsum(d_ao)
-    g["out_w"] = ops.gemm(saved["ctx"], d_ao, trans_a=True)
     d_ctx = ops.gemm(d_ao, P.out_w, trans_b=True)
-    del d_ao
     d_qkv = ops.attn_causal_bwd(d_ctx.view(b, s, -1), saved["qkv"].view(b, s, -1), saved["ctx"].view(b, s, -1),
                                 saved["lse"], saved["attn_mask"], M.nh_local, M.hd, scale, M.p_attn).view(T, -1)
     del d_ctx
+    d_attn_in = ops.gemm(d_qkv, P.qkv_w, trans_b=True, out=group.partial_buffer(T, h, d.device))
+    pending = group.all_reduce_start(d_attn_in)                                     # backward of _c_identity
+    g["out_b"] = ops.colsum(d_ao)
+    g["out_w"] = ops.gemm(saved["ctx"], d_ao, trans_a=True)
+    del d_ao
     g["qkv_b"] = ops.colsum(d_qkv)
     attn_in = saved["ln1"] if M.normalize_before else saved["x"]
     g["qkv_w"] = ops.gemm(attn_in, d_qkv, trans_a=True)
-    d_attn_in = ops.gemm(d_qkv, P.qkv_w, trans_b=True, out=group.partial_buffer(T, h, d.device))
     del d_qkv
-    d_attn_in = group.all_reduce(d_attn_in)                                         # backward of _c_identity
+    d_attn_in = group.all_reduce_finish(pending)
     if M.normalize_before:
         dx, g["norm1_w"], g["norm1_b"] = ops.layernorm_bwd(d_attn_in, saved["x"], P.norm1_w, saved["mean1"],
                                                            saved["rstd1"], dresidual=d_r1)
