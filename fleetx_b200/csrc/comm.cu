@@ -57,6 +57,7 @@ struct Params {
   float p_drop, scale;
   uint32_t thresh;
   uint64_t seed, offset;
+  uint64_t group0;           // dropout group index of vector 0 (row slices of a larger [T, h] tensor)
   const uint8_t* mask_in;
   int variant;               // 0: reduced slices are multicast to every rank (multimem.st), phase 3 reads locally
                              // 1: reduced slices stay with their owner, phase 3 pulls them with peer loads
@@ -224,7 +225,7 @@ tp_allreduce_kernel(const Params p) {
             o[4 + j] = r[4 + j] + (((m.y >> (8 * j)) & 0xFFu) ? y[4 + j] * p.scale : 0.f);
           }
         } else if (p.p_drop > 0.f) {
-          const Philox8 rnd = philox4x32_10(p.seed, p.offset, v);  // group index = vector index of [rows, h]
+          const Philox8 rnd = philox4x32_10(p.seed, p.offset, p.group0 + v);  // group index = vector index in [T, h]
 #pragma unroll
           for (int j = 0; j < 8; ++j) o[j] = r[j] + (philox_keep(rnd, j, p.thresh) ? y[j] * p.scale : 0.f);
         } else {
@@ -249,7 +250,8 @@ tp_allreduce_kernel(const Params p) {
 extern "C" int fx_tp_allreduce_bdr(void* stream, const uint64_t* peer_bufs, const uint64_t* peer_signal_pads,
                                    uint64_t multicast_ptr, int rank, int world, uint32_t epoch, int num_blocks,
                                    void* out, int rows, int h, const void* bias, const void* residual, float p,
-                                   uint64_t seed, uint64_t offset, const uint8_t* mask_in) {
+                                   uint64_t seed, uint64_t offset, const uint8_t* mask_in, uint64_t buf_elem_offset,
+                                   uint64_t dropout_elem_offset) {
   using namespace fx;
   FX_CHECK_ARG(world >= 2 && world <= comm::MAX_RANKS && rank >= 0 && rank < world,
                "fx_tp_allreduce_bdr: bad rank/world (%d/%d)", rank, world);
@@ -258,6 +260,8 @@ extern "C" int fx_tp_allreduce_bdr(void* stream, const uint64_t* peer_bufs, cons
   FX_CHECK_ARG(out != nullptr || residual == nullptr, "fx_tp_allreduce_bdr: out may only be null for a plain allreduce");
   FX_CHECK_ARG(p >= 0.f && p < 1.f, "fx_tp_allreduce_bdr: dropout p must be in [0,1) (got %f)", p);
   FX_CHECK_ARG(epoch > 0, "fx_tp_allreduce_bdr: epoch must start at 1");
+  FX_CHECK_ARG(buf_elem_offset % 8 == 0 && dropout_elem_offset % 8 == 0,
+               "fx_tp_allreduce_bdr: element offsets must be multiples of 8");
   FX_CHECK_ARG(num_blocks > 0 && num_blocks <= num_sms(), "fx_tp_allreduce_bdr: num_blocks must be in [1, #SMs] "
                "(all blocks of all ranks wait on each other, so they must be co-resident)");
   FX_CHECK_ARG((bias == nullptr && mask_in == nullptr && p == 0.f) || residual != nullptr,
@@ -265,9 +269,10 @@ extern "C" int fx_tp_allreduce_bdr(void* stream, const uint64_t* peer_bufs, cons
   comm::Params q{};
   for (int i = 0; i < world; ++i) {
     q.sig[i] = peer_signal_pads[i];
-    q.buf[i] = peer_bufs[i];
+    q.buf[i] = peer_bufs[i] + buf_elem_offset * 2;
   }
-  q.mc = multicast_ptr;
+  q.mc = multicast_ptr + buf_elem_offset * 2;
+  q.group0 = dropout_elem_offset / 8;
   q.rank = rank; q.world = world;
   q.rows = rows; q.h = h;
   q.epoch = epoch;

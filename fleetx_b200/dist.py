@@ -132,10 +132,21 @@ class SymmetricTPGroup(TorchDistGroup):
             return super().partial_buffer(rows, cols, device)
         return self._buf[: rows * cols].view(rows, cols)
 
-    def _is_symmetric(self, t: torch.Tensor) -> bool:
-        return t.data_ptr() == self._buf.data_ptr() and t.is_contiguous() and t.dtype == torch.bfloat16
+    supports_chunks = True  # the layer may pipeline batch halves through all_reduce_bdr_start / _finish
 
-    def _launch(self, y, out, bias, residual, p, seed, offset, mask_in):
+    def _symm_offset(self, t: torch.Tensor):
+        """Element offset of t inside the symmetric buffer, or None if t is not a contiguous view of it."""
+        if t.dtype != torch.bfloat16 or not t.is_contiguous():
+            return None
+        off = t.data_ptr() - self._buf.data_ptr()
+        if off < 0 or off % 16 or off // 2 + t.numel() > self.max_elems:
+            return None
+        return off // 2
+
+    def _is_symmetric(self, t: torch.Tensor) -> bool:
+        return self._symm_offset(t) is not None
+
+    def _launch(self, y, out, bias, residual, p, seed, offset, mask_in, dropout_elem_offset=0):
         rows, h = y.shape[0], y.shape[1]
         self._epoch += 1
         lib = self._lib.lib()
@@ -143,7 +154,8 @@ class SymmetricTPGroup(TorchDistGroup):
             torch.cuda.current_stream().cuda_stream, self._peer_bufs, self._peer_sigs, self._mc, self.rank, self.nranks,
             self._epoch, self.num_blocks, None if out is None else out.data_ptr(), rows, h,
             None if bias is None else bias.data_ptr(), None if residual is None else residual.data_ptr(),
-            float(p), int(seed), int(offset), None if mask_in is None else mask_in.data_ptr()), "fx_tp_allreduce_bdr")
+            float(p), int(seed), int(offset), None if mask_in is None else mask_in.data_ptr(),
+            self._symm_offset(y), int(dropout_elem_offset)), "fx_tp_allreduce_bdr")
         return out
 
     def all_reduce(self, t: torch.Tensor) -> torch.Tensor:
@@ -184,6 +196,22 @@ class SymmetricTPGroup(TorchDistGroup):
         y2 = y.view(-1, y.shape[-1])
         out = torch.empty_like(y2)
         return self._launch(y2, out, bias, residual.view_as(y2), p, seed, offset, mask_in).view(y.shape)
+
+    def all_reduce_bdr_start(self, y, out, bias, residual, p, seed, offset, mask_in, dropout_elem_offset):
+        """Fused allreduce + bias + dropout + residual of a row slice, on the group's stream. y is a view
+        of the symmetric buffer, out / residual / mask_in are the matching row slices."""
+        main = torch.cuda.current_stream()
+        ready = torch.cuda.Event()
+        ready.record(main)
+        with torch.cuda.stream(self._comm_stream):
+            self._comm_stream.wait_event(ready)
+            self._launch(y, out, bias, residual, p, seed, offset, mask_in, dropout_elem_offset)
+            done = torch.cuda.Event()
+            done.record(self._comm_stream)
+        return done
+
+    def all_reduce_bdr_finish(self, done) -> None:
+        torch.cuda.current_stream().wait_event(done)
 
 
 _DEFAULT_GROUP = None

@@ -49,14 +49,19 @@ def _workspace(nbytes: int, device) -> torch.Tensor:
 
 
 # ------------------------------------------------------------------------------- LayerNorm
-def layernorm_fwd(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float = 1e-5):
+def layernorm_fwd(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float = 1e-5, out=None):
+    """out: optional (y, mean, rstd) to write into (row slices of larger buffers)."""
     h = x.shape[-1]
     x2 = _need(x, torch.bfloat16, "x").view(-1, h)
     rows = x2.shape[0]
     _need(gamma, torch.float32, "gamma"), _need(beta, torch.float32, "beta")
-    y = torch.empty_like(x2)
-    mean = torch.empty(rows, dtype=torch.float32, device=x.device)
-    rstd = torch.empty(rows, dtype=torch.float32, device=x.device)
+    if out is not None:
+        y, mean, rstd = out
+        _need(y, torch.bfloat16, "y"), _need(mean, torch.float32, "mean"), _need(rstd, torch.float32, "rstd")
+    else:
+        y = torch.empty_like(x2)
+        mean = torch.empty(rows, dtype=torch.float32, device=x.device)
+        rstd = torch.empty(rows, dtype=torch.float32, device=x.device)
     check(_lib.lib().fx_layernorm_fwd(_stream(), _p(x2), _p(gamma), _p(beta), _p(y), _p(mean), _p(rstd),
                                       rows, h, float(eps)), "fx_layernorm_fwd")
     return y.view(x.shape), mean, rstd

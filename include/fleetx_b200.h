@@ -147,11 +147,16 @@ int fx_attn_causal_bwd(void* stream, const void* dout, const void* qkv, const vo
  * out (ordinary local memory) = residual + dropout(sum + bias), or just the sum; with out = NULL
  * (plain allreduce only) the sum is left in every rank's copy of the symmetric buffer.
  * num_blocks <= #SMs: the blocks of all ranks wait on each other and must be co-resident. One
- * process per GPU. */
+ * process per GPU. Row slices of a larger [T,h] tensor (the layer pipelines two batch halves so that
+ * one half's transfer hides under the other half's GEMMs): buf_elem_offset is where this slice starts
+ * inside the symmetric buffer, dropout_elem_offset where it starts inside [T,h] (the dropout mask is
+ * indexed by position in the whole tensor); both in elements, multiples of 8; out / residual /
+ * mask_in already point at the slice. */
 int fx_tp_allreduce_bdr(void* stream, const uint64_t* peer_bufs, const uint64_t* peer_signal_pads,
                         uint64_t multicast_ptr, int rank, int world, uint32_t epoch, int num_blocks,
                         void* out, int rows, int h, const void* bias, const void* residual, float p,
-                        uint64_t seed, uint64_t offset, const uint8_t* mask_in);
+                        uint64_t seed, uint64_t offset, const uint8_t* mask_in, uint64_t buf_elem_offset,
+                        uint64_t dropout_elem_offset);
 
 #ifdef __cplusplus
 }
