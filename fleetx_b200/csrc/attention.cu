@@ -282,22 +282,23 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FwdParams p) 
     __nv_bfloat16* xch = reinterpret_cast<__nv_bfloat16*>(smem + C::OFF_XCH);
     constexpr int OC = HD / 2;  // output columns per thread
 
-    float o[OC];
+    uint64_t o2[OC / 2];  // packed fp32 pairs (FFMA2): o2[i] = output columns 2i, 2i+1 of my half
 #pragma unroll
-    for (int i = 0; i < OC; ++i) o[i] = 0.f;
+    for (int i = 0; i < OC / 2; ++i) o2[i] = 0ull;
     float m = -INFINITY, l = 0.f, alpha_prev = 0.f;
 
     auto o_update = [&](int j, float alpha) {
       const int buf = j & 1;
       mbar_wait(&pv_full[buf], (j >> 1) & 1, 30);
       tc_fence_after();
+      const uint64_t alpha2 = f2_pack(alpha, alpha);
 #pragma unroll
       for (int c = 0; c < OC / 32; ++c) {
         uint32_t r[32];
         tmem_ld_32x32(lane_base + C::TMEM_PV + buf * HD + half * OC + c * 32, r);
         tmem_ld_wait();
 #pragma unroll
-        for (int i = 0; i < 32; ++i) o[c * 32 + i] = o[c * 32 + i] * alpha + __uint_as_float(r[i]);
+        for (int i = 0; i < 16; ++i) o2[c * 16 + i] = fma2(o2[c * 16 + i], alpha2, f2_pack_u(r[2 * i], r[2 * i + 1]));
       }
       tc_fence_before();
       __syncwarp();
@@ -307,10 +308,13 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FwdParams p) 
     // Dropout's 1/(1-p) is folded into the exponent (p' = 2^(s·sl2 - m·sl2 + log2 inv_keep)), so the
     // row sum below runs over p' too and is scaled back once at the end.
     const float log2_inv_keep = p.log2_inv_keep;
+    const uint64_t sl2_2 = f2_pack(sl2, sl2);
 
-    for (int j = 0; j < n_kv; ++j) {
+    // One kv tile. DIAG (only the diagonal tile needs the causal predicate) is a compile-time flag: as a
+    // run-time one the compiler if-converted it into a compare + select per element of EVERY tile.
+    auto tile = [&](int j, auto diag_c) {
+      constexpr bool DIAG = decltype(diag_c)::value;
       const int sb = j % C::NS;
-      const bool diag = (j == qt);  // only the diagonal tile needs the causal predicate
       uint2 mw = make_uint2(0, 0);
       if (drop) mw = __ldg(mask_row + 2 * j);  // issued before the wait: the load overlaps sweep 1
       mbar_wait(&s_full[sb], (j / C::NS) & 1, 31);
@@ -322,7 +326,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FwdParams p) 
         uint32_t r[32];
         tmem_ld_32x32(lane_base + sb * 128 + half * 64 + c * 32, r);
         tmem_ld_wait();
-        if (diag) {
+        if (DIAG) {
 #pragma unroll
           for (int i = 0; i < 32; ++i)
             mx = fmaxf(mx, (half * 64 + c * 32 + i > row_local) ? -INFINITY : __uint_as_float(r[i]));
@@ -341,10 +345,11 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FwdParams p) 
       const float m_new = fmaxf(m, fmaxf(__bfloat162float(mine_up), other));
       const float alpha = ex2_approx((m - m_new) * sl2);
       const float neg_m = log2_inv_keep - m_new * sl2;
+      const uint64_t neg_m2 = f2_pack(neg_m, neg_m);
       // P buffer must have been consumed by PV_{j-1}
       mbar_wait(p_empty, (j & 1) ^ 1, 32);
       // sweep 2: probabilities -> bf16 P tile (dropout folded in), row sum of the undropped p'
-      float rowsum = 0.f;
+      uint64_t rowsum2 = 0ull;
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
         uint32_t r[32];
@@ -353,13 +358,14 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FwdParams p) 
         uint32_t pk[16];
 #pragma unroll
         for (int i = 0; i < 32; i += 2) {
-          float e0 = ex2_approx(fmaf(__uint_as_float(r[i]), sl2, neg_m));
-          float e1 = ex2_approx(fmaf(__uint_as_float(r[i + 1]), sl2, neg_m));
-          if (diag) {
+          const uint64_t a = fma2(f2_pack_u(r[i], r[i + 1]), sl2_2, neg_m2);
+          float e0 = ex2_approx(f2_lo(a));
+          float e1 = ex2_approx(f2_hi(a));
+          if (DIAG) {
             e0 = (half * 64 + c * 32 + i > row_local) ? 0.f : e0;
             e1 = (half * 64 + c * 32 + i + 1 > row_local) ? 0.f : e1;
           }
-          rowsum += e0 + e1;
+          rowsum2 = add2(rowsum2, f2_pack(e0, e1));
           pk[i >> 1] = pack_bf16(e0, e1);
         }
         if (drop) {
@@ -384,11 +390,14 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FwdParams p) 
         mbar_arrive(&s_empty[sb]);
         mbar_arrive(p_full);
       }
-      l = l * alpha + rowsum;
+      l = l * alpha + (f2_lo(rowsum2) + f2_hi(rowsum2));
       m = m_new;
       if (j > 0) o_update(j - 1, alpha_prev);
       alpha_prev = alpha;
-    }
+    };
+
+    for (int j = 0; j < n_kv - 1; ++j) tile(j, std::false_type{});
+    tile(n_kv - 1, std::true_type{});  // n_kv - 1 == qt: the diagonal tile
     o_update(n_kv - 1, alpha_prev);
 
     // the two partial row sums share every rescale, so they simply add; exchange them in fp32 through
@@ -404,10 +413,10 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FwdParams p) 
                                            half * OC);
 #pragma unroll
       for (int g = 0; g < OC / 8; ++g)
-        op[g] = make_uint4(pack_bf16(o[g * 8 + 0] * inv_l, o[g * 8 + 1] * inv_l),
-                           pack_bf16(o[g * 8 + 2] * inv_l, o[g * 8 + 3] * inv_l),
-                           pack_bf16(o[g * 8 + 4] * inv_l, o[g * 8 + 5] * inv_l),
-                           pack_bf16(o[g * 8 + 6] * inv_l, o[g * 8 + 7] * inv_l));
+        op[g] = make_uint4(pack_bf16(f2_lo(o2[g * 4 + 0]) * inv_l, f2_hi(o2[g * 4 + 0]) * inv_l),
+                           pack_bf16(f2_lo(o2[g * 4 + 1]) * inv_l, f2_hi(o2[g * 4 + 1]) * inv_l),
+                           pack_bf16(f2_lo(o2[g * 4 + 2]) * inv_l, f2_hi(o2[g * 4 + 2]) * inv_l),
+                           pack_bf16(f2_lo(o2[g * 4 + 3]) * inv_l, f2_hi(o2[g * 4 + 3]) * inv_l));
       if (half == 0)
         p.lse[(static_cast<size_t>(batch) * p.nh + head) * p.s + row] = m * p.scale + __logf(l) - __logf(p.inv_keep);
     }
