@@ -486,8 +486,9 @@ __device__ unsigned long long g_trace[16];
 #endif
 
 struct BwdParams {
-  const float* lse2;    // [b, nh, s_pad]  lse·log2(e) − log2(inv_keep); +inf in the padding
-  const float* delta;   // [b, nh, s_pad]  rowsum(dO ∘ O) / inv_keep;     0 in the padding
+  // both statistics are stored NEGATED: they enter the element-wise math as addends of packed FMA / ADD
+  const float* lse2;    // [b, nh, s_pad]  −(lse·log2(e) − log2(inv_keep)); −inf in the padding
+  const float* delta;   // [b, nh, s_pad]  −rowsum(dO ∘ O) / inv_keep;       0 in the padding
   __nv_bfloat16* dqkv;  // [b, s, nh, 3, hd]
   int b, s, nh, s_pad;  // s_pad = s rounded up to 128
   float scale, p_drop, inv_keep;
@@ -503,7 +504,8 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
 // check: with dropout folded in as p' = p·inv_keep,
 //   dS = p'·(keep·dP − delta'),  p' = 2^(s·scale·log2e − lse2),
 //   lse2 = lse·log2e − log2(inv_keep),  delta' = rowsum(dO ∘ O) / inv_keep.
-// Padding rows get lse2 = +inf (p' = 0) and delta' = 0.
+// Both are stored negated (they are addends of a packed FMA / ADD in the kernels). Padding rows get
+// −lse2 = −inf (p' = 0) and delta' = 0.
 __global__ void __launch_bounds__(256)
 attn_delta_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16* __restrict__ out,
                   const float* __restrict__ lse, float* __restrict__ lse2, float* __restrict__ delta, int b, int s,
@@ -517,7 +519,7 @@ attn_delta_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16* _
   const int batch = (int)(br / s_pad);
   const size_t o_idx = ((size_t)batch * nh + head) * s_pad + row;
   if (row >= s) {
-    lse2[o_idx] = INFINITY;
+    lse2[o_idx] = -INFINITY;
     delta[o_idx] = 0.f;
     return;
   }
@@ -531,8 +533,8 @@ attn_delta_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16* _
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc += bf16_lo(xs[j]) * bf16_lo(ys[j]) + bf16_hi(xs[j]) * bf16_hi(ys[j]);
   }
-  delta[o_idx] = acc * keep;
-  lse2[o_idx] = lse[((size_t)batch * nh + head) * s + row] * LOG2E - log2_inv_keep;
+  delta[o_idx] = -acc * keep;
+  lse2[o_idx] = log2_inv_keep - lse[((size_t)batch * nh + head) * s + row] * LOG2E;
 }
 
 // TMEM accumulator columns [taddr, taddr + NCOLS) of this thread's row -> bf16, times `mul`, to dst.
@@ -712,8 +714,9 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tma_q,   // qkv, box rows
     const uint32_t* mask_row = p.mask + (static_cast<size_t>(batch * p.nh + head) * p.s + min(row, p.s - 1)) * p.wpr + (part >> 1);
     const int mshift = (part & 1) * 4;
     const size_t stat_idx = (static_cast<size_t>(batch) * p.nh + head) * p.s_pad + row;  // row < s_pad always
-    const float neg_lse2 = -p.lse2[stat_idx];
-    const float delta_r = p.delta[stat_idx];
+    const float neg_lse2 = p.lse2[stat_idx];
+    const uint64_t sl2_2 = f2_pack(sl2, sl2), nl2_2 = f2_pack(neg_lse2, neg_lse2);
+    const uint64_t nd_2 = f2_pack(p.delta[stat_idx], p.delta[stat_idx]);
 
     // One 128 x 64 tile: p' = 2^(s·sl2 − lse2), dS = p'·(keep·dP − delta'). DIAG / DROP are compile-time
     // so that the common tile (below the diagonal) carries no predicate or select per element.
@@ -743,13 +746,15 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tma_q,   // qkv, box rows
       uint32_t pk[8];
 #pragma unroll
       for (int i = 0; i < 16; i += 2) {
-        float p0 = ex2_approx(fmaf(__uint_as_float(rs[i]), sl2, neg_lse2));
-        float p1 = ex2_approx(fmaf(__uint_as_float(rs[i + 1]), sl2, neg_lse2));
+        const uint64_t a = fma2(f2_pack_u(rs[i], rs[i + 1]), sl2_2, nl2_2);
+        float p0 = ex2_approx(f2_lo(a));
+        float p1 = ex2_approx(f2_hi(a));
         if constexpr (DIAG) {
           p0 = (kv0 + i > row) ? 0.f : p0;
           p1 = (kv0 + i + 1 > row) ? 0.f : p1;
         }
-        pk[i >> 1] = pack_bf16(p0 * (__uint_as_float(rp[i]) - delta_r), p1 * (__uint_as_float(rp[i + 1]) - delta_r));
+        const uint64_t ds = mul2(f2_pack(p0, p1), add2(f2_pack_u(rp[i], rp[i + 1]), nd_2));
+        pk[i >> 1] = pack_bf16(f2_lo(ds), f2_hi(ds));
       }
       // dS (bf16 pairs) goes back into the first 8 of this thread's own 16 dP columns
       tmem_st_32x8(lane_base + C::TM_DP + buf * 64 + part * 16, pk);
@@ -961,6 +966,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tma_kv,  // qkv, box row
     // query's 4 words, element e = r % 32 at bit 8·(e & 3) + 7 − e/4; mask_sh moves that bit to bit 31.
     const int mask_word = r_local >> 5;
     const int mask_sh = 31 - (8 * (r_local & 3) + 7 - ((r_local & 31) >> 2));
+    const uint64_t sl2_2 = f2_pack(sl2, sl2);
 
     FX_T0();
     // One 128 x 64 tile: p' = 2^(s·sl2 − lse2), P^T = keep·p', dS^T = p'·(keep·dP^T − delta'). DIAG / DROP
@@ -989,14 +995,15 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tma_kv,  // qkv, box row
       uint32_t pk_p[8], pk_ds[8];
 #pragma unroll
       for (int i4 = 0; i4 < 16; i4 += 4) {
-        const float4 l2 = *reinterpret_cast<const float4*>(stat + i4);       // warp-uniform: broadcast
-        const float4 dl = *reinterpret_cast<const float4*>(stat + 64 + i4);
-        const float l2v[4] = {l2.x, l2.y, l2.z, l2.w}, dlv[4] = {dl.x, dl.y, dl.z, dl.w};
+        // (−lse2, −delta') of queries i4 .. i4+3 as two packed pairs each; warp-uniform: broadcast
+        const ulonglong2 l2 = *reinterpret_cast<const ulonglong2*>(stat + i4);
+        const ulonglong2 dl = *reinterpret_cast<const ulonglong2*>(stat + 64 + i4);
 #pragma unroll
         for (int u = 0; u < 4; u += 2) {
           const int i = i4 + u;
-          float p0 = ex2_approx(fmaf(__uint_as_float(rs[i]), sl2, -l2v[u]));
-          float p1 = ex2_approx(fmaf(__uint_as_float(rs[i + 1]), sl2, -l2v[u + 1]));
+          const uint64_t a = fma2(f2_pack_u(rs[i], rs[i + 1]), sl2_2, u == 0 ? l2.x : l2.y);
+          float p0 = ex2_approx(f2_lo(a));
+          float p1 = ex2_approx(f2_hi(a));
           if constexpr (DIAG) {
             p0 = (qh + i < kv) ? 0.f : p0;
             p1 = (qh + i + 1 < kv) ? 0.f : p1;
@@ -1010,7 +1017,8 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tma_kv,  // qkv, box row
             pp &= prmt(m0, m1, 0x5410u);
           }
           pk_p[i >> 1] = pp;
-          pk_ds[i >> 1] = pack_bf16(p0 * (__uint_as_float(d0) - dlv[u]), p1 * (__uint_as_float(d1) - dlv[u + 1]));
+          const uint64_t ds = mul2(f2_pack(p0, p1), add2(f2_pack_u(d0, d1), u == 0 ? dl.x : dl.y));
+          pk_ds[i >> 1] = pack_bf16(f2_lo(ds), f2_hi(ds));
         }
       }
       FX_T(3);
