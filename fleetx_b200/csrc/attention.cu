@@ -23,6 +23,7 @@
 //              S^T = K·Q^T, dP^T = V·dO^T, dV += P^T·dO, dK += dS^T·Q
 //   dQ  kernel: CTA owns a 128-row Q tile, walks KV tiles: S = Q·K^T, dP = dO·V^T, dQ += dS·K
 //   with delta = rowsum(dO ∘ O) from a small pre-pass (workspace, fp32 [b, nh, s]).
+#include <stdlib.h>
 #include <type_traits>
 
 #include "common.cuh"
@@ -1069,15 +1070,28 @@ static int make_out_map_rows(CUtensorMap* map, const void* out, int b, int s, in
   return make_tma_bf16(map, out, 4, dims, strides, box);
 }
 
+#include "attention_bwd_fused.cuh"
+
+// head_dim 64 runs the single-kernel backward unless FX_ATTN_BWD=split asks for the deterministic pair
+static bool use_fused_bwd(int hd) {
+  static const bool split = [] {
+    const char* e = getenv("FX_ATTN_BWD");
+    return e && e[0] == 's';
+  }();
+  return hd == 64 && !split;
+}
+
 template <int HD>
 static int launch_bwd(cudaStream_t st, const void* dout, const void* qkv, const void* out, const float* lse,
-                      const BwdParams& p, float* lse2, float* delta) {
+                      const BwdParams& p, float* lse2, float* delta, float* dq_acc) {
   static bool attr_set[64] = {false};
   int dev = 0;
   FX_CUDA(cudaGetDevice(&dev));
   if (dev < 64 && !attr_set[dev]) {
     FX_CUDA(cudaFuncSetAttribute(attn_bwd_dq_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, DqCfg<HD>::SMEM_BYTES));
     FX_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, DkvCfg<HD>::SMEM_BYTES));
+    if (HD == 64)
+      FX_CUDA(cudaFuncSetAttribute(attn_bwd_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FusedCfg::SMEM_BYTES));
     attr_set[dev] = true;
   }
   CUtensorMap qkv128, qkv64, do128, do64, mmap;
@@ -1098,6 +1112,16 @@ static int launch_bwd(cudaStream_t st, const void* dout, const void* qkv, const 
       p.nh, HD, p.s_pad, p.p_drop > 0.f ? log2f(p.inv_keep) : 0.f, 1.0f - p.p_drop);
   FX_LAUNCH_CHECK();
   dim3 grid((p.s + 127) / 128, p.nh, p.b);
+  if (HD == 64 && use_fused_bwd(HD)) {
+    const size_t acc_floats = (size_t)p.b * p.nh * p.s_pad * 64;
+    FX_CUDA(cudaMemsetAsync(dq_acc, 0, acc_floats * sizeof(float), st));
+    attn_bwd_fused_kernel<<<grid, BWD_THREADS, FusedCfg::SMEM_BYTES, st>>>(qkv128, qkv64, do64, mmap, p, dq_acc);
+    FX_LAUNCH_CHECK();
+    const size_t n = (size_t)p.b * p.nh * p.s_pad * 8;
+    attn_dq_convert_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(dq_acc, p.dqkv, p.b, p.s, p.nh, p.s_pad, p.scale);
+    FX_LAUNCH_CHECK();
+    return FX_OK;
+  }
   attn_bwd_dkv_kernel<HD><<<grid, BWD_THREADS, DkvCfg<HD>::SMEM_BYTES, st>>>(qkv128, qkv64, do64, mmap, p);
   FX_LAUNCH_CHECK();
   attn_bwd_dq_kernel<HD><<<grid, BWD_THREADS, DqCfg<HD>::SMEM_BYTES, st>>>(qkv128, qkv64, do128, p);
@@ -1164,10 +1188,11 @@ extern "C" int fx_debug_trace(unsigned long long* host16, int reset) {
 #endif
 
 extern "C" size_t fx_attn_causal_bwd_workspace_bytes(int b, int s, int nh, int hd) {
-  (void)hd;
   if (b <= 0 || s <= 0 || nh <= 0) return 0;
   const size_t s_pad = ((size_t)s + 127) / 128 * 128;
-  return 2 * (size_t)b * nh * s_pad * sizeof(float);  // lse2 and delta', padded per (batch, head) row
+  // −lse2 and −delta', padded per (batch, head) row; head_dim 64 adds the fp32 dQ accumulator of the
+  // single-kernel backward ([b, nh, s_pad, 64])
+  return (size_t)b * nh * s_pad * sizeof(float) * (hd == 64 ? 2 + 64 : 2);
 }
 
 extern "C" int fx_attn_causal_bwd(void* stream, const void* dout, const void* qkv, const void* out,
@@ -1195,6 +1220,7 @@ extern "C" int fx_attn_causal_bwd(void* stream, const void* dout, const void* qk
   p.mask = static_cast<const uint32_t*>(dropout_mask);
   p.wpr = (s + 127) / 128 * 4;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  return hd == 64 ? attn::launch_bwd<64>(st, dout, qkv, out, lse, p, lse2, delta)
-                  : attn::launch_bwd<128>(st, dout, qkv, out, lse, p, lse2, delta);
+  float* dq_acc = delta + (size_t)b * nh * p.s_pad;  // head_dim 64 only (see fx_attn_causal_bwd_workspace_bytes)
+  return hd == 64 ? attn::launch_bwd<64>(st, dout, qkv, out, lse, p, lse2, delta, dq_acc)
+                  : attn::launch_bwd<128>(st, dout, qkv, out, lse, p, lse2, delta, nullptr);
 }
