@@ -306,8 +306,10 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tma_kv,    // qkv, box
     };
 
     for (int t = 0; t < n_q; ++t) {
-      // the dQ block of the previous pair is drained one tile late, so its MMAs have long retired
-      if ((t & 1) == 0 && t >= 2) drain_dq((t >> 1) - 1, 128 * 64 * 4);
+      // The dQ block of pair P is drained before tile 2P+3: its MMAs were issued after tile 2P+1 and sit
+      // behind that tile's dV / dK MMAs in the tensor pipe, so one full tile of element-wise work later
+      // they have retired and the drain does not wait.
+      if ((t & 1) == 1 && t >= 3) drain_dq((t >> 1) - 1, 128 * 64 * 4);
       const bool diag = (t < 2);  // the first two 64-row query tiles straddle the diagonal
       if (drop) {
         if (diag) tile(t, std::true_type{}, std::true_type{});
@@ -317,7 +319,10 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tma_kv,    // qkv, box
         else tile(t, std::false_type{}, std::false_type{});
       }
     }
-    // last pair: a single tile when n_q is odd (rows 64..127 of the accumulator are then stale: not added)
+    // what the loop has not drained: the pair before the last when n_q is odd (its drain slot would have
+    // been tile n_q), and the last pair — a single tile when n_q is odd (rows 64..127 of the accumulator
+    // are then stale and are not added)
+    if ((n_q & 1) == 1 && n_q >= 3) drain_dq((n_q >> 1) - 1, 128 * 64 * 4);
     drain_dq((n_q - 1) >> 1, (n_q & 1) ? 64 * 64 * 4 : 128 * 64 * 4);
 
     // dV = P_drop^T · dO, dK = scale * dS^T · Q; this warp drains columns [part*16, +16)
