@@ -187,7 +187,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FwdParams p) 
 
   if (warp == FWD_TMA_WARP) {
     // ------------------------------------------------------------------ TMA producer
-    if (lane == 0) {
+    if (elect_one()) {
       mbar_expect_tx(q_full, C::TILE_BYTES);
 #pragma unroll
       for (int h2 = 0; h2 < HD / 64; ++h2)
@@ -226,7 +226,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FwdParams p) 
       mbar_wait(&k_full[buf], (j >> 1) & 1, 20);
       mbar_wait(&s_empty[sb], ((j / C::NS) & 1) ^ 1, 21);
       tc_fence_after();
-      if (lane == 0) {
+      if (elect_one()) {
         const uint32_t k_lo = k_lo0 + buf * (C::TILE_BYTES >> 4);
         const uint32_t d = tmem_base + sb * 128;
 #pragma unroll
@@ -251,7 +251,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FwdParams p) 
       mbar_wait(&v_full[buf], ph, 24);
       mbar_wait(&pv_empty[buf], ph ^ 1, 25);
       tc_fence_after();
-      if (lane == 0) {
+      if (elect_one()) {
         const uint32_t v_lo = v_lo0 + buf * (C::TILE_BYTES >> 4);
         const uint32_t d = tmem_base + C::TMEM_PV + buf * HD;
 #pragma unroll
@@ -632,7 +632,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tma_q,   // qkv, box rows
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == BWD_TMA_WARP) {
-    if (lane == 0) {
+    if (elect_one()) {
       mbar_expect_tx(qdo_full, 2 * C::QT_BYTES);
 #pragma unroll
       for (int h2 = 0; h2 < HD / 64; ++h2) {
@@ -665,7 +665,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tma_q,   // qkv, box rows
       const int buf = j % C::NB, st = j % C::NKV;
       mbar_wait(&kv_full[st], (j / C::NKV) & 1, 41);
       tc_fence_after();
-      if (lane == 0) {
+      if (elect_one()) {
         const uint32_t k_lo = k_lo0 + st * (C::KV_BYTES >> 4), v_lo = v_lo0 + st * (C::KV_BYTES >> 4);
         const uint32_t d_s = tmem_base + C::TM_S + buf * 64, d_dp = tmem_base + C::TM_DP + buf * 64;
 #pragma unroll
@@ -691,7 +691,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tma_q,   // qkv, box rows
       const int buf = j % C::NB, st = j % C::NKV;
       mbar_wait(&ds_full[buf], (j / C::NB) & 1, 44);
       tc_fence_after();
-      if (lane == 0) {
+      if (elect_one()) {
         const uint32_t k_lo = kmn_lo0 + st * (C::KV_BYTES >> 4);
         const uint32_t a = tmem_base + C::TM_DP + buf * 64;
         // k-step kk = the 16 kv columns of elementwise part kk
@@ -866,7 +866,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tma_kv,  // qkv, box row
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == BWD_TMA_WARP) {
-    if (lane == 0) {
+    if (elect_one()) {
       mbar_expect_tx(kv_full, 2 * C::KV_BYTES);
 #pragma unroll
       for (int h2 = 0; h2 < HD / 64; ++h2) {
@@ -910,7 +910,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tma_kv,  // qkv, box row
       mbar_wait(&q_full[st], (t / C::NQ) & 1, 51);
       FX_TM(8);
       tc_fence_after();
-      if (lane == 0) {
+      if (elect_one()) {
         const uint32_t q_lo = q_lo0 + st * (C::Q_BYTES >> 4), do_lo = do_lo0 + st * (C::Q_BYTES >> 4);
         const uint32_t d_st = tmem_base + C::TM_ST + buf * 64, d_dpt = tmem_base + C::TM_DPT + buf * 64;
 #pragma unroll
@@ -938,7 +938,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tma_kv,  // qkv, box row
       mbar_wait(&pt_full[buf], (t / C::NB) & 1, 54);
       FX_TM(10);
       tc_fence_after();
-      if (lane == 0) {
+      if (elect_one()) {
         const uint32_t q_lo = qmn_lo0 + st * (C::Q_BYTES >> 4), do_lo = domn_lo0 + st * (C::Q_BYTES >> 4);
         const uint32_t a_p = tmem_base + C::TM_ST + buf * 64, a_ds = tmem_base + C::TM_DPT + buf * 64;
         const uint32_t d_dv = tmem_base + C::TM_DV, d_dk = tmem_base + C::TM_DK;

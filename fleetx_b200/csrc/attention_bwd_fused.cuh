@@ -33,8 +33,13 @@ struct FusedCfg {
   static constexpr int SMEM_BYTES = OFF_BAR + 256;
   static_assert(OFF_DS % 1024 == 0 && OFF_STG % 1024 == 0, "");
   static constexpr int NB = 2;  // S^T / dP^T buffers
+  // TMEM: S^T[2] | dP^T[2] | dV | dK | dQ | K | V. K and V (bf16, one kv row per lane) are copied into TMEM
+  // once and feed the S^T / dP^T MMAs as A operands from there: shared-memory bandwidth (MMA operand
+  // reads + element-wise loads/stores + TMA + the bulk reduce) is what bounds this kernel, and the two
+  // resident 16 KB tiles would otherwise be re-read for every query tile.
   static constexpr int TM_ST = 0, TM_DPT = NB * 64, TM_DV = 2 * NB * 64, TM_DK = TM_DV + HD, TM_DQ = TM_DK + HD;
-  static constexpr int TMEM_COLS = 512;  // 128 + 128 + 64 + 64 + 2 x 64
+  static constexpr int TM_K = TM_DQ + HD, TM_V = TM_K + 32;
+  static constexpr int TMEM_COLS = 512;  // 128 + 128 + 64 + 64 + 64 + 32 + 32
   static constexpr int EW_BARRIER = 1;   // named barrier of the 512 element-wise threads
 };
 
@@ -58,8 +63,9 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tma_kv,    // qkv, box
   uint64_t* pt_full = bars + 11;    // NB
   uint64_t* acc_full = bars + 13;   // 1
   uint64_t* ds_empty = bars + 14;   // 2 (pair buffers of dS^T in shared memory)
-  uint64_t* dq_full = bars + 16;    // 2 (dQ accumulators in TMEM)
-  uint64_t* dq_empty = bars + 18;   // 2
+  uint64_t* dq_full = bars + 16;    // 1 (dQ accumulator in TMEM)
+  uint64_t* dq_empty = bars + 17;   // 1
+  uint64_t* kvt_full = bars + 18;   // 1 (K, V copied into TMEM)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 20);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -78,6 +84,9 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tma_kv,    // qkv, box
     if (lane == 0) {
       mbar_init(kv_full, 1);
       mbar_init(acc_full, 1);
+      mbar_init(dq_full, 1);
+      mbar_init(dq_empty, BWD_EW_WARPS);
+      mbar_init(kvt_full, 8);
       for (int i = 0; i < C::NQ; ++i) {
         mbar_init(&q_full[i], 1);
         mbar_init(&q_empty[i], 1);
@@ -86,8 +95,6 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tma_kv,    // qkv, box
         mbar_init(&st_full[i], 1);
         mbar_init(&pt_full[i], BWD_EW_WARPS);
         mbar_init(&ds_empty[i], 1);
-        mbar_init(&dq_full[i], 1);
-        mbar_init(&dq_empty[i], BWD_EW_WARPS);
       }
       mbar_fence_init();
     }
@@ -101,7 +108,7 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tma_kv,    // qkv, box
 
   if (warp == BWD_TMA_WARP) {
     // ------------------------------------------------------------------ TMA producer
-    if (lane == 0) {
+    if (elect_one()) {
       const bool drop = p.p_drop > 0.f;
       mbar_expect_tx(kv_full, 2 * C::KV_BYTES);
       tma_load_4d(smem + C::OFF_K, &tma_kv, kv_full, 0, head * 3 + 1, jt * 128, batch);
@@ -122,79 +129,84 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tma_kv,    // qkv, box
     }
   } else if (warp == BWD_MMA_WARP) {
     // ------------------------------------------------------------------ MMA issuer
-    const uint32_t idesc_st = instr_desc_bf16(128, 64, 0, 0);   // S^T, dP^T: both operands K-major
+    FX_T0();
+    const uint32_t idesc_st = instr_desc_bf16(128, 64, 0, 0);   // S^T, dP^T: A (K / V) from TMEM, B (Q / dO) K-major
     const uint32_t idesc_acc = instr_desc_bf16(128, HD, 0, 1);  // dV, dK: B (dO / Q) MN-major
     const uint32_t idesc_dq = instr_desc_bf16(128, HD, 1, 1);   // dQ: A (dS) and B (K) MN-major
-    const uint32_t k_lo = desc_lo(smem_u32(smem + C::OFF_K), 0), v_lo = desc_lo(smem_u32(smem + C::OFF_V), 0);
     const uint32_t kmn_lo = desc_lo(smem_u32(smem + C::OFF_K), 0);  // one 64-wide chunk: LBO unused
     const uint32_t q_lo0 = desc_lo(smem_u32(smem + C::OFF_Q), 0), do_lo0 = desc_lo(smem_u32(smem + C::OFF_DO), 0);
-    const uint32_t ds_lo0 = desc_lo(smem_u32(smem + C::OFF_DS), 0);                 // K-major A of dK
     const uint32_t dsmn_lo0 = desc_lo(smem_u32(smem + C::OFF_DS), C::DS_BYTES);      // MN-major A of dQ: two q chunks
 
     auto issue_st = [&](int t) {
       // S^T/dP^T buffer t % NB was last used by tile t-NB, whose dV MMA has been issued already (the
       // tensor pipe runs MMAs in issue order), after every element-wise warp had finished with it.
       const int buf = t % C::NB, st = t % C::NQ;
+      FX_TM(12);
       mbar_wait(&q_full[st], (t / C::NQ) & 1, 71);
+      FX_TM(8);
       tc_fence_after();
-      if (lane == 0) {
+      if (elect_one()) {
         const uint32_t q_lo = q_lo0 + st * (C::Q_BYTES >> 4), do_lo = do_lo0 + st * (C::Q_BYTES >> 4);
         const uint32_t d_st = tmem_base + C::TM_ST + buf * 64, d_dpt = tmem_base + C::TM_DPT + buf * 64;
 #pragma unroll
         for (int kk = 0; kk < HD / 16; ++kk) {
-          const uint32_t off = (kk * 32) >> 4;
+          const uint32_t off = (kk * 32) >> 4;  // k-step = 16 hd columns: 32 bytes of Q / dO, 8 TMEM columns of K / V
           if (kk == 0) {
-            umma_ss_lo<0>(d_st, k_lo + off, q_lo + off, idesc_st);
-            umma_ss_lo<0>(d_dpt, v_lo + off, do_lo + off, idesc_st);
+            umma_ts_lo<0>(d_st, tmem_base + C::TM_K + kk * 8, q_lo + off, idesc_st);
+            umma_ts_lo<0>(d_dpt, tmem_base + C::TM_V + kk * 8, do_lo + off, idesc_st);
           } else {
-            umma_ss_lo<1>(d_st, k_lo + off, q_lo + off, idesc_st);
-            umma_ss_lo<1>(d_dpt, v_lo + off, do_lo + off, idesc_st);
+            umma_ts_lo<1>(d_st, tmem_base + C::TM_K + kk * 8, q_lo + off, idesc_st);
+            umma_ts_lo<1>(d_dpt, tmem_base + C::TM_V + kk * 8, do_lo + off, idesc_st);
           }
         }
         umma_commit(&st_full[buf]);
       }
       __syncwarp();
+      FX_TM(9);
     };
 
-    mbar_wait(kv_full, 0, 72);
+    mbar_wait(kvt_full, 0, 72);
     issue_st(0);
     for (int t = 0; t < n_q; ++t) {
       if (t + 1 < n_q) issue_st(t + 1);
-      const int buf = t % C::NB, st = t % C::NQ, slot = t & 3;
+      const int buf = t % C::NB, st = t % C::NQ;
       const bool pair_done = (t & 1) || t == n_q - 1;
-      const int pair = t >> 1, dqb = pair & 1;
+      const int pair = t >> 1;
       mbar_wait(&pt_full[buf], (t / C::NB) & 1, 73);
-      if (pair_done) mbar_wait(&dq_empty[dqb], ((pair >> 1) & 1) ^ 1, 74);
+      // one dQ accumulator: pair-1 was drained before the element-wise pass of tile 2·pair+1, i.e. before
+      // the pt_full just waited for, so this never blocks in the steady state
+      if (pair_done) mbar_wait(dq_empty, (pair & 1) ^ 1, 74);
+      FX_TM(10);
       tc_fence_after();
-      if (lane == 0) {
+      if (elect_one()) {
         const uint32_t q_lo = q_lo0 + st * (C::Q_BYTES >> 4), do_lo = do_lo0 + st * (C::Q_BYTES >> 4);
-        const uint32_t a_p = tmem_base + C::TM_ST + buf * 64;
-        const uint32_t a_ds = ds_lo0 + slot * (C::DS_BYTES >> 4);
+        const uint32_t a_p = tmem_base + C::TM_ST + buf * 64, a_ds = tmem_base + C::TM_DPT + buf * 64;
         const uint32_t d_dv = tmem_base + C::TM_DV, d_dk = tmem_base + C::TM_DK;
         // k-step kk = the 16 query columns of element-wise part kk; dV and dK interleaved.
         // Q / dO tiles are the MN-major B operands here (64 hd contiguous per query row).
         umma_ts_lo<2>(d_dv, a_p, do_lo, idesc_acc, t != 0);
-        umma_ss_lo<2>(d_dk, a_ds, q_lo, idesc_acc, t != 0);
+        umma_ts_lo<2>(d_dk, a_ds, q_lo, idesc_acc, t != 0);
 #pragma unroll
         for (int kk = 1; kk < 4; ++kk) {
           umma_ts_lo<1>(d_dv, a_p + kk * 16, do_lo + kk * (2048 >> 4), idesc_acc);
-          umma_ss_lo<1>(d_dk, a_ds + kk * (32 >> 4), q_lo + kk * (2048 >> 4), idesc_acc);
+          umma_ts_lo<1>(d_dk, a_ds + kk * 16, q_lo + kk * (2048 >> 4), idesc_acc);
         }
         umma_commit(&q_empty[st]);
         if (pair_done) {
           // dQ_partial[q pair (128) x hd] = dS[q x kv] · K[kv x hd]: A = the pair's two dS^T tiles read
           // MN-major (64 q contiguous per kv row), k-step = 16 kv rows = 2048 bytes in both operands
           const uint32_t a_mn = dsmn_lo0 + (pair & 1) * (2 * C::DS_BYTES >> 4);
-          const uint32_t d_dq = tmem_base + C::TM_DQ + dqb * 64;
+          const uint32_t d_dq = tmem_base + C::TM_DQ;
           umma_ss_lo<0>(d_dq, a_mn, kmn_lo, idesc_dq);
 #pragma unroll
           for (int kk = 1; kk < 8; ++kk) umma_ss_lo<1>(d_dq, a_mn + kk * (2048 >> 4), kmn_lo + kk * (2048 >> 4), idesc_dq);
-          umma_commit(&dq_full[dqb]);
+          umma_commit(dq_full);
           umma_commit(&ds_empty[pair & 1]);
         }
         if (t == n_q - 1) umma_commit(acc_full);
       }
       __syncwarp();
+      FX_TM(11);
     }
   } else {
     // ------------------------------------------------------------------ element-wise warps
@@ -216,13 +228,35 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tma_kv,    // qkv, box
     const uint32_t stg_row = smem_u32(smem + C::OFF_STG) + r_local * 256;
     float* dq_block0 = dq_acc + ((static_cast<size_t>(batch) * p.nh + head) * (p.s_pad / 128) + jt) * DQACC_BLOCK;
 
+    // K (parts 0) and V (parts 1) rows -> TMEM as bf16 A operands: lane = kv row, 32 columns of packed pairs
+    if (part < 2) {
+      mbar_wait(kv_full, 0, 85);
+      const uint32_t src = smem_u32(smem + (part == 0 ? C::OFF_K : C::OFF_V));
+      uint32_t r[32];
+#pragma unroll
+      for (int c = 0; c < 8; ++c)
+        asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                     : "=r"(r[4 * c]), "=r"(r[4 * c + 1]), "=r"(r[4 * c + 2]), "=r"(r[4 * c + 3])
+                     : "r"(src + sw128_off(r_local, c)));
+      uint32_t lo[16], hi[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) { lo[i] = r[i]; hi[i] = r[16 + i]; }
+      const uint32_t dst = lane_base + (part == 0 ? C::TM_K : C::TM_V);
+      tmem_st_32x16(dst, lo);
+      tmem_st_32x16(dst + 16, hi);
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(kvt_full);
+    }
+
+    FX_T0();
     // Drain dQ accumulator of query pair P (128-row block jt + P) and add it into the global accumulator.
     auto drain_dq = [&](int P, uint32_t bytes) {
-      const int dqb = P & 1;
-      mbar_wait(&dq_full[dqb], (P >> 1) & 1, 80);
+      mbar_wait(dq_full, P & 1, 80);
       tc_fence_after();
       uint32_t r[16];
-      tmem_ld_32x16(lane_base + C::TM_DQ + dqb * 64 + part * 16, r);
+      tmem_ld_32x16(lane_base + C::TM_DQ + part * 16, r);
       tmem_ld_wait();
       tc_fence_before();
       // the previous block's bulk reduce must have finished reading the staging tile
@@ -240,7 +274,7 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tma_kv,    // qkv, box
                      : "memory");
         asm volatile("cp.async.bulk.commit_group;" ::: "memory");
       }
-      if (lane == 0) mbar_arrive(&dq_empty[dqb]);
+      if (lane == 0) mbar_arrive(dq_empty);
     };
 
     // One 128 x 64 tile: p' = 2^(s·sl2 − lse2), P^T = keep·p', dS^T = p'·(keep·dP^T − delta'). DIAG / DROP
@@ -250,15 +284,18 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tma_kv,    // qkv, box
       const int buf = t % C::NB;
       const int q0 = (i0 + t) * 64;
       const int qst = t % C::NQ;
+      FX_T(0);
       // dS^T slot t % 4 belongs to pair buffer (t / 2) % 2: free once the dQ MMA two pairs back has retired
       if ((t & 1) == 0) mbar_wait(&ds_empty[(t >> 1) & 1], ((t >> 2) & 1) ^ 1, 81);
       mbar_wait(&q_full[qst], (t / C::NQ) & 1, 82);   // row statistics and keep bits of this tile have landed
       mbar_wait(&st_full[buf], (t / C::NB) & 1, 83);  // S^T / dP^T are in TMEM
+      FX_T(1);
       tc_fence_after();
       uint32_t rs[16], rp[16];
       tmem_ld_32x16(lane_base + C::TM_ST + buf * 64 + part * 16, rs);
       tmem_ld_32x16(lane_base + C::TM_DPT + buf * 64 + part * 16, rp);
       tmem_ld_wait();
+      FX_T(2);
 
       const int qh = q0 + part * 16;  // first query column of this thread's 16
       const float* stat = reinterpret_cast<const float*>(smem + C::OFF_STAT + qst * 512) + part * 16;
@@ -292,9 +329,11 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tma_kv,    // qkv, box
           pk_ds[i >> 1] = pack_bf16(f2_lo(ds), f2_hi(ds));
         }
       }
-      // P^T (bf16 pairs) goes back into the first 8 of this thread's own 16 S^T columns; dS^T goes to the
-      // shared-memory tile both the dK MMA (K-major) and the dQ MMA (MN-major) read
+      FX_T(3);
+      // P^T / dS^T (bf16 pairs) go back into the first 8 of this thread's own 16 S^T / dP^T columns (A
+      // operands of the dV / dK MMAs); dS^T also goes to shared memory, where the dQ MMA reads it MN-major
       tmem_st_32x8(lane_base + C::TM_ST + buf * 64 + part * 16, pk_p);
+      tmem_st_32x8(lane_base + C::TM_DPT + buf * 64 + part * 16, pk_ds);
       const uint32_t ds_tile = ds_row + (t & 3) * C::DS_BYTES;
       st_shared_v4(ds_tile + ds_c0, pk_ds[0], pk_ds[1], pk_ds[2], pk_ds[3]);
       st_shared_v4(ds_tile + ds_c1, pk_ds[4], pk_ds[5], pk_ds[6], pk_ds[7]);
@@ -303,6 +342,7 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tma_kv,    // qkv, box
       fence_async_smem();
       __syncwarp();
       if (lane == 0) mbar_arrive(&pt_full[buf]);
+      FX_T(5);
     };
 
     for (int t = 0; t < n_q; ++t) {

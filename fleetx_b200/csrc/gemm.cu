@@ -196,7 +196,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
 
   if (warp == TMA_WARP) {
     // ---------------------------------------------------------------- TMA producer
-    if (lane == 0) {
+    if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
@@ -250,7 +250,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
       for (int kb = 0; kb < p.num_kb; ++kb) {
         mbar_wait(&full[stage], phase, 3);
         tc_fence_after();
-        if (lane == 0) {
+        if (elect_one()) {
           const uint32_t a_lo = a_lo0 + stage * (C::STAGE_BYTES >> 4), b_lo = b_lo0 + stage * (C::STAGE_BYTES >> 4);
           umma_ss_lo<2>(tmem_d, a_lo, b_lo, idesc, kb != 0);
           umma_ss_lo<1>(tmem_d, a_lo + a_k, b_lo + b_k, idesc);

@@ -16,6 +16,10 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
 }
 __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31; }
 
+// One lane of a converged warp. Use THIS, not `lane == 0`, around tcgen05.mma / tcgen05.commit / TMA
+// issue: those are uniform-datapath instructions, and inside an `if (lane == 0)` region the compiler
+// cannot prove a single active thread, so it wraps every one of them in an ELECT + BRA.U.ANY retry loop
+// (≈9 instructions per MMA instead of ≈2; the issuing thread then cannot keep up with N = 64 MMAs).
 __device__ __forceinline__ bool elect_one() {
   uint32_t pred = 0;
   asm volatile(
