@@ -3,23 +3,24 @@
 //
 // The split pair recomputes S and dP (and their exponentials) twice: once per KV tile for dK/dV, once per
 // Q tile for dQ. Here the CTA that owns a 128-row KV tile also produces the dQ contribution of that tile:
+//   once per CTA:             K, V rows -> TMEM (bf16): A operands of the S^T / dP^T MMAs from then on
 //   per 64-row query tile t:  S^T = K·Q^T, dP^T = V·dO^T           (tcgen05, into TMEM)
-//                             P^T -> TMEM (bf16), dS^T -> shared memory (bf16, 128B-swizzled)
-//                             dV += P^T·dO (A from TMEM), dK += dS^T·Q (A from shared memory)
-//   per pair of query tiles:  dQ_partial[128 q x 64] = dS·K — the SAME shared-memory bytes of dS^T read as
-//                             an MN-major A operand — into a double-buffered TMEM accumulator, drained by
-//                             the element-wise warps into a staging tile and added into a fp32 global
-//                             accumulator with ONE bulk reduce (cp.reduce.async.bulk .add.f32, 32 KB).
-// The bulk reduce runs at ~5 TB/s on B200 (tools/micro/bulk_red.cu), 1.1 GB per bench step, hidden under
-// the math. A small kernel then scales the accumulator and writes bf16 dQ into the packed dqkv tensor.
-// fp32 adds from different KV-tile CTAs arrive in no fixed order: dQ can differ in the last bf16 bit from
-// run to run (dK, dV are exact). FX_ATTN_BWD=split selects the deterministic two-kernel path.
+//                             P^T, dS^T -> TMEM (bf16); dS^T also -> shared memory (bf16, 128B-swizzled)
+//                             dV += P^T·dO, dK += dS^T·Q           (A from TMEM)
+//   per pair of query tiles:  dQ_partial[128 q x 64] = dS·K — the shared-memory bytes of dS^T read as an
+//                             MN-major A operand — into a TMEM accumulator, drained by the element-wise
+//                             warps and added into a fp32 global accumulator with red.global.add.v4.f32.
+// The L2 atomic path takes ~26 B/clk per SM (5.6 TB/s chip-wide; tools/micro/bulk_red.cu, red_v4.cu) for
+// the 1.1 GB of dQ partials of a bench step. A small kernel then scales the accumulator and writes bf16 dQ
+// into the packed dqkv tensor. fp32 adds from different KV-tile CTAs arrive in no fixed order: dQ can
+// differ in the last bf16 bit from run to run (dK, dV are exact). FX_ATTN_BWD=split selects the
+// deterministic two-kernel path.
 
 struct FusedCfg {
   static constexpr int HD = 64;
   static constexpr int KV_BYTES = 128 * HD * 2;  // K / V tile, resident
   static constexpr int Q_BYTES = 64 * HD * 2;    // Q / dO tile (64 rows)
-  static constexpr int NQ = 4;                   // Q / dO ring depth
+  static constexpr int NQ = 6;                   // Q / dO ring depth
   static constexpr int DS_BYTES = 128 * 128;     // dS^T tile: [128 kv rows][64 q] bf16
   static constexpr int OFF_K = 0;
   static constexpr int OFF_V = KV_BYTES;
@@ -28,10 +29,10 @@ struct FusedCfg {
   static constexpr int OFF_MASK = OFF_DO + NQ * Q_BYTES;  // [NQ][64 queries][4 words]
   static constexpr int OFF_STAT = OFF_MASK + NQ * 1024;   // [NQ][-lse2 | -delta'][64 queries] fp32
   static constexpr int OFF_DS = OFF_STAT + NQ * 512;      // 4 tiles = 2 pair buffers of 2 x 16 KB
-  static constexpr int OFF_STG = OFF_DS + 4 * DS_BYTES;   // dQ staging: [128 q][64] fp32, 16-byte chunks XOR-swizzled
-  static constexpr int OFF_BAR = OFF_STG + 128 * 64 * 4;
+  static constexpr int OFF_BAR = OFF_DS + 4 * DS_BYTES;
+  static_assert(OFF_BAR + 256 <= 227 * 1024, "");
   static constexpr int SMEM_BYTES = OFF_BAR + 256;
-  static_assert(OFF_DS % 1024 == 0 && OFF_STG % 1024 == 0, "");
+  static_assert(OFF_DS % 1024 == 0, "");
   static constexpr int NB = 2;  // S^T / dP^T buffers
   // TMEM: S^T[2] | dP^T[2] | dV | dK | dQ | K | V. K and V (bf16, one kv row per lane) are copied into TMEM
   // once and feed the S^T / dP^T MMAs as A operands from there: shared-memory bandwidth (MMA operand
@@ -40,7 +41,6 @@ struct FusedCfg {
   static constexpr int TM_ST = 0, TM_DPT = NB * 64, TM_DV = 2 * NB * 64, TM_DK = TM_DV + HD, TM_DQ = TM_DK + HD;
   static constexpr int TM_K = TM_DQ + HD, TM_V = TM_K + 32;
   static constexpr int TMEM_COLS = 512;  // 128 + 128 + 64 + 64 + 64 + 32 + 32
-  static constexpr int EW_BARRIER = 1;   // named barrier of the 512 element-wise threads
 };
 
 // floats per (batch, head, 128-query block) in the dQ accumulator
@@ -57,16 +57,17 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tma_kv,    // qkv, box
   extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::OFF_BAR);
   uint64_t* kv_full = bars;         // 1
-  uint64_t* q_full = bars + 1;      // NQ
-  uint64_t* q_empty = bars + 5;     // NQ
-  uint64_t* st_full = bars + 9;     // NB
-  uint64_t* pt_full = bars + 11;    // NB
-  uint64_t* acc_full = bars + 13;   // 1
-  uint64_t* ds_empty = bars + 14;   // 2 (pair buffers of dS^T in shared memory)
-  uint64_t* dq_full = bars + 16;    // 1 (dQ accumulator in TMEM)
-  uint64_t* dq_empty = bars + 17;   // 1
-  uint64_t* kvt_full = bars + 18;   // 1 (K, V copied into TMEM)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 20);
+  uint64_t* q_full = bars + 1;                 // NQ
+  uint64_t* q_empty = q_full + C::NQ;          // NQ
+  uint64_t* st_full = q_empty + C::NQ;         // NB
+  uint64_t* pt_full = st_full + 2;             // NB
+  uint64_t* acc_full = pt_full + 2;            // 1
+  uint64_t* ds_empty = acc_full + 1;           // 2 (pair buffers of dS^T in shared memory)
+  uint64_t* dq_full = ds_empty + 2;            // 1 (dQ accumulator in TMEM)
+  uint64_t* dq_empty = dq_full + 1;            // 1
+  uint64_t* kvt_full = dq_empty + 1;           // 1 (K, V copied into TMEM)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(kvt_full + 1);
+  static_assert((1 + 2 * C::NQ + 2 + 2 + 1 + 2 + 1 + 1 + 1) * 8 + 4 <= 256, "barrier area");
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int jt = blockIdx.x;  // KV tile; low tiles walk the most query tiles and start first
@@ -113,9 +114,12 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tma_kv,    // qkv, box
       mbar_expect_tx(kv_full, 2 * C::KV_BYTES);
       tma_load_4d(smem + C::OFF_K, &tma_kv, kv_full, 0, head * 3 + 1, jt * 128, batch);
       tma_load_4d(smem + C::OFF_V, &tma_kv, kv_full, 0, head * 3 + 2, jt * 128, batch);
+      FX_T0();
       for (int t = 0; t < n_q; ++t) {
         const int st = t % C::NQ;
+        FX_TM(15);
         mbar_wait(&q_empty[st], ((t / C::NQ) & 1) ^ 1, 70);
+        FX_TM(14);
         mbar_expect_tx(&q_full[st], 2 * C::Q_BYTES + 512 + (drop ? 1024 : 0));
         if (drop)  // keep bits of query rows q0 .. q0+63 for this CTA's 128 kv columns (4 words per row)
           tma_load_2d(smem + C::OFF_MASK + st * 1024, &tma_mask, &q_full[st], 4 * jt,
@@ -143,7 +147,7 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tma_kv,    // qkv, box
       const int buf = t % C::NB, st = t % C::NQ;
       FX_TM(12);
       mbar_wait(&q_full[st], (t / C::NQ) & 1, 71);
-      FX_TM(8);
+      FX_TM(t < 2 ? 13 : 8);
       tc_fence_after();
       if (elect_one()) {
         const uint32_t q_lo = q_lo0 + st * (C::Q_BYTES >> 4), do_lo = do_lo0 + st * (C::Q_BYTES >> 4);
@@ -173,9 +177,6 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tma_kv,    // qkv, box
       const bool pair_done = (t & 1) || t == n_q - 1;
       const int pair = t >> 1;
       mbar_wait(&pt_full[buf], (t / C::NB) & 1, 73);
-      // one dQ accumulator: pair-1 was drained before the element-wise pass of tile 2·pair+1, i.e. before
-      // the pt_full just waited for, so this never blocks in the steady state
-      if (pair_done) mbar_wait(dq_empty, (pair & 1) ^ 1, 74);
       FX_TM(10);
       tc_fence_after();
       if (elect_one()) {
@@ -192,6 +193,15 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tma_kv,    // qkv, box
           umma_ts_lo<1>(d_dk, a_ds + kk * 16, q_lo + kk * (2048 >> 4), idesc_acc);
         }
         umma_commit(&q_empty[st]);
+      }
+      __syncwarp();
+      if (pair_done) {
+        // one dQ accumulator: pair-1 is drained right after the element-wise pass of tile 2·pair+1, whose
+        // pt_full was waited for above; the dV / dK MMAs just issued cover that short gap
+        mbar_wait(dq_empty, (pair & 1) ^ 1, 74);
+        tc_fence_after();
+      }
+      if (elect_one()) {
         if (pair_done) {
           // dQ_partial[q pair (128) x hd] = dS[q x kv] · K[kv x hd]: A = the pair's two dS^T tiles read
           // MN-major (64 q contiguous per kv row), k-step = 16 kv rows = 2048 bytes in both operands
@@ -223,11 +233,6 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tma_kv,    // qkv, box
     const uint64_t sl2_2 = f2_pack(sl2, sl2);
     const uint32_t ds_row = smem_u32(smem + C::OFF_DS);  // my 32 bytes of a dS^T tile: chunks 2·part, 2·part+1 of row r_local
     const uint32_t ds_c0 = sw128_off(r_local, 2 * part), ds_c1 = sw128_off(r_local, 2 * part + 1);
-    // dQ staging: thread (lane = query row of the pair) owns hd columns [16·part, +16) = 16-byte chunks
-    // 4·part .. 4·part+3 of its 256-byte row, XOR-swizzled with the row so the stores spread over the banks
-    const uint32_t stg_row = smem_u32(smem + C::OFF_STG) + r_local * 256;
-    float* dq_block0 = dq_acc + ((static_cast<size_t>(batch) * p.nh + head) * (p.s_pad / 128) + jt) * DQACC_BLOCK;
-
     // K (parts 0) and V (parts 1) rows -> TMEM as bf16 A operands: lane = kv row, 32 columns of packed pairs
     if (part < 2) {
       mbar_wait(kv_full, 0, 85);
@@ -251,30 +256,32 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tma_kv,    // qkv, box
     }
 
     FX_T0();
-    // Drain dQ accumulator of query pair P (128-row block jt + P) and add it into the global accumulator.
-    auto drain_dq = [&](int P, uint32_t bytes) {
+    // Drain the dQ accumulator of query pair P (128-row block jt + P) and add it into the global fp32
+    // accumulator with vector reductions straight from registers (red.global.add.v4.f32). The L2 atomic path
+    // takes ~26 B/clk per SM whichever unit feeds it (tools/micro/bulk_red.cu, red_v4.cu); a TMA bulk reduce
+    // of the block was tried first and queues in front of the tile loads for ~1.3k cycles, which starves the
+    // MMA warp; four dedicated reducer warps were tried too and cost more in registers than they hide. The
+    // accumulator block is laid out [16 column groups][128 rows][4]: a warp's 32 rows make one contiguous
+    // 512-byte access.
+    float* dq_block0 = dq_acc + ((static_cast<size_t>(batch) * p.nh + head) * (p.s_pad / 128) + jt) * DQACC_BLOCK +
+                       (part * 4 * 128 + r_local) * 4;
+    auto drain_dq = [&](int P, bool both_tiles) {
       mbar_wait(dq_full, P & 1, 80);
       tc_fence_after();
       uint32_t r[16];
       tmem_ld_32x16(lane_base + C::TM_DQ + part * 16, r);
       tmem_ld_wait();
       tc_fence_before();
-      // the previous block's bulk reduce must have finished reading the staging tile
-      if (threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-      named_bar_sync_fwd(C::EW_BARRIER, BWD_EW_WARPS * 32);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(dq_empty);  // the accumulator is free again before the reductions go out
+      if (both_tiles || r_local < 64) {      // rows 64..127 are stale when the pair has a single tile
+        float* dst = dq_block0 + static_cast<size_t>(P) * DQACC_BLOCK;
 #pragma unroll
-      for (int g = 0; g < 4; ++g)
-        st_shared_v4(stg_row + (((part * 4 + g) ^ (r_local & 15)) << 4), r[4 * g], r[4 * g + 1], r[4 * g + 2], r[4 * g + 3]);
-      fence_async_smem();
-      named_bar_sync_fwd(C::EW_BARRIER, BWD_EW_WARPS * 32);
-      if (threadIdx.x == 0) {
-        asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;" ::"l"(
-                         dq_block0 + static_cast<size_t>(P) * DQACC_BLOCK),
-                     "r"(smem_u32(smem + C::OFF_STG)), "r"(bytes)
-                     : "memory");
-        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        for (int g = 0; g < 4; ++g)
+          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + g * 128 * 4), "r"(r[4 * g]),
+                       "r"(r[4 * g + 1]), "r"(r[4 * g + 2]), "r"(r[4 * g + 3])
+                       : "memory");
       }
-      if (lane == 0) mbar_arrive(dq_empty);
     };
 
     // One 128 x 64 tile: p' = 2^(s·sl2 − lse2), P^T = keep·p', dS^T = p'·(keep·dP^T − delta'). DIAG / DROP
@@ -289,7 +296,7 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tma_kv,    // qkv, box
       if ((t & 1) == 0) mbar_wait(&ds_empty[(t >> 1) & 1], ((t >> 2) & 1) ^ 1, 81);
       mbar_wait(&q_full[qst], (t / C::NQ) & 1, 82);   // row statistics and keep bits of this tile have landed
       mbar_wait(&st_full[buf], (t / C::NB) & 1, 83);  // S^T / dP^T are in TMEM
-      FX_T(1);
+      FX_T(t == 0 ? 6 : 1);
       tc_fence_after();
       uint32_t rs[16], rp[16];
       tmem_ld_32x16(lane_base + C::TM_ST + buf * 64 + part * 16, rs);
@@ -346,10 +353,6 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tma_kv,    // qkv, box
     };
 
     for (int t = 0; t < n_q; ++t) {
-      // The dQ block of pair P is drained before tile 2P+3: its MMAs were issued after tile 2P+1 and sit
-      // behind that tile's dV / dK MMAs in the tensor pipe, so one full tile of element-wise work later
-      // they have retired and the drain does not wait.
-      if ((t & 1) == 1 && t >= 3) drain_dq((t >> 1) - 1, 128 * 64 * 4);
       const bool diag = (t < 2);  // the first two 64-row query tiles straddle the diagonal
       if (drop) {
         if (diag) tile(t, std::true_type{}, std::true_type{});
@@ -358,12 +361,16 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tma_kv,    // qkv, box
         if (diag) tile(t, std::true_type{}, std::false_type{});
         else tile(t, std::false_type{}, std::false_type{});
       }
+      // The dQ block of pair P is drained after tile 2P+3: its MMAs were issued after tile 2P+1, two tiles
+      // of element-wise work ago, so the drain does not wait; and it comes right AFTER this tile's release
+      // (mbarrier arrive = membar), so the reductions have a whole tile to land before the next membar
+      // would have to wait for them.
+      if ((t & 1) == 1 && t >= 3) drain_dq((t >> 1) - 1, true);
     }
-    // what the loop has not drained: the pair before the last when n_q is odd (its drain slot would have
-    // been tile n_q), and the last pair — a single tile when n_q is odd (rows 64..127 of the accumulator
-    // are then stale and are not added)
-    if ((n_q & 1) == 1 && n_q >= 3) drain_dq((n_q >> 1) - 1, 128 * 64 * 4);
-    drain_dq((n_q - 1) >> 1, (n_q & 1) ? 64 * 64 * 4 : 128 * 64 * 4);
+    // what the loop has not drained: the pair before the last when n_q is odd (its slot would have been
+    // tile n_q), and the last pair — a single tile when n_q is odd
+    if ((n_q & 1) == 1 && n_q >= 3) drain_dq((n_q >> 1) - 1, true);
+    drain_dq((n_q - 1) >> 1, (n_q & 1) == 0);
 
     // dV = P_drop^T · dO, dK = scale * dS^T · Q; this warp drains columns [part*16, +16)
     mbar_wait(acc_full, 0, 84);
@@ -371,8 +378,7 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tma_kv,    // qkv, box
     __nv_bfloat16* base = p.dqkv + ((static_cast<size_t>(batch) * p.s + kv) * p.nh + head) * (3 * HD) + part * (HD / 4);
     drain_scaled<HD / 4>(lane_base + C::TM_DK + part * (HD / 4), base + HD, p.scale, kv < p.s);
     drain_scaled<HD / 4>(lane_base + C::TM_DV + part * (HD / 4), base + 2 * HD, 1.0f, kv < p.s);
-    // the staging tile must outlive the last bulk reduce, and its adds must have landed before exit
-    if (threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    FX_T(7);
   }
 
   tc_fence_before();
@@ -380,8 +386,8 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tma_kv,    // qkv, box
   if (warp == BWD_MMA_WARP) tmem_dealloc<C::TMEM_COLS>(tmem_base);
 }
 
-// dQ accumulator (fp32, 16-byte chunks XOR-swizzled per row as the staging tile left them) -> scale ->
-// bf16 into the q slot of the packed dqkv tensor. One thread per 8 hd columns.
+// dQ accumulator (fp32, per 128-row block [16 column groups][128 rows][4]) -> scale -> bf16 into the q
+// slot of the packed dqkv tensor. One thread per 8 hd columns.
 __global__ void __launch_bounds__(256)
 attn_dq_convert_kernel(const float* __restrict__ dq_acc, __nv_bfloat16* __restrict__ dqkv, int b, int s, int nh,
                        int s_pad, float scale) {
@@ -394,9 +400,8 @@ attn_dq_convert_kernel(const float* __restrict__ dq_acc, __nv_bfloat16* __restri
   const size_t bh = rowi / s_pad;
   if (row >= s) return;
   const int head = static_cast<int>(bh % nh), batch = static_cast<int>(bh / nh);
-  const float4* src = reinterpret_cast<const float4*>(dq_acc + rowi * 64);
-  const int sw = row & 15;  // row inside its 128-row block, mod 16
-  const float4 x = __ldg(src + ((2 * c8) ^ sw)), y = __ldg(src + ((2 * c8 + 1) ^ sw));
+  const float4* blk = reinterpret_cast<const float4*>(dq_acc + (bh * (s_pad / 128) + row / 128) * DQACC_BLOCK);
+  const float4 x = __ldg(blk + (2 * c8) * 128 + (row & 127)), y = __ldg(blk + (2 * c8 + 1) * 128 + (row & 127));
   uint4 o = make_uint4(pack_bf16(x.x * scale, x.y * scale), pack_bf16(x.z * scale, x.w * scale),
                        pack_bf16(y.x * scale, y.y * scale), pack_bf16(y.z * scale, y.w * scale));
   *reinterpret_cast<uint4*>(dqkv + ((static_cast<size_t>(batch) * s + row) * nh + head) * 192 + c8 * 8) = o;

@@ -43,8 +43,8 @@ int main() {
   cudaEventCreate(&e0);
   cudaEventCreate(&e1);
   for (int mode = 0; mode < 2; ++mode)
-    for (int grid : {148, 296, 592}) {
-      const int iters = static_cast<int>((1140ull << 20) / CHUNK / grid);  // ~1.14 GB total
+    for (int grid : {1, 16, 148, 592}) {
+      const int iters = grid < 148 ? 2000 : static_cast<int>((1140ull << 20) / CHUNK / grid);  // ~1.14 GB total at full grids
       red_kernel<CHUNK><<<grid, 128, CHUNK>>>(d, tiles, iters, mode);
       cudaDeviceSynchronize();
       cudaEventRecord(e0);

@@ -28,5 +28,5 @@ for i, n in enumerate(names):
     print(f"{n:18s} {buf[i] / tiles:9.1f} cycles/tile")
     tot += buf[i] / tiles
 print("sum", tot)
-for i, n in ((12, "mma: loop/other"), (8, "mma: wait q_full"), (9, "mma: issue ST/DPT"), (10, "mma: wait pt_full"), (11, "mma: issue dV/dK")):
+for i, n in ((14, "tma: wait q_empty"), (15, "tma: issue"), (6, "ew: first wait"), (7, "ew: epilogue"), (13, "mma: first q_full"), (12, "mma: loop/other"), (8, "mma: wait q_full"), (9, "mma: issue ST/DPT"), (10, "mma: wait pt_full"), (11, "mma: issue dV/dK")):
     print(f"{n:18s} {buf[i] / tiles:9.1f} cycles/tile")
