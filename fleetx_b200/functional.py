@@ -59,6 +59,9 @@ class LayerMeta:
     # parity-test hooks: injected keep masks for dropout1 / dropout2 (uint8 [T, h])
     mask_h1: Optional[torch.Tensor] = None
     mask_h2: Optional[torch.Tensor] = None
+    # activation recompute (hybrid_model.py:332-335 'core_attn', :537-539 'full_attn', :406-408 'full'):
+    # None keeps every activation; otherwise the named part of the forward is re-run inside backward
+    recompute: Optional[str] = None
 
 
 import os as _os
@@ -229,6 +232,53 @@ def decoder_layer_bwd(dout: torch.Tensor, saved: dict, P: LayerParams, M: LayerM
     return dx.view(b, s, h), g
 
 
+RECOMPUTE_GRANULARITIES = ("full", "full_attn", "core_attn")
+
+
+def prune_saved(saved: dict, M: LayerMeta) -> dict:
+    """Drop what `M.recompute` says backward will rebuild. Dropout needs no RNG state to be stashed: every
+    mask is a pure function of the (seed, offset) pairs in M (the reference restores the tracker state
+    instead, hybrid_model.py:406-408 via paddle recompute's preserve_rng_state)."""
+    if M.recompute is None:
+        return saved
+    if M.recompute == "full":        # the whole layer is re-run: keep the input only
+        return dict(x=saved["x"], shape=saved["shape"])
+    keep = dict(saved)
+    for k in ("ctx", "lse", "attn_mask"):   # 'core_attn': scores / softmax / PV are re-run from q, k, v
+        keep[k] = None
+    if M.recompute == "full_attn":   # the attention block is re-run from its input: qkv goes too
+        keep["qkv"] = None
+    return keep
+
+
+def rebuild_saved(saved: dict, P: LayerParams, M: LayerMeta, group) -> dict:
+    """Inverse of prune_saved, run at the start of backward: same kernels, same (seed, offset) pairs, so
+    the rebuilt activations are the forward's bit for bit."""
+    if M.recompute is None:
+        return saved
+    b, s, h = saved["shape"]
+    if M.recompute == "full":
+        return decoder_layer_fwd(saved["x"].view(b, s, h), P, M, group)[1]
+    full = dict(saved)
+    if full["qkv"] is None:
+        attn_in = full["ln1"] if M.normalize_before else full["x"]
+        full["qkv"] = ops.gemm(attn_in, P.qkv_w, epilogue=FX_EPI_BIAS, bias=P.qkv_b)
+    ctx, full["lse"], full["attn_mask"] = ops.attn_causal_fwd(full["qkv"].view(b, s, -1), M.nh_local, M.hd,
+                                                               M.hd ** -0.5, M.p_attn, *M.rng_attn)
+    full["ctx"] = ctx.view(b * s, -1)
+    return full
+
+
+def saved_bytes(saved: dict) -> int:
+    """Bytes of activation memory a `saved` dict pins between forward and backward (distinct buffers)."""
+    seen, n = set(), 0
+    for v in saved.values():
+        if isinstance(v, torch.Tensor) and v.data_ptr() not in seen:
+            seen.add(v.data_ptr())
+            n += v.numel() * v.element_size()
+    return n
+
+
 _GRAD_ORDER = ("norm1_w", "norm1_b", "qkv_w", "qkv_b", "out_w", "out_b",
                "norm2_w", "norm2_b", "lin1_w", "lin1_b", "lin2_w", "lin2_b")
 
@@ -239,13 +289,16 @@ class DecoderLayerFunction(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, meta, group, *params):
         P = LayerParams(*params)
+        if meta.recompute is not None and meta.recompute not in RECOMPUTE_GRANULARITIES:
+            raise ValueError(f"recompute_granularity must be one of {RECOMPUTE_GRANULARITIES}, got {meta.recompute!r}")
         out, saved = decoder_layer_fwd(x, P, meta, group)
-        ctx.saved, ctx.P, ctx.meta, ctx.group = saved, P, meta, group
+        ctx.saved, ctx.P, ctx.meta, ctx.group = prune_saved(saved, meta), P, meta, group
         return out
 
     @staticmethod
     def backward(ctx, dout):
-        dx, g = decoder_layer_bwd(dout.contiguous(), ctx.saved, ctx.P, ctx.meta, ctx.group)
+        saved = rebuild_saved(ctx.saved, ctx.P, ctx.meta, ctx.group)
+        dx, g = decoder_layer_bwd(dout.contiguous(), saved, ctx.P, ctx.meta, ctx.group)
         ctx.saved = None
         return (dx, None, None) + tuple(g[k] for k in _GRAD_ORDER)
 
@@ -322,16 +375,25 @@ class CausalSelfAttentionFunction(torch.autograd.Function):
     """core_attn on the packed qkv_proj output (hybrid_model.py:165-186, 268-298)."""
 
     @staticmethod
-    def forward(ctx, qkv, nh_local, hd, p_drop, seed, offset):
+    def forward(ctx, qkv, nh_local, hd, p_drop, seed, offset, recompute=False):
         out, lse, mask = ops.attn_causal_fwd(qkv, nh_local, hd, hd ** -0.5, p_drop, seed, offset)
-        ctx.save_for_backward(qkv, out, lse)
-        ctx.mask = mask
-        ctx.cfg = (nh_local, hd, p_drop)
+        if recompute:  # 'core_attn' recompute (hybrid_model.py:332-335): keep q, k, v only
+            ctx.save_for_backward(qkv)
+            ctx.mask = None
+        else:
+            ctx.save_for_backward(qkv, out, lse)
+            ctx.mask = mask
+        ctx.cfg = (nh_local, hd, p_drop, seed, offset, recompute)
         return out
 
     @staticmethod
     def backward(ctx, dout):
-        qkv, out, lse = ctx.saved_tensors
-        nh_local, hd, p_drop = ctx.cfg
-        dqkv = ops.attn_causal_bwd(dout.contiguous(), qkv, out, lse, ctx.mask, nh_local, hd, hd ** -0.5, p_drop)
-        return dqkv, None, None, None, None, None
+        nh_local, hd, p_drop, seed, offset, recompute = ctx.cfg
+        if recompute:
+            (qkv,) = ctx.saved_tensors
+            out, lse, mask = ops.attn_causal_fwd(qkv, nh_local, hd, hd ** -0.5, p_drop, seed, offset)
+        else:
+            qkv, out, lse = ctx.saved_tensors
+            mask = ctx.mask
+        dqkv = ops.attn_causal_bwd(dout.contiguous(), qkv, out, lse, mask, nh_local, hd, hd ** -0.5, p_drop)
+        return dqkv, None, None, None, None, None, None

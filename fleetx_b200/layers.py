@@ -160,7 +160,9 @@ class MultiHeadAttention(nn.Module):
         if p > 0:
             with get_rng_state_tracker().rng_state("local_seed"):  # :280
                 seed, offset = get_rng_state_tracker().draw()
-        out = Fn.CausalSelfAttentionFunction.apply(mix.contiguous(), self.num_heads, self.head_dim, p, seed, offset)
+        recompute = self.use_recompute and self.recompute_granularity == "core_attn" and self.training  # :332-335
+        out = Fn.CausalSelfAttentionFunction.apply(mix.contiguous(), self.num_heads, self.head_dim, p, seed, offset,
+                                                   recompute)
         return self.out_proj(out)
 
 
@@ -229,9 +231,12 @@ class TransformerDecoderLayer(nn.Module):
             rng_h1 = tracker.draw("global_seed")
         if p2 > 0 and self._inject_mask2 is None:
             rng_h2 = tracker.draw("global_seed")
+        # use_recompute / recompute_granularity as in the reference (hybrid_model.py:332-335, 406-408,
+        # 537-539): only in training, and only the granularity named
+        recompute = self.recompute_granularity if (self.use_recompute and train) else None
         return Fn.LayerMeta(nh_local=self.self_attn.num_heads, hd=self.self_attn.head_dim, p_attn=p_attn,
                             p_hidden1=p1, p_hidden2=p2, normalize_before=self.normalize_before,
-                            rng_attn=rng_attn, rng_h1=rng_h1, rng_h2=rng_h2,
+                            rng_attn=rng_attn, rng_h1=rng_h1, rng_h2=rng_h2, recompute=recompute,
                             mask_h1=self._inject_mask1 if p1 > 0 else None,
                             mask_h2=self._inject_mask2 if p2 > 0 else None)
 

@@ -128,7 +128,11 @@ size_t fx_attn_dropout_mask_bytes(int b, int s, int nh);
 int fx_attn_causal_fwd(void* stream, const void* qkv, void* out, float* lse, void* dropout_mask, int b,
                        int s, int nh, int hd, float scale, float p_drop, uint64_t seed, uint64_t offset);
 size_t fx_attn_causal_bwd_workspace_bytes(int b, int s, int nh, int hd);
-/* dqkv bf16, same packed layout as qkv, fully overwritten. dropout_mask: what the forward wrote. */
+/* dqkv bf16, same packed layout as qkv, fully overwritten. dropout_mask: what the forward wrote.
+ * hd == 64 runs ONE kernel that produces dK, dV and adds the dQ contribution of each KV tile into an
+ * fp32 accumulator in the workspace (L2 reductions; their order is not fixed, so dQ may differ in the
+ * last bf16 bit between runs — dK, dV are exact). With FX_ATTN_BWD=split in the environment, and always
+ * for hd == 128, the deterministic pair of kernels (dK/dV, then dQ) runs instead. */
 int fx_attn_causal_bwd(void* stream, const void* dout, const void* qkv, const void* out,
                        const float* lse, const void* dropout_mask, void* dqkv, void* workspace, int b,
                        int s, int nh, int hd, float scale, float p_drop);

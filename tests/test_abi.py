@@ -30,7 +30,9 @@ def test_host_side_helpers_and_argument_validation():
     assert lib.fx_layernorm_bwd_workspace_bytes(16384, 2048) == 592 * 2 * 2048 * 4
     assert lib.fx_layernorm_bwd_workspace_bytes(10, 128) == 10 * 2 * 128 * 4
     assert lib.fx_layernorm_bwd_workspace_bytes(0, 128) == 0
-    assert lib.fx_attn_causal_bwd_workspace_bytes(2, 100, 4, 64) == 2 * (2 * 4 * 128 * 4)
+    # head_dim 64: -lse2, -delta' and the fp32 dQ accumulator [b, nh, s_pad, 64]; head_dim 128: the two rows only
+    assert lib.fx_attn_causal_bwd_workspace_bytes(2, 100, 4, 64) == (2 + 64) * (2 * 4 * 128 * 4)
+    assert lib.fx_attn_causal_bwd_workspace_bytes(2, 100, 4, 128) == 2 * (2 * 4 * 128 * 4)
     assert lib.fx_colsum_workspace_bytes(0, 8) == 0
     assert lib.fx_attn_dropout_mask_bytes(2, 100, 3) == 2 * 3 * 100 * 4 * 4  # 1 bit per (row, col), cols padded to 128
     # bad arguments are rejected before any CUDA call, with a message

@@ -151,3 +151,77 @@ def test_standalone_parallel_linears_and_attention_module():
     assert rel_err(out, ref) < TOL
     with pytest.raises(NotImplementedError):
         mha(q.cuda(), use_cache=True)
+
+
+@pytest.mark.parametrize("granularity", ["full", "full_attn", "core_attn"])
+@pytest.mark.parametrize("hd128", [False, True])
+def test_layer_recompute_matches_plain(granularity, hd128):
+    """use_recompute (hybrid_model.py:332-335 core_attn, :537-539 full_attn, :406-408 full): the re-run
+    forward must rebuild the dropped activations exactly (same kernels, same Philox (seed, offset)), so
+    outputs are bit-identical and gradients differ at most by the last bf16 bit of dQ (head_dim 64: the
+    single-kernel attention backward adds dQ partials in no fixed order), and fewer bytes stay pinned."""
+    from fleetx_b200 import functional as Fn
+    from fleetx_b200.rng import set_seed
+    from fleetx_b200.selfcheck import layer_from_oracle_params
+
+    b, s, h, f = 2, 256, 256, 1024
+    nh = 2 if hd128 else 4
+    cfg = O.LayerConfig(d_model=h, nhead=nh, dim_feedforward=f, dropout=0.1)
+    params, x, dy = _setup(cfg, b, s)
+
+    def run(use, gran):
+        set_seed(77)
+        layer = layer_from_oracle_params(cfg, params)
+        layer.use_recompute, layer.recompute_granularity = use, gran
+        layer.train()
+        xd = x.cuda().requires_grad_(True)
+        y = layer(xd)
+        pinned = Fn.saved_bytes(y.grad_fn.saved)
+        y.backward(dy.cuda())
+        torch.cuda.synchronize()
+        return y.detach(), xd.grad, {n: p.grad for n, p in layer.named_parameters()}, pinned
+
+    y0, dx0, g0, pinned0 = run(False, "full")
+    y1, dx1, g1, pinned1 = run(True, granularity)
+    assert torch.equal(y0, y1)
+    tol = 0.0 if hd128 else 4e-3  # head_dim 128 runs the deterministic split backward: exact
+    assert rel_err(dx1, dx0.float().cpu()) <= tol
+    for n in g0:
+        assert rel_err(g1[n], g0[n].float().cpu()) <= tol, n
+    assert pinned1 < pinned0
+    if granularity == "full":
+        assert pinned1 == x.numel() * 2  # only the layer input stays
+
+
+def test_layer_recompute_rejects_unknown_granularity():
+    from fleetx_b200.selfcheck import layer_from_oracle_params
+
+    cfg = O.LayerConfig(d_model=128, nhead=2, dim_feedforward=512, dropout=0.0)
+    params, x, _ = _setup(cfg, 1, 8)
+    layer = layer_from_oracle_params(cfg, params)
+    layer.use_recompute, layer.recompute_granularity = True, "everything"
+    layer.train()
+    with pytest.raises(ValueError):
+        layer(x.cuda())
+
+
+def test_mha_core_attn_recompute():
+    from fleetx_b200.layers import MultiHeadAttention
+    from fleetx_b200.rng import set_seed
+
+    x = torch.randn(2, 128, 256).to(torch.bfloat16)
+    dy = torch.randn(2, 128, 256).to(torch.bfloat16)
+
+    def run(use):
+        torch.manual_seed(3)
+        set_seed(5)
+        m = MultiHeadAttention(256, 2, dropout=0.1, use_recompute=use, recompute_granularity="core_attn")  # hd 128
+        m.train()
+        xd = x.cuda().requires_grad_(True)
+        y = m(xd)
+        y.backward(dy.cuda())
+        return y.detach(), xd.grad
+
+    y0, d0 = run(False)
+    y1, d1 = run(True)
+    assert torch.equal(y0, y1) and torch.equal(d0, d1)
