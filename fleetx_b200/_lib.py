@@ -20,6 +20,30 @@ FX_EPI_NONE, FX_EPI_BIAS, FX_EPI_BIAS_GELU, FX_EPI_DGELU = 0, 1, 2, 3
 
 _vp, _i, _f, _u64, _sz = C.c_void_p, C.c_int, C.c_float, C.c_uint64, C.c_size_t
 
+class TpComm(C.Structure):
+    """fx_tp_comm (include/fleetx_b200.h)."""
+    _fields_ = [("peer_bufs", C.POINTER(C.c_uint64)), ("peer_signal_pads", C.POINTER(C.c_uint64)),
+                ("multicast_ptr", C.c_uint64), ("local_buf", C.c_void_p), ("rank", C.c_int), ("world", C.c_int),
+                ("num_blocks", C.c_int), ("epoch", C.POINTER(C.c_uint32))]
+
+
+class LayerDesc(C.Structure):
+    """fx_layer_desc (include/fleetx_b200.h)."""
+    _fields_ = [("b", C.c_int), ("s", C.c_int), ("h", C.c_int), ("nh_local", C.c_int), ("hd", C.c_int),
+                ("f_local", C.c_int), ("normalize_before", C.c_int), ("eps", C.c_float), ("p_attn", C.c_float),
+                ("p_hidden1", C.c_float), ("p_hidden2", C.c_float), ("seed_attn", C.c_uint64),
+                ("offset_attn", C.c_uint64), ("seed_h1", C.c_uint64), ("offset_h1", C.c_uint64),
+                ("seed_h2", C.c_uint64), ("offset_h2", C.c_uint64)] + [
+        (n, C.c_void_p) for n in ("norm1_w", "norm1_b", "norm2_w", "norm2_b", "qkv_w", "qkv_b", "out_w", "out_b",
+                                  "lin1_w", "lin1_b", "lin2_w", "lin2_b")] + [("tp", C.POINTER(TpComm))]
+
+
+class LayerGrads(C.Structure):
+    """fx_layer_grads (include/fleetx_b200.h)."""
+    _fields_ = [(n, C.c_void_p) for n in ("norm1_w", "norm1_b", "norm2_w", "norm2_b", "qkv_w", "qkv_b", "out_w",
+                                          "out_b", "lin1_w", "lin1_b", "lin2_w", "lin2_b")]
+
+
 # name -> (restype, argtypes); must list every function the header declares
 SIGNATURES = {
     "fx_last_error": (C.c_char_p, []),
@@ -39,6 +63,10 @@ SIGNATURES = {
     "fx_attn_causal_fwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _f, _u64, _u64]),
     "fx_attn_causal_bwd_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "fx_attn_causal_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _f]),
+    "fx_decoder_layer_saved_bytes": (_sz, [C.POINTER(LayerDesc)]),
+    "fx_decoder_layer_workspace_bytes": (_sz, [C.POINTER(LayerDesc)]),
+    "fx_decoder_layer_fwd": (_i, [_vp, C.POINTER(LayerDesc), _vp, _vp, _vp, _vp]),
+    "fx_decoder_layer_bwd": (_i, [_vp, C.POINTER(LayerDesc), _vp, _vp, _vp, _vp, C.POINTER(LayerGrads), _vp]),
 }
 
 

@@ -134,6 +134,26 @@ class SymmetricTPGroup(TorchDistGroup):
 
     supports_chunks = True  # the layer may pipeline batch halves through all_reduce_bdr_start / _finish
 
+    def native_comm(self, rows: int, cols: int, device):
+        """fx_tp_comm for the native whole-layer entry points (fleetx_b200.native): this group's symmetric
+        buffer, flag pages and call counter as plain addresses. The returned object owns the ctypes storage."""
+        import ctypes
+
+        if rows * cols > self.max_elems:
+            raise RuntimeError(f"symmetric buffer of {self.max_elems} elements is too small for [{rows}, {cols}]")
+
+        class _Comm:
+            pass
+
+        c = _Comm()
+        c.epoch = ctypes.c_uint32(self._epoch)
+        c.comm = self._lib.TpComm(
+            peer_bufs=ctypes.cast(self._peer_bufs, ctypes.POINTER(ctypes.c_uint64)),
+            peer_signal_pads=ctypes.cast(self._peer_sigs, ctypes.POINTER(ctypes.c_uint64)),
+            multicast_ptr=self._mc, local_buf=self._buf.data_ptr(), rank=self.rank, world=self.nranks,
+            num_blocks=self.num_blocks, epoch=ctypes.pointer(c.epoch))
+        return c
+
     def _symm_offset(self, t: torch.Tensor):
         """Element offset of t inside the symmetric buffer, or None if t is not a contiguous view of it."""
         if t.dtype != torch.bfloat16 or not t.is_contiguous():

@@ -162,6 +162,53 @@ int fx_tp_allreduce_bdr(void* stream, const uint64_t* peer_bufs, const uint64_t*
                         uint64_t seed, uint64_t offset, const uint8_t* mask_in, uint64_t buf_elem_offset,
                         uint64_t dropout_elem_offset);
 
+/* ---- the whole decoder layer: TransformerDecoderLayer.forward, hybrid_model.py:525-566 -------------
+ * One call runs every kernel above in the order of the reference forward (LN -> qkv_proj -> core_attn
+ * -> out_proj -> allreduce + bias + dropout1 + residual -> LN -> linear1 + GELU -> linear2 -> allreduce
+ * + bias + dropout2 + residual; the post-LN order when normalize_before == 0), resp. its adjoint
+ * (Paddle autograd in the reference), on ONE stream, with no host synchronisation and no allocation:
+ * what a Paddle custom op or any non-Python host binds instead of sequencing the kernels itself.
+ * All pointers are device pointers, per-rank shards in the reference's layouts (weights [in, out]). */
+typedef struct fx_tp_comm {
+  const uint64_t* peer_bufs;        /* host array [world]: every rank's symmetric buffer as mapped here  */
+  const uint64_t* peer_signal_pads; /* host array [world]: every rank's flag page                        */
+  uint64_t multicast_ptr;           /* NVSwitch multicast address of the symmetric buffer (0: none)      */
+  void* local_buf;                  /* this rank's symmetric buffer, >= b*s*h bf16                       */
+  int rank, world, num_blocks;
+  uint32_t* epoch;                  /* host counter of allreduces issued on these buffers; updated       */
+} fx_tp_comm;
+
+typedef struct fx_layer_desc {
+  int b, s, h;                /* micro-batch, sequence, d_model                                         */
+  int nh_local, hd, f_local;  /* heads and FFN columns of THIS rank (nhead / n, dim_feedforward / n)    */
+  int normalize_before;       /* hybrid_model.py:453; the reference configs use 1                       */
+  float eps;                  /* LayerNorm epsilon (1e-5 at :513-514)                                   */
+  float p_attn, p_hidden1, p_hidden2; /* attention dropout (:279-285), dropout1 (:546), dropout2 (:556); 0 in eval */
+  uint64_t seed_attn, offset_attn;    /* 'local_seed' stream draw                                       */
+  uint64_t seed_h1, offset_h1, seed_h2, offset_h2; /* 'global_seed' stream draws                        */
+  const float *norm1_w, *norm1_b, *norm2_w, *norm2_b;                /* fp32 [h]                        */
+  const void *qkv_w, *qkv_b;   /* bf16 [h, 3*nh_local*hd], [3*nh_local*hd]  (per head q|k|v)            */
+  const void *out_w, *out_b;   /* bf16 [nh_local*hd, h], [h]                                             */
+  const void *lin1_w, *lin1_b; /* bf16 [h, f_local], [f_local]                                           */
+  const void *lin2_w, *lin2_b; /* bf16 [f_local, h], [h]                                                 */
+  const fx_tp_comm* tp;        /* NULL: single rank (no collective)                                      */
+} fx_layer_desc;
+
+typedef struct fx_layer_grads { /* caller-allocated, fully overwritten; dtypes as the parameters         */
+  float *norm1_w, *norm1_b, *norm2_w, *norm2_b;
+  void *qkv_w, *qkv_b, *out_w, *out_b, *lin1_w, *lin1_b, *lin2_w, *lin2_b;
+} fx_layer_grads;
+
+/* Bytes of activations kept from forward to backward / of scratch either call may overwrite. */
+size_t fx_decoder_layer_saved_bytes(const fx_layer_desc* d);
+size_t fx_decoder_layer_workspace_bytes(const fx_layer_desc* d);
+/* x, out: bf16 [b, s, h]. `saved` receives the activations backward needs (x itself is not copied). */
+int fx_decoder_layer_fwd(void* stream, const fx_layer_desc* d, const void* x, void* out, void* saved,
+                         void* workspace);
+/* dout, dx: bf16 [b, s, h]; x and saved as given to / filled by the forward call with the same desc. */
+int fx_decoder_layer_bwd(void* stream, const fx_layer_desc* d, const void* dout, const void* x,
+                         const void* saved, void* dx, const fx_layer_grads* grads, void* workspace);
+
 #ifdef __cplusplus
 }
 #endif
