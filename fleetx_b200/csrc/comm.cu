@@ -172,6 +172,10 @@ tp_allreduce_kernel(const Params p) {
   if (tid < p.world) red_release_sys_add(reinterpret_cast<uint32_t*>(p.sig[tid]) + SLOT_RS_DONE, 1u);
   if (tid == 0) spin_until(my_sig + SLOT_RS_DONE, p.epoch * nblk * p.world, 1);
   __syncthreads();
+  } else {
+    // the one-shot variant has no reduce-scatter barrier, but it still counts itself in, so that calls of
+    // different variants can be mixed on one set of flag pages (every counter advances on every call)
+    if (tid < p.world) red_release_sys_add(reinterpret_cast<uint32_t*>(p.sig[tid]) + SLOT_RS_DONE, 1u);
   }
 
   // ---- phase 3: epilogue over the complete sum; fused bias + dropout + residual.

@@ -23,7 +23,7 @@ struct SavedPlan {
 // Offsets of scratch buffers. Forward and backward plans share one workspace (max of the two).
 struct WorkPlan {
   size_t part;                                     // [T,h] partial sums of a row-parallel GEMM (no TP buffer given)
-  size_t d_y, d_z, d_in, d_x1, d_ctx, d_qkv, aux;  // backward
+  size_t d_y, d_z, d_in, d_x1, d_ctx, d_qkv, d_red, aux;  // backward
   size_t total;
 };
 
@@ -87,6 +87,7 @@ static WorkPlan plan_work(const fx_layer_desc* d) {
   p.d_x1 = take(m.T * m.h * 2);
   p.d_ctx = take(m.T * m.hl * 2);
   p.d_qkv = take(m.T * m.q3 * 2);
+  p.d_red = take(m.T * m.h * 2);
   size_t aux = fx_layernorm_bwd_workspace_bytes(static_cast<int>(m.T), d->h);
   const size_t widest = m.f > m.q3 ? m.f : m.q3;
   const size_t cs = fx_colsum_workspace_bytes(static_cast<int>(m.T), static_cast<int>(widest > m.h ? widest : m.h));
@@ -118,6 +119,13 @@ static int check_desc(const fx_layer_desc* d, const char* who) {
 }
 
 static bool tp_on(const fx_layer_desc* d) { return d->tp != nullptr && d->tp->world > 1; }
+
+// Plain allreduce of dX (backward of _c_identity): where the sum ends up. More than two ranks: the switch
+// writes it into every rank's copy of the symmetric buffer (in place). Two ranks: the one-shot peer-load
+// variant is faster but the peer still reads this rank's copy, so the sum goes to scratch.
+static void* reduced_dx(const fx_layer_desc* d, void* part, void* scratch) {
+  return (tp_on(d) && d->tp->world == 2) ? scratch : part;
+}
 
 // sum over ranks of `part` (+ bias, dropout, residual when out != null; else the sum stays in part)
 static int reduce_bdr(void* stream, const fx_layer_desc* d, void* part, void* out, const void* bias,
@@ -250,7 +258,8 @@ extern "C" int fx_decoder_layer_bwd(void* stream, const fx_layer_desc* d, const 
   FX_TRY(fx_gemm_bf16(stream, 0, 1, T, f, h, d_y2, h, d->lin2_w, h, ws + W.d_z, f, FX_BF16, 0, FX_EPI_DGELU, nullptr,
                       const_cast<char*>(sv + S.z), f));
   FX_TRY(fx_gemm_bf16(stream, 0, 1, T, h, f, ws + W.d_z, f, d->lin1_w, f, part, h, FX_BF16, 0, FX_EPI_NONE, nullptr, nullptr, 0));
-  FX_TRY(reduce_bdr(stream, d, part, nullptr, nullptr, nullptr, 0.f, 0, 0));  // backward of _c_identity
+  void* red = reduced_dx(d, part, ws + W.d_red);
+  FX_TRY(reduce_bdr(stream, d, part, red == part ? nullptr : red, nullptr, nullptr, 0.f, 0, 0));  // backward of _c_identity
   FX_TRY(fx_colsum_bf16(stream, d_y2, h, g->lin2_b, FX_BF16, aux, T, h));
   FX_TRY(fx_gemm_bf16(stream, 1, 0, f, h, T, sv + S.act, f, d_y2, h, g->lin2_w, h, FX_BF16, 0, FX_EPI_NONE, nullptr, nullptr, 0));
   FX_TRY(fx_colsum_bf16(stream, ws + W.d_z, f, g->lin1_b, FX_BF16, aux, T, f));
@@ -261,14 +270,14 @@ extern "C" int fx_decoder_layer_bwd(void* stream, const fx_layer_desc* d, const 
   void* d_ao;
   if (pre) {
     // x1 feeds LN2 and the skip: d(x1) = LN2'(d_ffn_in) + dY
-    FX_TRY(fx_layernorm_bwd(stream, part, x1, d->norm2_w, reinterpret_cast<const float*>(sv + S.mean2),
+    FX_TRY(fx_layernorm_bwd(stream, red, x1, d->norm2_w, reinterpret_cast<const float*>(sv + S.mean2),
                             reinterpret_cast<const float*>(sv + S.rstd2), dy, ws + W.d_x1, g->norm2_w, g->norm2_b, aux, T, h));
     d_r1 = ws + W.d_x1;
     d_ao = ws + W.d_y;
   } else {
     // x1 = LN1(r1) feeds linear1 and the skip: d(x1) = d_ffn_in + dY (dY lives in d_x1: add in place is not
     // possible with distinct in/out kernels, so the sum goes to d_in), then through LN1
-    FX_TRY(fx_bias_dropout_residual_fwd(stream, part, nullptr, dy, ws + W.d_in, T, h, 0.f, 0, 0, nullptr, nullptr));
+    FX_TRY(fx_bias_dropout_residual_fwd(stream, red, nullptr, dy, ws + W.d_in, T, h, 0.f, 0, 0, nullptr, nullptr));
     FX_TRY(fx_layernorm_bwd(stream, ws + W.d_in, sv + S.r1, d->norm1_w, mean1, rstd1, nullptr, ws + W.d_y, g->norm1_w,
                             g->norm1_b, aux, T, h));
     d_r1 = ws + W.d_y;
@@ -281,16 +290,16 @@ extern "C" int fx_decoder_layer_bwd(void* stream, const fx_layer_desc* d, const 
                             d->p_attn > 0.f ? sv + S.mask : nullptr, ws + W.d_qkv, aux, d->b, d->s, d->nh_local, d->hd, scale,
                             d->p_attn));
   FX_TRY(fx_gemm_bf16(stream, 0, 1, T, h, q3, ws + W.d_qkv, q3, d->qkv_w, q3, part, h, FX_BF16, 0, FX_EPI_NONE, nullptr, nullptr, 0));
-  FX_TRY(reduce_bdr(stream, d, part, nullptr, nullptr, nullptr, 0.f, 0, 0));  // backward of _c_identity
+  FX_TRY(reduce_bdr(stream, d, part, red == part ? nullptr : red, nullptr, nullptr, 0.f, 0, 0));  // backward of _c_identity
   FX_TRY(fx_colsum_bf16(stream, d_ao, h, g->out_b, FX_BF16, aux, T, h));
   FX_TRY(fx_gemm_bf16(stream, 1, 0, hl, h, T, sv + S.ctx, hl, d_ao, h, g->out_w, h, FX_BF16, 0, FX_EPI_NONE, nullptr, nullptr, 0));
   FX_TRY(fx_colsum_bf16(stream, ws + W.d_qkv, q3, g->qkv_b, FX_BF16, aux, T, q3));
   const void* attn_in = pre ? sv + S.ln1 : x;
   FX_TRY(fx_gemm_bf16(stream, 1, 0, h, q3, T, attn_in, h, ws + W.d_qkv, q3, g->qkv_w, q3, FX_BF16, 0, FX_EPI_NONE, nullptr, nullptr, 0));
   if (pre) {  // x feeds LN1 and the skip
-    FX_TRY(fx_layernorm_bwd(stream, part, x, d->norm1_w, mean1, rstd1, d_r1, dx, g->norm1_w, g->norm1_b, aux, T, h));
+    FX_TRY(fx_layernorm_bwd(stream, red, x, d->norm1_w, mean1, rstd1, d_r1, dx, g->norm1_w, g->norm1_b, aux, T, h));
   } else {
-    FX_TRY(fx_bias_dropout_residual_fwd(stream, part, nullptr, d_r1, dx, T, h, 0.f, 0, 0, nullptr, nullptr));
+    FX_TRY(fx_bias_dropout_residual_fwd(stream, red, nullptr, d_r1, dx, T, h, 0.f, 0, 0, nullptr, nullptr));
   }
   return FX_OK;
 }

@@ -36,7 +36,7 @@ def _worker(rank, world, port, ret, kind):
         x = torch.randn(b, s, cfg.d_model, generator=g).to(torch.bfloat16)
         dy = torch.randn(b, s, cfg.d_model, generator=g).to(torch.bfloat16)
         set_seed(1024, mp_rank=rank)
-        group = SymmetricTPGroup(max_elems=b * s * cfg.d_model, num_blocks=32) if kind == "symmetric" else TorchDistGroup()
+        group = TorchDistGroup() if kind == "nccl" else SymmetricTPGroup(max_elems=b * s * cfg.d_model, num_blocks=32)
         layer = layer_from_oracle_params(cfg, params, group=group, device=f"cuda:{rank}")
         layer.train()
         worst = 0.0
@@ -55,16 +55,37 @@ def _worker(rank, world, port, ret, kind):
             for n, p in layer.named_parameters():
                 errs[n] = rel_err(p.grad, g_shard[n])
             worst = max(worst, max(errs.values()))
+        if kind == "native":
+            # the same layer through fx_decoder_layer_fwd / _bwd with the group's fx_tp_comm, interleaved with
+            # the Python path on the same symmetric buffer and flag epochs: results must agree
+            from fleetx_b200 import functional as Fn
+            from fleetx_b200.native import NativeLayer
+
+            layer.eval()  # dropout off: module and native entry need no shared draws
+            P = Fn.LayerParams(*layer._params())
+            M = layer._meta()
+            xd = x.cuda()
+            y_py, saved = Fn.decoder_layer_fwd(xd, P, M, group)
+            dx_py, g_py = Fn.decoder_layer_bwd(dy.cuda(), saved, P, M, group)
+            nat = NativeLayer(b, s, P, M, group)
+            for it in range(2):
+                y_n = nat.forward(xd)
+                dx_n, g_n = nat.backward(dy.cuda())
+            y_py2, _ = Fn.decoder_layer_fwd(xd, P, M, group)  # and the Python path still works afterwards
+            torch.cuda.synchronize()
+            worst = max(worst, rel_err(y_n, y_py.float().cpu()), rel_err(dx_n, dx_py.float().cpu()), rel_err(y_py2, y_py.float().cpu()),
+                        max(rel_err(g_n[k], g_py[k].float().cpu()) for k in g_py))
         ret[rank] = worst
     finally:
         dist.destroy_process_group()
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
-@pytest.mark.parametrize("kind", ["nccl", "symmetric"])
+@pytest.mark.parametrize("kind", ["nccl", "symmetric", "native"])
 def test_tp2_layer_matches_oracle(kind):
     """kind = "nccl": torch.distributed allreduce; "symmetric": the library's own fused allreduce
-    kernel over NVLink peer memory (csrc/comm.cu)."""
+    kernel over NVLink peer memory (csrc/comm.cu); "native": additionally the whole-layer C entry points
+    (csrc/layer.cu) driving that kernel through an fx_tp_comm."""
     ctx = mp.get_context("spawn")
     ret = ctx.Manager().dict()
     port = _free_port()
