@@ -13,7 +13,8 @@ the N GPUs (mp_degree = N, so total work is fixed: "strong" scaling).
 One "step" = one forward + one backward of the layer over the whole batch. `value` is timed with
 inputs resident in HBM (CUDA events per step, L2 flushed between steps, max over ranks);
 `e2e` is the same step through the public API (TransformerDecoderLayer + autograd) with HOST
-buffers: x and dy are copied from pinned memory and dx is copied back inside the timed region.
+buffers: every step's x and dy are copied from pinned memory and its dx is copied back inside the timed
+region, on copy streams, double-buffered against the neighbouring steps' kernels (an input pipeline).
 
 --impl reference times the CPU restatement of the reference layer (oracle/, torch-CPU fp32; the
 reference's own Paddle path cannot run here — see BASELINE.md) on a bounded sample.
@@ -309,30 +310,65 @@ def run_gpu(args):
     gemm_tf = gemm_flops / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
     layer_tf = layer_flops(T, s, H) / n / (ms_per_step * 1e-3) / 1e12
 
-    # ---- e2e: public API (module + autograd), host buffers, copies inside the timed region
-    def step_e2e():
-        xd = x_host.to(dev, non_blocking=True).requires_grad_(True)
-        dyd = dy_host.to(dev, non_blocking=True)
-        y = layer(xd)
-        y.backward(dyd)
-        dx_host.copy_(xd.grad, non_blocking=True)
-        for p_ in layer.parameters():
-            p_.grad = None
+    # ---- e2e: public API (module + autograd), host buffers, copies inside the timed region.
+    # Every step copies ITS x and dy from pinned host memory and copies ITS dx back; as an input pipeline
+    # does, the copies run on their own streams, double-buffered: H2D of step i+1 and D2H of step i-1
+    # overlap the kernels of step i. The first H2D and the last D2H are inside the timed region too.
+    h2d_s, d2h_s = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+    xd_buf = [torch.empty(b, s, H, dtype=torch.bfloat16, device=dev) for _ in range(2)]
+    dyd_buf = [torch.empty(b, s, H, dtype=torch.bfloat16, device=dev) for _ in range(2)]
+
+    def run_e2e(k_steps):
+        main = torch.cuda.current_stream()
+        ready = [torch.cuda.Event() for _ in range(2)]
+        done = [None, None]
+        keep = []  # gradients being copied out on d2h_s stay referenced until the final sync
+
+        def h2d(i):
+            slot = i % 2
+            with torch.cuda.stream(h2d_s):
+                if done[slot] is not None:
+                    h2d_s.wait_event(done[slot])  # the step that last used these buffers has finished
+                xd_buf[slot].copy_(x_host, non_blocking=True)
+                dyd_buf[slot].copy_(dy_host, non_blocking=True)
+                ready[slot].record(h2d_s)
+
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(main)
+        h2d_s.wait_stream(main)
+        d2h_s.wait_stream(main)
+        h2d(0)
+        for i in range(k_steps):
+            slot = i % 2
+            if i + 1 < k_steps:
+                h2d(i + 1)
+            main.wait_event(ready[slot])
+            flush.zero_()
+            xin = xd_buf[slot].detach().requires_grad_(True)
+            y = layer(xin)
+            y.backward(dyd_buf[slot])
+            ev = torch.cuda.Event()
+            ev.record(main)
+            done[slot] = ev
+            keep.append(xin.grad)
+            with torch.cuda.stream(d2h_s):
+                d2h_s.wait_event(ev)
+                dx_host.copy_(xin.grad, non_blocking=True)
+            for p_ in layer.parameters():
+                p_.grad = None
+        main.wait_stream(d2h_s)
+        main.wait_stream(h2d_s)
+        e1.record(main)
+        torch.cuda.synchronize(dev)
+        return e0.elapsed_time(e1)
 
     e2e_steps = 0 if args.profile_mode else max(3, min(args.steps, 10))
-    for _ in range(3 if e2e_steps else 0):
-        step_e2e()
-    barrier()
-    evs = []
-    for _ in range(e2e_steps):
-        flush.zero_()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        step_e2e()
-        e1.record()
-        evs.append((e0, e1))
-    barrier()
-    e2e_ms = sum(a.elapsed_time(c) for a, c in evs)
+    e2e_ms = 0.0
+    if e2e_steps:
+        run_e2e(3)
+        barrier()
+        e2e_ms = run_e2e(e2e_steps)
+        barrier()
     t = torch.tensor([e2e_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -357,7 +393,9 @@ def run_gpu(args):
             "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": dict(workload_config(args, n), collective=collective),
             "e2e": {"value": e2e_tokens_per_s, "unit": "tokens/s", "h2d_bytes_per_step": 2 * T * H * 2,
-                    "d2h_bytes_per_step": T * H * 2, "steps": e2e_steps},
+                    "d2h_bytes_per_step": T * H * 2, "steps": e2e_steps,
+                    "pipeline": "double-buffered copies on their own streams: H2D of step i+1 and D2H of step i-1 "
+                                "overlap the kernels of step i; first H2D and last D2H inside the timed region"},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "tensor", "kernel": "fx::gemm::gemm_kernel (tcgen05, all linears fwd+bwd)",
