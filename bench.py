@@ -314,7 +314,14 @@ def run_gpu(args):
     # Every step copies ITS x and dy from pinned host memory and copies ITS dx back; as an input pipeline
     # does, the copies run on their own streams, double-buffered: H2D of step i+1 and D2H of step i-1
     # overlap the kernels of step i. The first H2D and the last D2H are inside the timed region too.
+    # With N ranks the layer input is replicated: each rank copies 1/N of the rows from its host and the
+    # ranks all-gather over NVLink (what a TP input pipeline does); dx is identical everywhere, so each rank
+    # returns its 1/N of the rows. Whole-job host traffic per step is then the same at every N.
     h2d_s, d2h_s = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+    r0, r1 = rank * (T // world), (rank + 1) * (T // world)
+    xs_buf = torch.empty(r1 - r0, H, dtype=torch.bfloat16, device=dev)
+    dys_buf = torch.empty(r1 - r0, H, dtype=torch.bfloat16, device=dev)
+    xh2, dyh2, dxh2 = x_host.view(T, H), dy_host.view(T, H), dx_host.view(T, H)
     xd_buf = [torch.empty(b, s, H, dtype=torch.bfloat16, device=dev) for _ in range(2)]
     dyd_buf = [torch.empty(b, s, H, dtype=torch.bfloat16, device=dev) for _ in range(2)]
 
@@ -329,8 +336,14 @@ def run_gpu(args):
             with torch.cuda.stream(h2d_s):
                 if done[slot] is not None:
                     h2d_s.wait_event(done[slot])  # the step that last used these buffers has finished
-                xd_buf[slot].copy_(x_host, non_blocking=True)
-                dyd_buf[slot].copy_(dy_host, non_blocking=True)
+                if world == 1:
+                    xd_buf[slot].copy_(x_host, non_blocking=True)
+                    dyd_buf[slot].copy_(dy_host, non_blocking=True)
+                else:
+                    xs_buf.copy_(xh2[r0:r1], non_blocking=True)
+                    dys_buf.copy_(dyh2[r0:r1], non_blocking=True)
+                    dist.all_gather_into_tensor(xd_buf[slot].view(-1), xs_buf.view(-1))
+                    dist.all_gather_into_tensor(dyd_buf[slot].view(-1), dys_buf.view(-1))
                 ready[slot].record(h2d_s)
 
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -353,7 +366,7 @@ def run_gpu(args):
             keep.append(xin.grad)
             with torch.cuda.stream(d2h_s):
                 d2h_s.wait_event(ev)
-                dx_host.copy_(xin.grad, non_blocking=True)
+                dxh2[r0:r1].copy_(xin.grad.view(T, H)[r0:r1], non_blocking=True)
             for p_ in layer.parameters():
                 p_.grad = None
         main.wait_stream(d2h_s)
@@ -395,7 +408,9 @@ def run_gpu(args):
             "e2e": {"value": e2e_tokens_per_s, "unit": "tokens/s", "h2d_bytes_per_step": 2 * T * H * 2,
                     "d2h_bytes_per_step": T * H * 2, "steps": e2e_steps,
                     "pipeline": "double-buffered copies on their own streams: H2D of step i+1 and D2H of step i-1 "
-                                "overlap the kernels of step i; first H2D and last D2H inside the timed region"},
+                                "overlap the kernels of step i; first H2D and last D2H inside the timed region"
+                                + ("" if world == 1 else f"; each of the {world} ranks moves 1/{world} of the rows over PCIe and "
+                                   "the replicated input is all-gathered over NVLink (byte counts are whole-job totals)")},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "tensor", "kernel": "fx::gemm::gemm_kernel (tcgen05, all linears fwd+bwd)",
