@@ -59,6 +59,8 @@ SIGNATURES = {
     "fx_colsum_bf16": (_i, [_vp, _vp, _i, _vp, _i, _vp, _i, _i]),
     "fx_gemm_bf16": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _i, _vp, _i, _vp, _i, _i, _i, _i, _vp, _vp, _i]),
     "fx_tp_allreduce_bdr": (_i, [_vp, _vp, _vp, _u64, _i, _i, C.c_uint32, _i, _vp, _i, _i, _vp, _vp, _f, _u64, _u64, _vp, _u64, _u64]),
+    "fx_tp_allgather_rows": (_i, [_vp, _vp, _u64, _i, _i, C.c_uint32, _i, _vp, _i, _i, _i, _u64]),
+    "fx_tp_reduce_scatter_bdr": (_i, [_vp, _vp, _u64, _i, _i, C.c_uint32, _i, _vp, _i, _i, _i, _vp, _vp, _f, _u64, _u64, _vp, _u64]),
     "fx_attn_dropout_mask_bytes": (_sz, [_i, _i, _i]),
     "fx_attn_causal_fwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _f, _u64, _u64]),
     "fx_attn_causal_bwd_workspace_bytes": (_sz, [_i, _i, _i, _i]),

@@ -248,8 +248,161 @@ tp_allreduce_kernel(const Params p) {
   if (blockIdx.x == 0 && tid == 0) spin_until(my_sig + SLOT_AG_DONE, p.epoch * nblk * p.world, 2);
 }
 
+// ---------------------------------------------------------------------------------------------------
+// Sequence parallelism (sequence_parallel_utils.py:36-126, 150-326): between the attention and FFN blocks
+// the activations are sharded along the sequence, rank r holding [s/n, b, h] (sequence-first, the
+// reference's layout). The allreduce above then splits into its two halves, with the row permutation
+// between the sharded sequence-first layout and the batch-first [b, s, h] layout of the GEMM / attention
+// kernels folded into the transfer:
+//   mode 0  all-gather (AllGatherOp forward, ReduceScatterOp backward): each rank multicasts its shard
+//           rows into every rank's copy of the symmetric buffer (multimem.st), counter barrier;
+//   mode 1  reduce-scatter (ReduceScatterOp forward, AllGatherOp backward) fused with bias + dropout +
+//           residual: flag handshake, each rank sums ITS rows over all replicas in the switch
+//           (multimem.ld_reduce) and applies the epilogue into an ordinary local shard tensor, counter
+//           barrier before anyone overwrites the buffer.
+// Dropout here is indexed by position in the LOCAL shard: the reference draws the mask of a [s/n, b, h]
+// tensor under 'global_seed', which is the same on every mp rank (hybrid_model.py:546, :556).
+struct SeqParParams {
+  uint64_t sig[MAX_RANKS];
+  uint64_t mc;               // multicast address of the [b*s, h] buffer
+  int rank, world, mode;
+  int b, s, h;               // full tensor [b, s, h]; shard = [s/world, b, h]
+  uint32_t epoch;
+  const __nv_bfloat16* src;  // mode 0: local shard to publish
+  __nv_bfloat16* out;        // mode 1: local shard result
+  const __nv_bfloat16* bias;
+  const __nv_bfloat16* residual;
+  float p_drop, scale;
+  uint32_t thresh;
+  uint64_t seed, offset;
+  const uint8_t* mask_in;
+};
+
+__global__ void __launch_bounds__(THREADS)
+tp_seqpar_kernel(const SeqParParams p) {
+  const int tid = threadIdx.x;
+  uint32_t* my_sig = reinterpret_cast<uint32_t*>(p.sig[p.rank]);
+  const uint32_t nblk = gridDim.x;
+  // every call advances every flag and counter, whichever kernel or mode it is (epochs stay in lockstep)
+  if (blockIdx.x == 0 && tid < p.world)
+    st_release_sys(reinterpret_cast<uint32_t*>(p.sig[tid]) + SLOT_READY + p.rank, p.epoch);
+  // Every rank has reached this call, i.e. (stream order) finished everything before it: mode 1 — all
+  // partial sums are in place before the switch reads them; mode 0 — nobody still reads the previous
+  // contents of its copy (a GEMM over an earlier gather) when the multicast stores arrive.
+  if (tid < p.world) spin_until(my_sig + SLOT_READY + tid, p.epoch, 0);
+  __syncthreads();
+  const int hv = p.h >> 3;
+  const int sl = p.s / p.world;                       // sequence positions per rank
+  const size_t total = static_cast<size_t>(sl) * p.b * hv;  // 16-byte vectors of the local shard
+  const size_t stride = static_cast<size_t>(gridDim.x) * THREADS;
+  for (size_t v = static_cast<size_t>(blockIdx.x) * THREADS + tid; v < total; v += stride) {
+    const size_t row_l = v / hv;                      // local row = s_local * b + batch
+    const int c = static_cast<int>(v - row_l * hv);
+    const size_t s_local = row_l / p.b, batch = row_l - s_local * p.b;
+    const size_t row_g = batch * p.s + static_cast<size_t>(p.rank) * sl + s_local;  // row in [b, s]
+    const uint64_t addr = p.mc + (row_g * hv + c) * 16;
+    if (p.mode == 0) {
+      multimem_st_v4(addr, __ldg(reinterpret_cast<const uint4*>(p.src) + v));
+    } else {
+      uint4 res = multimem_ld_reduce_bf16x8(addr);
+      if (p.residual != nullptr) {
+        float y[8], r[8], o[8];
+        unpack8(res, y);
+        unpack8(__ldg(reinterpret_cast<const uint4*>(p.residual) + v), r);
+        if (p.bias != nullptr) {
+          float bb[8];
+          unpack8(__ldg(reinterpret_cast<const uint4*>(p.bias) + c), bb);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) y[j] += bb[j];
+        }
+        if (p.mask_in != nullptr) {
+          const uint2 m = __ldg(reinterpret_cast<const uint2*>(p.mask_in) + v);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            o[j] = r[j] + (((m.x >> (8 * j)) & 0xFFu) ? y[j] * p.scale : 0.f);
+            o[4 + j] = r[4 + j] + (((m.y >> (8 * j)) & 0xFFu) ? y[4 + j] * p.scale : 0.f);
+          }
+        } else if (p.p_drop > 0.f) {
+          const Philox8 rnd = philox4x32_10(p.seed, p.offset, v);  // group index = vector index in the local shard
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] = r[j] + (philox_keep(rnd, j, p.thresh) ? y[j] * p.scale : 0.f);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] = r[j] + y[j];
+        }
+        res = pack8(o);
+      }
+      reinterpret_cast<uint4*>(p.out)[v] = res;
+    }
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (tid < p.world) red_release_sys_add(reinterpret_cast<uint32_t*>(p.sig[tid]) + SLOT_RS_DONE, 1u);
+  // mode 0: the gathered tensor is complete once every block of every rank has stored its rows
+  if (p.mode == 0 && tid == 0) spin_until(my_sig + SLOT_RS_DONE, p.epoch * nblk * p.world, 1);
+  __syncthreads();
+  if (tid < p.world) red_release_sys_add(reinterpret_cast<uint32_t*>(p.sig[tid]) + SLOT_AG_DONE, 1u);
+  // mode 1: nobody may overwrite the buffer while a peer's switch reduction still reads it
+  if (p.mode == 1 && blockIdx.x == 0 && tid == 0) spin_until(my_sig + SLOT_AG_DONE, p.epoch * nblk * p.world, 2);
+}
+
+static int launch_seqpar(void* stream, const uint64_t* peer_signal_pads, uint64_t multicast_ptr, int rank, int world,
+                         uint32_t epoch, int num_blocks, SeqParParams& q, int b, int s, int h, uint64_t buf_elem_offset,
+                         const char* who) {
+  FX_CHECK_ARG(world >= 2 && world <= MAX_RANKS && rank >= 0 && rank < world, "%s: bad rank/world (%d/%d)", who, rank, world);
+  FX_CHECK_ARG(b > 0 && s > 0 && h > 0 && h % 8 == 0, "%s: b %d, s %d, h %d (h must be a multiple of 8)", who, b, s, h);
+  FX_CHECK_ARG(s % world == 0, "%s: sequence length %d can't be divided exactly by sequence parallelism %d", who, s, world);
+  FX_CHECK_ARG(peer_signal_pads && multicast_ptr, "%s: null pointer", who);
+  FX_CHECK_ARG(epoch > 0, "%s: epoch must start at 1", who);
+  FX_CHECK_ARG(buf_elem_offset % 8 == 0, "%s: element offsets must be multiples of 8", who);
+  FX_CHECK_ARG(num_blocks > 0 && num_blocks <= num_sms(), "%s: num_blocks must be in [1, #SMs]", who);
+  for (int i = 0; i < world; ++i) q.sig[i] = peer_signal_pads[i];
+  q.mc = multicast_ptr + buf_elem_offset * 2;
+  q.rank = rank; q.world = world;
+  q.b = b; q.s = s; q.h = h;
+  q.epoch = epoch;
+  tp_seqpar_kernel<<<num_blocks, THREADS, 0, static_cast<cudaStream_t>(stream)>>>(q);
+  FX_LAUNCH_CHECK();
+  return FX_OK;
+}
+
 }  // namespace comm
 }  // namespace fx
+
+extern "C" int fx_tp_allgather_rows(void* stream, const uint64_t* peer_signal_pads, uint64_t multicast_ptr, int rank,
+                                    int world, uint32_t epoch, int num_blocks, const void* shard, int b, int s, int h,
+                                    uint64_t buf_elem_offset) {
+  using namespace fx;
+  FX_CHECK_ARG(shard != nullptr && (uintptr_t)shard % 16 == 0, "fx_tp_allgather_rows: null or misaligned shard");
+  comm::SeqParParams q{};
+  q.mode = 0;
+  q.src = static_cast<const __nv_bfloat16*>(shard);
+  return comm::launch_seqpar(stream, peer_signal_pads, multicast_ptr, rank, world, epoch, num_blocks, q, b, s, h,
+                             buf_elem_offset, "fx_tp_allgather_rows");
+}
+
+extern "C" int fx_tp_reduce_scatter_bdr(void* stream, const uint64_t* peer_signal_pads, uint64_t multicast_ptr, int rank,
+                                        int world, uint32_t epoch, int num_blocks, void* out_shard, int b, int s, int h,
+                                        const void* bias, const void* residual_shard, float p, uint64_t seed,
+                                        uint64_t offset, const uint8_t* mask_in, uint64_t buf_elem_offset) {
+  using namespace fx;
+  FX_CHECK_ARG(out_shard != nullptr && ((uintptr_t)out_shard | (uintptr_t)residual_shard | (uintptr_t)bias) % 16 == 0,
+               "fx_tp_reduce_scatter_bdr: null or misaligned pointer");
+  FX_CHECK_ARG(p >= 0.f && p < 1.f, "fx_tp_reduce_scatter_bdr: dropout p must be in [0,1) (got %f)", p);
+  FX_CHECK_ARG((bias == nullptr && mask_in == nullptr && p == 0.f) || residual_shard != nullptr,
+               "fx_tp_reduce_scatter_bdr: bias / dropout need a residual");
+  comm::SeqParParams q{};
+  q.mode = 1;
+  q.out = static_cast<__nv_bfloat16*>(out_shard);
+  q.bias = static_cast<const __nv_bfloat16*>(bias);
+  q.residual = static_cast<const __nv_bfloat16*>(residual_shard);
+  q.p_drop = p; q.scale = 1.0f / (1.0f - p);
+  q.thresh = dropout_threshold(p);
+  q.seed = seed; q.offset = offset;
+  q.mask_in = mask_in;
+  return comm::launch_seqpar(stream, peer_signal_pads, multicast_ptr, rank, world, epoch, num_blocks, q, b, s, h,
+                             buf_elem_offset, "fx_tp_reduce_scatter_bdr");
+}
 
 extern "C" int fx_tp_allreduce_bdr(void* stream, const uint64_t* peer_bufs, const uint64_t* peer_signal_pads,
                                    uint64_t multicast_ptr, int rank, int world, uint32_t epoch, int num_blocks,

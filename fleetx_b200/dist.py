@@ -44,6 +44,41 @@ class _GroupOps:
         self.all_reduce_(y)
         return ops.bias_dropout_residual_fwd(y, bias, residual, p, seed, offset, mask_in=mask_in)
 
+    # ---- sequence parallelism (sequence_parallel_utils.py:36-126). Shards are sequence-first [s/n, b, h]
+    # flattened to [s/n * b, h]; full tensors are batch-first [b * s, h] (what the GEMM / attention kernels
+    # take). The base versions go through torch.distributed and torch permutes (the plumbing backend).
+    def sp_all_gather(self, shard: torch.Tensor, b: int, s: int) -> torch.Tensor:
+        """[s/n * b, h] shard of this rank -> full [b * s, h], batch-first (all_gather, :47-55)."""
+        n, h = self.nranks, shard.shape[-1]
+        if n == 1:
+            return shard.view(s, b, h).transpose(0, 1).reshape(b * s, h)
+        full = torch.empty(n, s // n, b, h, dtype=shard.dtype, device=shard.device)
+        self._dist.all_gather_into_tensor(full, shard.contiguous().view(s // n, b, h), group=self.pg)
+        return full.view(s, b, h).transpose(0, 1).reshape(b * s, h)
+
+    def sp_reduce_scatter(self, part: torch.Tensor, b: int, s: int) -> torch.Tensor:
+        """partial sums [b * s, h], batch-first -> this rank's rows of the sum, [s/n * b, h] (:58-70)."""
+        n, h = self.nranks, part.shape[-1]
+        seq_first = part.view(b, s, h).transpose(0, 1).contiguous()  # [s, b, h]
+        if n == 1:
+            return seq_first.view(s * b, h)
+        if self._dist.get_backend(self.pg) == "nccl":
+            out = torch.empty(s // n, b, h, dtype=part.dtype, device=part.device)
+            self._dist.reduce_scatter_tensor(out, seq_first, op=self._dist.ReduceOp.SUM, group=self.pg)
+            return out.view(-1, h)
+        self._dist.all_reduce(seq_first, op=self._dist.ReduceOp.SUM, group=self.pg)  # gloo has no reduce_scatter
+        sl = s // n
+        return seq_first[self.rank * sl:(self.rank + 1) * sl].reshape(-1, h)
+
+    def sp_reduce_scatter_bdr(self, part, b, s, bias, residual, p, seed, offset, mask_in=None):
+        """reduce-scatter, then residual + dropout(sum + bias) on the local shard (dropout indexed locally)."""
+        from . import ops
+
+        y = self.sp_reduce_scatter(part, b, s)
+        if residual is None:
+            return y
+        return ops.bias_dropout_residual_fwd(y, bias, residual, p, seed, offset, mask_in=mask_in)
+
 
 class SingleGroup(_GroupOps):
     rank = 0
@@ -133,6 +168,32 @@ class SymmetricTPGroup(TorchDistGroup):
         return self._buf[: rows * cols].view(rows, cols)
 
     supports_chunks = True  # the layer may pipeline batch halves through all_reduce_bdr_start / _finish
+
+    def sp_all_gather(self, shard: torch.Tensor, b: int, s: int) -> torch.Tensor:
+        h = shard.shape[-1]
+        if b * s * h > self.max_elems or shard.dtype != torch.bfloat16 or not shard.is_contiguous():
+            return super().sp_all_gather(shard, b, s)
+        self._epoch += 1
+        self._lib.check(self._lib.lib().fx_tp_allgather_rows(
+            torch.cuda.current_stream().cuda_stream, self._peer_sigs, self._mc, self.rank, self.nranks, self._epoch,
+            self.num_blocks, shard.data_ptr(), b, s, h, 0), "fx_tp_allgather_rows")
+        return self._buf[: b * s * h].view(b * s, h)
+
+    def sp_reduce_scatter_bdr(self, part, b, s, bias, residual, p, seed, offset, mask_in=None):
+        if not self._is_symmetric(part):
+            return super().sp_reduce_scatter_bdr(part, b, s, bias, residual, p, seed, offset, mask_in)
+        h = part.shape[-1]
+        out = torch.empty(s // self.nranks * b, h, dtype=torch.bfloat16, device=part.device)
+        self._epoch += 1
+        self._lib.check(self._lib.lib().fx_tp_reduce_scatter_bdr(
+            torch.cuda.current_stream().cuda_stream, self._peer_sigs, self._mc, self.rank, self.nranks, self._epoch,
+            self.num_blocks, out.data_ptr(), b, s, h, None if bias is None else bias.data_ptr(),
+            None if residual is None else residual.data_ptr(), float(p), int(seed), int(offset),
+            None if mask_in is None else mask_in.data_ptr(), self._symm_offset(part)), "fx_tp_reduce_scatter_bdr")
+        return out
+
+    def sp_reduce_scatter(self, part, b, s):
+        return self.sp_reduce_scatter_bdr(part, b, s, None, None, 0.0, 0, 0)
 
     def native_comm(self, rows: int, cols: int, device):
         """fx_tp_comm for the native whole-layer entry points (fleetx_b200.native): this group's symmetric
@@ -310,3 +371,100 @@ def c_identity(x: torch.Tensor, group) -> torch.Tensor:
 
 def mp_allreduce(x: torch.Tensor, group) -> torch.Tensor:
     return _MpAllReduce.apply(x, group)
+
+
+# ---------------------------------------------------------------------------- sequence-parallel operators
+# sequence_parallel_utils.py:36-126: scatter / all_gather / reduce_scatter along dim 0 of a sequence-first
+# [s, b, h] tensor and the four autograd operators built on them. These keep the reference's layout on both
+# sides (no permutation): the building blocks of ColumnSequenceParallelLinear / RowSequenceParallelLinear
+# outside the fused layer path, and what the CPU (gloo) tests drive.
+def sp_scatter(x: torch.Tensor, group) -> torch.Tensor:
+    n = group.nranks
+    if x.shape[0] % n != 0:
+        raise ValueError(f"Input sequence length {x.shape[0]} can't be divided exactly by sequence parallelism {n}")
+    sl = x.shape[0] // n
+    return x[group.rank * sl:(group.rank + 1) * sl].contiguous()
+
+
+def sp_all_gather_dim0(x: torch.Tensor, group) -> torch.Tensor:
+    n = group.nranks
+    if n == 1:
+        return x
+    out = torch.empty((x.shape[0] * n,) + tuple(x.shape[1:]), dtype=x.dtype, device=x.device)
+    group._dist.all_gather_into_tensor(out, x.contiguous(), group=group.pg)
+    return out
+
+
+def sp_reduce_scatter_dim0(x: torch.Tensor, group) -> torch.Tensor:
+    n = group.nranks
+    if n == 1:
+        return x
+    if x.shape[0] % n != 0:
+        raise ValueError(f"Input sequence length {x.shape[0]} can't be divided exactly by sequence parallelism {n}")
+    if group._dist.get_backend(group.pg) == "nccl":
+        out = torch.empty((x.shape[0] // n,) + tuple(x.shape[1:]), dtype=x.dtype, device=x.device)
+        group._dist.reduce_scatter_tensor(out, x.contiguous(), op=group._dist.ReduceOp.SUM, group=group.pg)
+        return out
+    t = x.clone()
+    group._dist.all_reduce(t, op=group._dist.ReduceOp.SUM, group=group.pg)  # gloo has no reduce_scatter
+    return sp_scatter(t, group)
+
+
+class ScatterOp(torch.autograd.Function):
+    """[s, b, h] -> [s/n, b, h]; backward all-gathers (sequence_parallel_utils.py:73-83)."""
+
+    @staticmethod
+    def forward(ctx, x, group):
+        ctx.group = group
+        return sp_scatter(x, group)
+
+    @staticmethod
+    def backward(ctx, g):
+        return sp_all_gather_dim0(g, ctx.group), None
+
+
+class GatherOp(torch.autograd.Function):
+    """[s/n, b, h] -> [s, b, h]; backward scatters (:86-96)."""
+
+    @staticmethod
+    def forward(ctx, x, group):
+        ctx.group = group
+        return sp_all_gather_dim0(x, group)
+
+    @staticmethod
+    def backward(ctx, g):
+        return sp_scatter(g, ctx.group), None
+
+
+class AllGatherOp(torch.autograd.Function):
+    """all-gather forward, reduce-scatter backward (:99-112): in front of ColumnSequenceParallelLinear."""
+
+    @staticmethod
+    def forward(ctx, x, group):
+        ctx.group = group
+        return sp_all_gather_dim0(x, group)
+
+    @staticmethod
+    def backward(ctx, g):
+        return sp_reduce_scatter_dim0(g, ctx.group), None
+
+
+class ReduceScatterOp(torch.autograd.Function):
+    """reduce-scatter forward, all-gather backward (:115-126): behind RowSequenceParallelLinear's matmul."""
+
+    @staticmethod
+    def forward(ctx, x, group):
+        ctx.group = group
+        return sp_reduce_scatter_dim0(x, group)
+
+    @staticmethod
+    def backward(ctx, g):
+        return sp_all_gather_dim0(g, ctx.group), None
+
+
+def all_reduce_gradient_hook(group):
+    """sequence_parallel_utils.py:136-140: parameters that see only this rank's sequence shard (LayerNorm
+    weight / bias, the bias of RowSequenceParallelLinear) sum their gradients over the mp group."""
+    def hook(grad):
+        return group.all_reduce_(grad.contiguous())
+    return hook

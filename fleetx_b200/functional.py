@@ -62,6 +62,8 @@ class LayerMeta:
     # activation recompute (hybrid_model.py:332-335 'core_attn', :537-539 'full_attn', :406-408 'full'):
     # None keeps every activation; otherwise the named part of the forward is re-run inside backward
     recompute: Optional[str] = None
+    # sequence_parallel (hybrid_model.py:462, 475-520): activations between the blocks are [s/n, b, h] shards
+    sequence_parallel: bool = False
 
 
 import os as _os
@@ -279,6 +281,98 @@ def saved_bytes(saved: dict) -> int:
     return n
 
 
+# ---------------------------------------------------------------------------- sequence parallel
+def decoder_layer_fwd_sp(x_shard: torch.Tensor, P: LayerParams, M: LayerMeta, group):
+    """sequence_parallel=True (hybrid_model.py:475-520 with Column/RowSequenceParallelLinear,
+    sequence_parallel_utils.py:150-326): x_shard is THIS rank's [s/n, b, h] slice of the sequence-first
+    activations; LayerNorm, dropout and the residual adds run on the shard only, an all-gather stands in
+    front of each column-parallel matmul and a reduce-scatter (fused with bias + dropout + residual)
+    behind each row-parallel one. Returns ([s/n, b, h], saved)."""
+    if not M.normalize_before:
+        raise NotImplementedError("sequence_parallel with normalize_before=False is not built (the reference "
+                                  "configurations are pre-LN)")
+    sl, b, h = x_shard.shape
+    n = group.nranks
+    s = sl * n
+    T, Tl = b * s, sl * b
+    dev = x_shard.device
+    xs = x_shard.reshape(Tl, h)
+    scale = M.hd ** -0.5
+
+    ln1, mean1, rstd1 = ops.layernorm_fwd(xs, P.norm1_w, P.norm1_b, M.eps)          # :534 on the shard
+    a_full = group.sp_all_gather(ln1, b, s)                                          # AllGatherOp, utils:225
+    qkv = ops.gemm(a_full, P.qkv_w, epilogue=FX_EPI_BIAS, bias=P.qkv_b)
+    ctx, lse, attn_mask = ops.attn_causal_fwd(qkv.view(b, s, -1), M.nh_local, M.hd, scale, M.p_attn, *M.rng_attn)
+    ctx2 = ctx.view(T, -1)
+    part = ops.gemm(ctx2, P.out_w, out=group.partial_buffer(T, h, dev))
+    # ReduceScatterOp (utils:319) + bias (:322) + dropout1 + residual (:546-547), one kernel
+    x1 = group.sp_reduce_scatter_bdr(part, b, s, P.out_b, xs, M.p_hidden1, *M.rng_h1, mask_in=M.mask_h1)
+    ln2, mean2, rstd2 = ops.layernorm_fwd(x1, P.norm2_w, P.norm2_b, M.eps)           # :554
+    f_full = group.sp_all_gather(ln2, b, s)
+    z = torch.empty(T, P.lin1_w.shape[1], dtype=torch.bfloat16, device=dev)
+    act = ops.gemm(f_full, P.lin1_w, epilogue=FX_EPI_BIAS_GELU, bias=P.lin1_b, aux=z)
+    part = ops.gemm(act, P.lin2_w, out=group.partial_buffer(T, h, dev))
+    out = group.sp_reduce_scatter_bdr(part, b, s, P.lin2_b, x1, M.p_hidden2, *M.rng_h2, mask_in=M.mask_h2)
+    saved = dict(x=xs, ln1=ln1, mean1=mean1, rstd1=rstd1, qkv=qkv, ctx=ctx2, lse=lse, attn_mask=attn_mask, x1=x1,
+                 ln2=ln2, mean2=mean2, rstd2=rstd2, z=z, act=act, shape=(b, s, h))
+    return out.view(sl, b, h), saved
+
+
+def decoder_layer_bwd_sp(dout_shard: torch.Tensor, saved: dict, P: LayerParams, M: LayerMeta, group):
+    """Adjoint of decoder_layer_fwd_sp: every all-gather becomes a reduce-scatter and back
+    (sequence_parallel_utils.py:99-126); the gathered LayerNorm outputs are not kept but gathered again for
+    the weight gradients; gradients of parameters that saw only this rank's rows (LayerNorm weight / bias,
+    out_proj / linear2 bias) are summed over the group (all_reduce_gradient_hook, utils:136-140, :297-298,
+    hybrid_model.py:515-520)."""
+    b, s, h = saved["shape"]
+    n = group.nranks
+    T, Tl = b * s, (s // n) * b
+    dev = dout_shard.device
+    d = dout_shard.reshape(Tl, h)
+    scale = M.hd ** -0.5
+    g = {}
+
+    d_y2s = ops.bias_dropout_residual_bwd(d, M.p_hidden2, *M.rng_h2, mask_in=M.mask_h2)
+    lin2_b = ops.colsum(d_y2s, out_dtype=torch.float32)
+    d_y2 = group.sp_all_gather(d_y2s, b, s)                                          # backward of ReduceScatterOp
+    d_z = ops.gemm(d_y2, P.lin2_w, trans_b=True, epilogue=FX_EPI_DGELU, aux=saved["z"])
+    g["lin2_w"] = ops.gemm(saved["act"], d_y2, trans_a=True)
+    d_ln2_part = ops.gemm(d_z, P.lin1_w, trans_b=True, out=group.partial_buffer(T, h, dev))
+    d_ln2s = group.sp_reduce_scatter(d_ln2_part, b, s)                               # backward of AllGatherOp
+    g["lin1_b"] = ops.colsum(d_z)
+    f_full = group.sp_all_gather(saved["ln2"], b, s)
+    g["lin1_w"] = ops.gemm(f_full, d_z, trans_a=True)
+    del d_z
+    d_x1s, norm2_w, norm2_b = ops.layernorm_bwd(d_ln2s, saved["x1"], P.norm2_w, saved["mean2"], saved["rstd2"],
+                                                dresidual=d)
+    d_aos = ops.bias_dropout_residual_bwd(d_x1s, M.p_hidden1, *M.rng_h1, mask_in=M.mask_h1)
+    out_b = ops.colsum(d_aos, out_dtype=torch.float32)
+    d_ao = group.sp_all_gather(d_aos, b, s)
+    d_ctx = ops.gemm(d_ao, P.out_w, trans_b=True)
+    g["out_w"] = ops.gemm(saved["ctx"], d_ao, trans_a=True)
+    d_qkv = ops.attn_causal_bwd(d_ctx.view(b, s, -1), saved["qkv"].view(b, s, -1), saved["ctx"].view(b, s, -1),
+                                saved["lse"], saved["attn_mask"], M.nh_local, M.hd, scale, M.p_attn).view(T, -1)
+    del d_ctx
+    d_ln1_part = ops.gemm(d_qkv, P.qkv_w, trans_b=True, out=group.partial_buffer(T, h, dev))
+    d_ln1s = group.sp_reduce_scatter(d_ln1_part, b, s)
+    g["qkv_b"] = ops.colsum(d_qkv)
+    a_full = group.sp_all_gather(saved["ln1"], b, s)
+    g["qkv_w"] = ops.gemm(a_full, d_qkv, trans_a=True)
+    del d_qkv
+    dxs, norm1_w, norm1_b = ops.layernorm_bwd(d_ln1s, saved["x"], P.norm1_w, saved["mean1"], saved["rstd1"],
+                                              dresidual=d_x1s)
+    # one small fp32 allreduce for the six shard-local parameter gradients
+    parts = [norm1_w, norm1_b, norm2_w, norm2_b, out_b, lin2_b]
+    flat = torch.cat([t.reshape(-1) for t in parts])
+    group.all_reduce_(flat)
+    o = 0
+    for name, t in zip(("norm1_w", "norm1_b", "norm2_w", "norm2_b", "out_b", "lin2_b"), parts):
+        v = flat[o:o + t.numel()].view(t.shape)
+        g[name] = v if name.startswith("norm") else v.to(torch.bfloat16)
+        o += t.numel()
+    return dxs.view(s // n, b, h), g
+
+
 _GRAD_ORDER = ("norm1_w", "norm1_b", "qkv_w", "qkv_b", "out_w", "out_b",
                "norm2_w", "norm2_b", "lin1_w", "lin1_b", "lin2_w", "lin2_b")
 
@@ -291,12 +385,22 @@ class DecoderLayerFunction(torch.autograd.Function):
         P = LayerParams(*params)
         if meta.recompute is not None and meta.recompute not in RECOMPUTE_GRANULARITIES:
             raise ValueError(f"recompute_granularity must be one of {RECOMPUTE_GRANULARITIES}, got {meta.recompute!r}")
+        if meta.sequence_parallel:
+            if meta.recompute is not None:
+                raise NotImplementedError("recompute together with sequence_parallel is not built")
+            out, saved = decoder_layer_fwd_sp(x, P, meta, group)
+            ctx.saved, ctx.P, ctx.meta, ctx.group = saved, P, meta, group
+            return out
         out, saved = decoder_layer_fwd(x, P, meta, group)
         ctx.saved, ctx.P, ctx.meta, ctx.group = prune_saved(saved, meta), P, meta, group
         return out
 
     @staticmethod
     def backward(ctx, dout):
+        if ctx.meta.sequence_parallel:
+            dx, g = decoder_layer_bwd_sp(dout.contiguous(), ctx.saved, ctx.P, ctx.meta, ctx.group)
+            ctx.saved = None
+            return (dx, None, None) + tuple(g[k] for k in _GRAD_ORDER)
         saved = rebuild_saved(ctx.saved, ctx.P, ctx.meta, ctx.group)
         dx, g = decoder_layer_bwd(dout.contiguous(), saved, ctx.P, ctx.meta, ctx.group)
         ctx.saved = None
@@ -351,6 +455,19 @@ class RowParallelLinearFunction(torch.autograd.Function):
         db = ops.colsum(dy2) if ctx.has_bias else None
         dx = ops.gemm(dy2, weight, trans_b=True)
         return dx.view(ctx.in_shape), dw, db, None
+
+
+class AddBiasFunction(torch.autograd.Function):
+    """y + bias over the last dim (RowSequenceParallelLinear adds its bias after the reduce-scatter,
+    sequence_parallel_utils.py:322), with the library's own kernels on both sides."""
+
+    @staticmethod
+    def forward(ctx, y, bias):
+        return _add_bias(y.reshape(-1, y.shape[-1]).contiguous(), bias).view(y.shape)
+
+    @staticmethod
+    def backward(ctx, dy):
+        return dy, ops.colsum(dy.reshape(-1, dy.shape[-1]).contiguous())
 
 
 def _add_bias(y: torch.Tensor, bias: torch.Tensor) -> torch.Tensor:

@@ -91,6 +91,49 @@ class RowParallelLinear(nn.Module):
         return Fn.RowParallelLinearFunction.apply(x, self.weight, self.bias, self.model_parallel_group)
 
 
+class ColumnSequenceParallelLinear(ColumnParallelLinear):
+    """sequence_parallel_utils.py:150-232: the input is this rank's [s/n, b, h] sequence shard; an
+    all-gather along the sequence (AllGatherOp: reduce-scatter in backward) stands in front of the matmul.
+    Stand-alone form; inside TransformerDecoderLayer(sequence_parallel=True) the gather is the library's
+    own kernel and the layer runs as one autograd node."""
+
+    def __init__(self, in_features, out_features, weight_attr=None, has_bias=None, gather_output=True,
+                 fuse_matmul_bias=False, mp_group=None, name=None, device="cuda", dtype=torch.bfloat16):
+        assert gather_output is False, "If sequence_parallel is True, gather_output is False"  # utils:171-172
+        super().__init__(in_features, out_features, weight_attr, has_bias, False, fuse_matmul_bias, mp_group, name,
+                         device, dtype)
+
+    def forward(self, x):
+        from .dist import AllGatherOp, SingleGroup
+
+        x = AllGatherOp.apply(x, self.model_parallel_group) if self.is_mp else x  # utils:224-227
+        return Fn.ColumnParallelLinearFunction.apply(x, self.weight, self.bias, SingleGroup())
+
+
+class RowSequenceParallelLinear(RowParallelLinear):
+    """sequence_parallel_utils.py:235-326: local matmul, reduce-scatter along the sequence
+    (ReduceScatterOp: all-gather in backward), then the bias, whose gradient — it only sees this rank's rows
+    — is summed over the mp group by a hook (:297-298)."""
+
+    def __init__(self, in_features, out_features, weight_attr=None, has_bias=True, input_is_parallel=False,
+                 fuse_matmul_bias=False, mp_group=None, name=None, device="cuda", dtype=torch.bfloat16):
+        assert input_is_parallel is True, "If sequence_parallel is True, input_is_parallel should be true."  # utils:262-263
+        super().__init__(in_features, out_features, weight_attr, has_bias, True, fuse_matmul_bias, mp_group, name,
+                         device, dtype)
+        if self.bias is not None and self.is_mp:
+            from .dist import all_reduce_gradient_hook
+
+            self.bias.register_hook(all_reduce_gradient_hook(self.model_parallel_group))
+
+    def forward(self, x):
+        from .dist import ReduceScatterOp, SingleGroup
+
+        y = Fn.RowParallelLinearFunction.apply(x, self.weight, None, SingleGroup())
+        if self.is_mp:
+            y = ReduceScatterOp.apply(y, self.model_parallel_group)                # utils:319
+        return Fn.AddBiasFunction.apply(y, self.bias) if self.bias is not None else y  # utils:322
+
+
 class LayerNorm(nn.Module):
     """nn.LayerNorm(d_model, epsilon) with fp32 affine parameters (they stay fp32 under AMP-O2)."""
 
@@ -122,9 +165,7 @@ class MultiHeadAttention(nn.Module):
         self.fuse = fuse
         self.use_recompute = use_recompute
         self.recompute_granularity = recompute_granularity
-        self.sequence_parallel = sequence_parallel
-        if sequence_parallel:
-            raise NotImplementedError("sequence_parallel is the next scope row (SURVEY §8f #1), not built yet")
+        self.sequence_parallel = sequence_parallel  # honoured by TransformerDecoderLayer; see forward()
         if not fuse:
             raise NotImplementedError("only the fused qkv projection (fuse=True, the reference default) is built")
         if need_weights:
@@ -154,6 +195,9 @@ class MultiHeadAttention(nn.Module):
                                       "hybrid_model.py:733-734); the model's eval mask is the same causal mask")
         if (key is not None and key is not query) or (value is not None and value is not query):
             raise NotImplementedError("self-attention only")
+        if self.sequence_parallel:
+            raise NotImplementedError("sequence_parallel runs through TransformerDecoderLayer (one fused node); the "
+                                      "stand-alone attention module takes batch-first [b, s, h] input only")
         mix = self.qkv_proj(query)  # [b, s, 3h/n], packed per head q|k|v
         p = self.dropout if self.training else 0.0
         seed, offset = (0, 0)
@@ -183,8 +227,8 @@ class TransformerDecoderLayer(nn.Module):
         self.use_recompute = use_recompute
         self.recompute_granularity = recompute_granularity
         self.sequence_parallel = sequence_parallel
-        if sequence_parallel:
-            raise NotImplementedError("sequence_parallel is the next scope row (SURVEY §8f #1), not built yet")
+        if sequence_parallel and not normalize_before:
+            raise NotImplementedError("sequence_parallel with normalize_before=False is not built")
         if activation != "gelu":
             # the reference stores `activation` but hard-codes F.gelu(approximate=True) (:523, :558)
             raise NotImplementedError("the reference layer always applies tanh-GELU")
@@ -237,6 +281,7 @@ class TransformerDecoderLayer(nn.Module):
         return Fn.LayerMeta(nh_local=self.self_attn.num_heads, hd=self.self_attn.head_dim, p_attn=p_attn,
                             p_hidden1=p1, p_hidden2=p2, normalize_before=self.normalize_before,
                             rng_attn=rng_attn, rng_h1=rng_h1, rng_h2=rng_h2, recompute=recompute,
+                            sequence_parallel=self.sequence_parallel,
                             mask_h1=self._inject_mask1 if p1 > 0 else None,
                             mask_h2=self._inject_mask2 if p2 > 0 else None)
 

@@ -162,6 +162,28 @@ int fx_tp_allreduce_bdr(void* stream, const uint64_t* peer_bufs, const uint64_t*
                         uint64_t seed, uint64_t offset, const uint8_t* mask_in, uint64_t buf_elem_offset,
                         uint64_t dropout_elem_offset);
 
+/* ---- sequence parallelism: sequence_parallel_utils.py:36-126 (scatter / all_gather / reduce_scatter and
+ * the four PyLayers built on them), used by Column/RowSequenceParallelLinear (:150-326) ------------------
+ * Between the attention and FFN blocks rank r holds the rows of ITS s/n sequence positions, sequence-first:
+ * a shard is bf16 [s/n, b, h] (the reference's layout). The two halves of the allreduce above, with the
+ * permutation to the batch-first [b, s, h] layout of the GEMM / attention kernels folded in; same symmetric
+ * buffer, flag pages, epoch counting and num_blocks rule as fx_tp_allreduce_bdr (calls of all three may be
+ * mixed on one set of buffers; every call counts as one epoch).
+ *  - fx_tp_allgather_rows: AllGatherOp forward / ReduceScatterOp backward. Publishes this rank's shard;
+ *    on return (stream order) every rank's copy of the symmetric buffer holds the full [b, s, h] tensor.
+ *  - fx_tp_reduce_scatter_bdr: ReduceScatterOp forward / AllGatherOp backward, fused with what follows
+ *    RowSequenceParallelLinear in the decoder layer: out_shard = residual_shard + dropout(sum + bias)
+ *    over this rank's rows of the partial sums in the symmetric buffers (bias = residual = NULL, p = 0:
+ *    the plain reduce-scatter). The dropout mask is indexed by position in the LOCAL shard — the reference
+ *    draws the mask of a [s/n, b, h] tensor under 'global_seed', which is identical on all mp ranks. */
+int fx_tp_allgather_rows(void* stream, const uint64_t* peer_signal_pads, uint64_t multicast_ptr, int rank, int world,
+                         uint32_t epoch, int num_blocks, const void* shard, int b, int s, int h,
+                         uint64_t buf_elem_offset);
+int fx_tp_reduce_scatter_bdr(void* stream, const uint64_t* peer_signal_pads, uint64_t multicast_ptr, int rank,
+                             int world, uint32_t epoch, int num_blocks, void* out_shard, int b, int s, int h,
+                             const void* bias, const void* residual_shard, float p, uint64_t seed, uint64_t offset,
+                             const uint8_t* mask_in, uint64_t buf_elem_offset);
+
 /* ---- the whole decoder layer: TransformerDecoderLayer.forward, hybrid_model.py:525-566 -------------
  * One call runs every kernel above in the order of the reference forward (LN -> qkv_proj -> core_attn
  * -> out_proj -> allreduce + bias + dropout1 + residual -> LN -> linear1 + GELU -> linear2 -> allreduce

@@ -268,3 +268,48 @@ def make_masks(cfg: LayerConfig, b: int, s: int, seed: int = 1024, offsets=(0, 0
     if cfg.act_dropout > 0:
         h2 = torch.from_numpy(philox.dropout_mask(gseed, offsets[2], b * s * cfg.d_model, cfg.act_dropout)).reshape(b, s, cfg.d_model)
     return DropoutMasks(attn=attn, hidden1=h1, hidden2=h2)
+
+
+# ------------------------------------------------------------------------------------ sequence parallel
+# sequence_parallel=True (hybrid_model.py:475-520, sequence_parallel_utils.py:36-126, 150-326). The layer
+# then works on sequence-first activations and rank r of n keeps only rows [r·s/n, (r+1)·s/n) between the
+# blocks. Summed over the ranks this is the SAME arithmetic as the plain tensor-parallel layer, with one
+# difference the reference makes on purpose or not: dropout1 / dropout2 are applied to the [s/n, b, h]
+# shard under the 'global_seed' stream (hybrid_model.py:546, :556), whose state is identical on all mp
+# ranks, so every rank applies the same mask to its own rows. The oracle therefore restates the
+# sequence-parallel layer as: the plain layer on the batch-first full tensor, with hidden masks that repeat
+# one shard-sized mask n times along the sequence.
+def sp_scatter(x_bsh: torch.Tensor, n: int, r: int) -> torch.Tensor:
+    """Rank r's shard [s/n, b, h] (sequence-first, utils:36-45) of a batch-first [b, s, h] tensor."""
+    b, s, h = x_bsh.shape
+    assert s % n == 0, f"Input sequence length {s} can't be divided exactly by sequence parallelism {n}"
+    sl = s // n
+    return x_bsh[:, r * sl:(r + 1) * sl].transpose(0, 1).contiguous()
+
+
+def sp_gather(shards: List[torch.Tensor]) -> torch.Tensor:
+    """Inverse of sp_scatter: n shards [s/n, b, h] -> batch-first [b, s, h] (utils:47-55)."""
+    return torch.cat(shards, dim=0).transpose(0, 1).contiguous()
+
+
+def sp_tile_mask(mask_shard: torch.Tensor, n: int) -> torch.Tensor:
+    """One [s/n, b, h] keep mask, used by every rank on its own rows -> the equivalent [b, s, h] mask."""
+    return sp_gather([mask_shard] * n)
+
+
+def make_masks_sp(cfg: LayerConfig, b: int, s: int, seed: int = 1024, offsets=(0, 0, 1)) -> DropoutMasks:
+    """Masks of one sequence-parallel layer call: attention as in make_masks; dropout1 / dropout2 drawn for
+    a [s/n, b, h] shard (element index = position in the shard) and repeated over the n ranks."""
+    from . import philox
+
+    n = cfg.num_partitions
+    m = make_masks(cfg, b, s, seed, offsets)
+    gseed = rng_seeds(seed)["global_seed"]
+    shard_elems = (s // n) * b * cfg.d_model
+    if cfg.dropout > 0:
+        sh = torch.from_numpy(philox.dropout_mask(gseed, offsets[1], shard_elems, cfg.dropout)).reshape(s // n, b, cfg.d_model)
+        m.hidden1 = sp_tile_mask(sh, n)
+    if cfg.act_dropout > 0:
+        sh = torch.from_numpy(philox.dropout_mask(gseed, offsets[2], shard_elems, cfg.act_dropout)).reshape(s // n, b, cfg.d_model)
+        m.hidden2 = sp_tile_mask(sh, n)
+    return m

@@ -36,10 +36,32 @@ def _worker(rank, world, port, ret, kind):
         x = torch.randn(b, s, cfg.d_model, generator=g).to(torch.bfloat16)
         dy = torch.randn(b, s, cfg.d_model, generator=g).to(torch.bfloat16)
         set_seed(1024, mp_rank=rank)
-        group = TorchDistGroup() if kind == "nccl" else SymmetricTPGroup(max_elems=b * s * cfg.d_model, num_blocks=32)
+        group = TorchDistGroup() if kind in ("nccl", "sp_nccl") else SymmetricTPGroup(max_elems=b * s * cfg.d_model, num_blocks=32)
         layer = layer_from_oracle_params(cfg, params, group=group, device=f"cuda:{rank}")
         layer.train()
         worst = 0.0
+        if kind in ("sp", "sp_nccl"):
+            # sequence_parallel=True: this rank feeds / returns its [s/n, b, h] shard; the oracle is the plain
+            # layer with the shard-sized hidden masks repeated over the ranks (oracle.make_masks_sp)
+            layer.sequence_parallel = True
+            masks = O.make_masks_sp(cfg, b, s, 1024)
+            y_ref, dx_ref, g_ref = O.decoder_layer_fwd_bwd(x.float(), dy.float(), params, cfg, masks)
+            g_shard = O.shard_params(g_ref, cfg, rank)
+            for it in range(2):
+                set_seed(1024, mp_rank=rank)
+                for p_ in layer.parameters():
+                    p_.grad = None
+                xs = O.sp_scatter(x, world, rank).cuda().requires_grad_(True)
+                ys = layer(xs)
+                ys.backward(O.sp_scatter(dy, world, rank).cuda())
+                torch.cuda.synchronize()
+                errs = {"y": rel_err(ys, O.sp_scatter(y_ref, world, rank)),
+                        "dx": rel_err(xs.grad, O.sp_scatter(dx_ref, world, rank))}
+                for n, p in layer.named_parameters():
+                    errs[n] = rel_err(p.grad, g_shard[n])
+                worst = max(worst, max(errs.values()))
+            ret[rank] = worst
+            return
         for it in range(2):  # twice: the second call reuses the symmetric buffer and the epoch flags
             set_seed(1024, mp_rank=rank)
             for p_ in layer.parameters():
@@ -81,11 +103,12 @@ def _worker(rank, world, port, ret, kind):
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
-@pytest.mark.parametrize("kind", ["nccl", "symmetric", "native"])
+@pytest.mark.parametrize("kind", ["nccl", "symmetric", "native", "sp", "sp_nccl"])
 def test_tp2_layer_matches_oracle(kind):
     """kind = "nccl": torch.distributed allreduce; "symmetric": the library's own fused allreduce
     kernel over NVLink peer memory (csrc/comm.cu); "native": additionally the whole-layer C entry points
-    (csrc/layer.cu) driving that kernel through an fx_tp_comm."""
+    (csrc/layer.cu) driving that kernel through an fx_tp_comm; "sp" / "sp_nccl": sequence_parallel=True with
+    the library's all-gather / reduce-scatter kernel, resp. torch.distributed collectives + permutes."""
     ctx = mp.get_context("spawn")
     ret = ctx.Manager().dict()
     port = _free_port()
