@@ -123,7 +123,9 @@ def run_reference(args):
 def workload_config(args, n):
     return {"workload": f"GPT-1.3B decoder layer fwd+bwd: h={H}, heads={NH}, ffn={FFN}, seq={SEQ}, "
                         f"micro_batch={args.batch}, dropout={DROPOUT}",
-            "global_batch": args.batch, "seq_len": SEQ, "parallelism": f"tp{n}",
+            "global_batch": args.batch, "seq_len": SEQ,
+            "parallelism": f"tp{n}" + ("+sp (sequence_parallel=True: activations between the blocks are [s/n, b, h] "
+                                       "shards)" if getattr(args, "sequence_parallel", 0) and n > 1 else ""),
             "l2": "flushed between timed steps (256 MiB write); working set > L2"}
 
 
@@ -238,19 +240,32 @@ def run_gpu(args):
     }
     layer.load_full_state(full)
     layer.train()
+    sp = bool(args.sequence_parallel) and world > 1
+    layer.sequence_parallel = sp
     x_host = torch.randn(b, s, H, generator=gen).to(torch.bfloat16).pin_memory()
     dy_host = torch.randn(b, s, H, generator=gen).to(torch.bfloat16).pin_memory()
     dx_host = torch.empty_like(x_host).pin_memory()
-    x = x_host.to(dev)
-    dy = dy_host.to(dev)
+    sl = s // world
+    if sp:  # this rank's [s/n, b, h] sequence shard (sequence-first, the reference's layout)
+        xs_host = x_host[:, rank * sl:(rank + 1) * sl].transpose(0, 1).contiguous().pin_memory()
+        dys_host = dy_host[:, rank * sl:(rank + 1) * sl].transpose(0, 1).contiguous().pin_memory()
+        dxs_host = torch.empty_like(xs_host).pin_memory()
+        x, dy = xs_host.to(dev), dys_host.to(dev)
+    else:
+        x = x_host.to(dev)
+        dy = dy_host.to(dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     P = Fn.LayerParams(*[p.detach() for p in layer._params()])
 
     def step_device():
         """The hot path with inputs resident in HBM: explicit forward + backward kernel sequence."""
         meta = layer._meta()
-        out, saved = Fn.decoder_layer_fwd(x, P, meta, group)
-        dx, grads = Fn.decoder_layer_bwd(dy, saved, P, meta, group)
+        if sp:
+            out, saved = Fn.decoder_layer_fwd_sp(x, P, meta, group)
+            dx, grads = Fn.decoder_layer_bwd_sp(dy, saved, P, meta, group)
+        else:
+            out, saved = Fn.decoder_layer_fwd(x, P, meta, group)
+            dx, grads = Fn.decoder_layer_bwd(dy, saved, P, meta, group)
         return out, dx, grads
 
     def barrier():
@@ -322,8 +337,9 @@ def run_gpu(args):
     xs_buf = torch.empty(r1 - r0, H, dtype=torch.bfloat16, device=dev)
     dys_buf = torch.empty(r1 - r0, H, dtype=torch.bfloat16, device=dev)
     xh2, dyh2, dxh2 = x_host.view(T, H), dy_host.view(T, H), dx_host.view(T, H)
-    xd_buf = [torch.empty(b, s, H, dtype=torch.bfloat16, device=dev) for _ in range(2)]
-    dyd_buf = [torch.empty(b, s, H, dtype=torch.bfloat16, device=dev) for _ in range(2)]
+    in_shape = (sl, b, H) if sp else (b, s, H)
+    xd_buf = [torch.empty(in_shape, dtype=torch.bfloat16, device=dev) for _ in range(2)]
+    dyd_buf = [torch.empty(in_shape, dtype=torch.bfloat16, device=dev) for _ in range(2)]
 
     def run_e2e(k_steps):
         main = torch.cuda.current_stream()
@@ -336,7 +352,10 @@ def run_gpu(args):
             with torch.cuda.stream(h2d_s):
                 if done[slot] is not None:
                     h2d_s.wait_event(done[slot])  # the step that last used these buffers has finished
-                if world == 1:
+                if sp:  # the layer consumes and returns this rank's shard: nothing to gather
+                    xd_buf[slot].copy_(xs_host, non_blocking=True)
+                    dyd_buf[slot].copy_(dys_host, non_blocking=True)
+                elif world == 1:
                     xd_buf[slot].copy_(x_host, non_blocking=True)
                     dyd_buf[slot].copy_(dy_host, non_blocking=True)
                 else:
@@ -366,7 +385,10 @@ def run_gpu(args):
             keep.append(xin.grad)
             with torch.cuda.stream(d2h_s):
                 d2h_s.wait_event(ev)
-                dxh2[r0:r1].copy_(xin.grad.view(T, H)[r0:r1], non_blocking=True)
+                if sp:
+                    dxs_host.copy_(xin.grad, non_blocking=True)
+                else:
+                    dxh2[r0:r1].copy_(xin.grad.view(T, H)[r0:r1], non_blocking=True)
             for p_ in layer.parameters():
                 p_.grad = None
         main.wait_stream(d2h_s)
@@ -436,6 +458,8 @@ def main():
     ap.add_argument("--batch", type=int, default=8)
     ap.add_argument("--impl", default="fleetx_b200", choices=["fleetx_b200", "reference"])
     ap.add_argument("--collective", default="fused", choices=["fused", "nccl"])
+    ap.add_argument("--sequence-parallel", type=int, default=int(os.environ.get("FX_BENCH_SP", "0")),
+                    help="1: run the layer with sequence_parallel=True at N > 1 (hybrid_model.py:462)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--profile-mode", action="store_true",
                     help="device-timed steps only (no e2e / CPU legs): the command ncu wraps")

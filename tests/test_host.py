@@ -61,8 +61,15 @@ def test_layer_api_surface_on_cpu():
     assert layer._config["d_model"] == 128 and layer.self_attn.num_heads == 2 and layer.self_attn.head_dim == 64
     with pytest.raises(ValueError):
         TransformerDecoderLayer(128, 2, 512, num_partitions=2, device="cpu")   # group size is 1
-    with pytest.raises(NotImplementedError):
-        TransformerDecoderLayer(128, 2, 512, sequence_parallel=True, device="cpu")
+    assert TransformerDecoderLayer(128, 2, 512, sequence_parallel=True, device="cpu").sequence_parallel
+    with pytest.raises(NotImplementedError):  # sequence parallel is built for the pre-LN layer only
+        TransformerDecoderLayer(128, 2, 512, sequence_parallel=True, normalize_before=False, device="cpu")
+    from fleetx_b200.layers import ColumnSequenceParallelLinear, RowSequenceParallelLinear
+    with pytest.raises(AssertionError):   # sequence_parallel_utils.py:171-172, :262-263
+        ColumnSequenceParallelLinear(16, 32, has_bias=True, gather_output=True, device="cpu")
+    with pytest.raises(AssertionError):
+        RowSequenceParallelLinear(32, 16, input_is_parallel=False, device="cpu")
+    assert RowSequenceParallelLinear(32, 16, input_is_parallel=True, device="cpu").bias.shape == (16,)
     with pytest.raises(AssertionError):
         MultiHeadAttention(100, 3, device="cpu")
     assert ColumnParallelLinear(16, 32, has_bias=True, gather_output=False, device="cpu").bias.shape == (32,)
