@@ -65,6 +65,13 @@ SIGNATURES = {
     "fx_attn_causal_fwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _f, _u64, _u64]),
     "fx_attn_causal_bwd_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "fx_attn_causal_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _f]),
+    "fx_embedding_fwd": (_i, [_vp, _vp, _vp, _vp, C.c_int64, C.c_int64, _vp, _vp, _vp, C.c_int64, _i, _i, _f, _u64, _u64]),
+    "fx_embedding_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, C.c_int64, C.c_int64, _vp, C.c_int64, _i, _i, _f, _u64, _u64]),
+    "fx_f32_to_bf16": (_i, [_vp, _vp, _vp, C.c_int64]),
+    "fx_cross_entropy_stats": (_i, [_vp, _vp, _vp, C.c_int64, C.c_int64, _i, _vp, _vp, _vp]),
+    "fx_cross_entropy_rescale": (_i, [_vp, _vp, _vp, _vp, C.c_int64]),
+    "fx_cross_entropy_loss": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_int64]),
+    "fx_cross_entropy_bwd": (_i, [_vp, _vp, _vp, _vp, C.c_int64, C.c_int64, _i, _vp, _vp, _vp, _vp, _vp]),
     "fx_decoder_layer_saved_bytes": (_sz, [C.POINTER(LayerDesc)]),
     "fx_decoder_layer_workspace_bytes": (_sz, [C.POINTER(LayerDesc)]),
     "fx_decoder_layer_fwd": (_i, [_vp, C.POINTER(LayerDesc), _vp, _vp, _vp, _vp]),

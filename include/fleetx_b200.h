@@ -231,6 +231,43 @@ int fx_decoder_layer_fwd(void* stream, const fx_layer_desc* d, const void* x, vo
 int fx_decoder_layer_bwd(void* stream, const fx_layer_desc* d, const void* dout, const void* x,
                          const void* saved, void* dx, const fx_layer_grads* grads, void* workspace);
 
+/* ---- around the decoder stack: GPTModelHybrid / GPTForPretrainingHybrid ----------------
+ * GPTEmbeddings.forward, hybrid_model.py:603-622: out[t,:] = dropout(word[t,:] + wpe[pos[t],:]) with
+ * word[t,:] = wte[ids[t] - vocab_start,:] on the rank that owns the id and zeros elsewhere
+ * (fleet.meta_parallel.VocabParallelEmbedding, :589-593). ids / pos_ids int64 [T] (pos_ids NULL: t % s, the
+ * default of :604-607); wte bf16 [vocab_rows, h] (this rank's slice), wpe bf16 [max_pos, h]. One rank: one
+ * call. mp > 1: call once with wpe = NULL, p = 0 (the partial lookup), allreduce that tensor, then call
+ * again with word_in = the sum (ids / wte ignored) for the position term and the dropout. */
+int fx_embedding_fwd(void* stream, const int64_t* ids, const int64_t* pos_ids, const void* wte, int64_t vocab_start,
+                     int64_t vocab_rows, const void* word_in, const void* wpe, void* out, int64_t T, int s, int h,
+                     float p, uint64_t seed, uint64_t offset);
+/* Adjoint: d = dropout'(dout); dwte[ids[t] - vocab_start,:] += d[t,:], dwpe[pos[t],:] += d[t,:], both fp32
+ * accumulators (either may be NULL) that are ADDED to with L2 reductions, in no fixed order: zero them, or
+ * let dwte already hold the logits GEMM's share of the tied weight's gradient (:779-781). */
+int fx_embedding_bwd(void* stream, const void* dout, const int64_t* ids, const int64_t* pos_ids, float* dwte,
+                     int64_t vocab_start, int64_t vocab_rows, float* dwpe, int64_t T, int s, int h, float p,
+                     uint64_t seed, uint64_t offset);
+int fx_f32_to_bf16(void* stream, const float* src, void* dst, int64_t n); /* n % 8 == 0 */
+
+/* GPTPretrainingCriterionHybird.forward, hybrid_model.py:801-829: softmax cross entropy per token over the
+ * vocabulary (CrossEntropyLoss(reduction="none"), or fleet.meta_parallel.ParallelCrossEntropy when the
+ * logits are split over mp ranks: logits bf16 [T, vl] = columns [vocab_start, vocab_start + vl)), then
+ * sum(loss * loss_mask) / sum(loss_mask).
+ *   _stats:   lmax[t] = max_c l[t,c]; lsum[t] = sum_c exp(l[t,c] - lmax[t]); target[t] = l[t, label] or 0
+ *   mp > 1:   gmax = allreduce_max(lmax); _rescale (lsum *= exp(lmax - gmax)); allreduce_sum(lsum, target)
+ *   _loss:    out2[0] = sum_t (log gsum + gmax - target) * mask / sum_t mask, out2[1] = sum_t mask;
+ *             loss_tok (may be NULL) receives the per-token losses; loss_mask NULL = all ones
+ *   _bwd:     dlogits[t,c] = (exp(l - gmax) / gsum - [c == label]) * mask[t] / out2[1] * dloss[0]
+ *             (dloss NULL = 1; dlogits may alias logits). */
+int fx_cross_entropy_stats(void* stream, const void* logits, const int64_t* labels, int64_t vocab_start, int64_t T,
+                           int vl, float* lmax, float* lsum, float* target);
+int fx_cross_entropy_rescale(void* stream, const float* lmax, const float* gmax, float* lsum, int64_t T);
+int fx_cross_entropy_loss(void* stream, const float* gmax, const float* gsum, const float* target,
+                          const float* loss_mask, float* loss_tok, float* out2, int64_t T);
+int fx_cross_entropy_bwd(void* stream, const void* logits, void* dlogits, const int64_t* labels, int64_t vocab_start,
+                         int64_t T, int vl, const float* gmax, const float* gsum, const float* loss_mask,
+                         const float* out2, const float* dloss);
+
 #ifdef __cplusplus
 }
 #endif
