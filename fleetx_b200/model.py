@@ -303,6 +303,22 @@ class GPTForPretrainingHybrid(nn.Module):
                                self.gpt.model_parallel_group)
 
 
+def load_full_state(model: "GPTForPretrainingHybrid", full: dict) -> None:
+    """Load FULL (unsharded) reference-named parameters into `model`, keeping this rank's shards: vocabulary
+    rows of the word embedding, and per decoder layer what TransformerDecoderLayer.load_full_state keeps."""
+    gpt = model.gpt
+    we = gpt.embeddings.word_embeddings
+    with torch.no_grad():
+        w = full["gpt.embeddings.word_embeddings.weight"]
+        we.weight.copy_(w[we.vocab_start_index:we.vocab_start_index + we.per_part_size].to(we.weight.dtype))
+        gpt.embeddings.position_embeddings.weight.copy_(full["gpt.embeddings.position_embeddings.weight"].to(we.weight.dtype))
+        gpt.decoder.norm.weight.copy_(full["gpt.decoder.norm.weight"])
+        gpt.decoder.norm.bias.copy_(full["gpt.decoder.norm.bias"])
+    for i, layer in enumerate(gpt.decoder.layers):
+        pre = f"gpt.decoder.layers.{i}."
+        layer.load_full_state({k[len(pre):]: v for k, v in full.items() if k.startswith(pre)})
+
+
 class GPTPretrainingCriterionHybird(nn.Module):
     """hybrid_model.py:791-829 (spelling as in the reference)."""
 

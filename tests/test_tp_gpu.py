@@ -36,10 +36,51 @@ def _worker(rank, world, port, ret, kind):
         x = torch.randn(b, s, cfg.d_model, generator=g).to(torch.bfloat16)
         dy = torch.randn(b, s, cfg.d_model, generator=g).to(torch.bfloat16)
         set_seed(1024, mp_rank=rank)
-        group = TorchDistGroup() if kind in ("nccl", "sp_nccl") else SymmetricTPGroup(max_elems=b * s * cfg.d_model, num_blocks=32)
+        group = TorchDistGroup() if kind in ("nccl", "sp_nccl", "model") else SymmetricTPGroup(max_elems=b * s * cfg.d_model, num_blocks=32)
         layer = layer_from_oracle_params(cfg, params, group=group, device=f"cuda:{rank}")
         layer.train()
         worst = 0.0
+        if kind == "model":
+            # GPTForPretrainingHybrid over 2 mp ranks: vocab-parallel embedding, tensor-parallel layers, split
+            # logits and ParallelCrossEntropy, against the single-process model oracle
+            from fleetx_b200.model import (GPTForPretrainingHybrid, GPTModelHybrid, GPTPretrainingCriterionHybird,
+                                           load_full_state)
+            from oracle import gpt_model as G
+
+            mc = G.ModelConfig(vocab_size=1024, hidden_size=256, num_layers=2, num_attention_heads=4, ffn_hidden_size=1024,
+                               max_position_embeddings=128, num_partitions=world)
+            full = {k: v.to(torch.bfloat16).float() for k, v in G.init_params(mc, 1024).items()}
+            gg = torch.Generator().manual_seed(5)
+            ids = torch.randint(0, mc.vocab_size, (2, 64), generator=gg)
+            labels = torch.randint(0, mc.vocab_size, (2, 64), generator=gg)
+            lmask = (torch.rand(2, 64, generator=gg) > 0.2).float()
+            gpt = GPTModelHybrid(vocab_size=mc.vocab_size, hidden_size=mc.hidden_size, num_layers=mc.num_layers,
+                                 num_attention_heads=mc.num_attention_heads, ffn_hidden_size=mc.ffn_hidden_size,
+                                 max_position_embeddings=mc.max_position_embeddings, num_partitions=world, mp_group=group,
+                                 device=f"cuda:{rank}")
+            model = GPTForPretrainingHybrid(gpt)
+            load_full_state(model, full)
+            model.train()
+            crit = GPTPretrainingCriterionHybird(mp_group=group)
+            set_seed(1024, mp_rank=rank)
+            loss = crit(model(ids.cuda()), labels.cuda(), lmask.cuda())
+            loss.backward()
+            torch.cuda.synchronize()
+            loss_ref, g_ref = G.loss_and_grads(ids, labels, lmask, full, mc, G.make_masks(mc, 2, 64, 1024))
+            worst = abs(loss.item() - loss_ref.item()) / abs(loss_ref.item()) * 10  # loss within 2e-3
+            we = gpt.embeddings.word_embeddings
+            for n, p in model.named_parameters():
+                ref = g_ref[n]
+                if n == "gpt.embeddings.word_embeddings.weight":
+                    ref = ref[we.vocab_start_index:we.vocab_start_index + we.per_part_size]
+                elif ".layers." in n:
+                    i = int(n.split(".layers.")[1].split(".")[0])
+                    pre = f"gpt.decoder.layers.{i}."
+                    lp = O.shard_params({k[len(pre):]: v for k, v in g_ref.items() if k.startswith(pre)}, mc.layer_cfg(), rank)
+                    ref = lp[n[len(pre):]]
+                worst = max(worst, rel_err(p.grad, ref))
+            ret[rank] = worst
+            return
         if kind in ("sp", "sp_nccl"):
             # sequence_parallel=True: this rank feeds / returns its [s/n, b, h] shard; the oracle is the plain
             # layer with the shard-sized hidden masks repeated over the ranks (oracle.make_masks_sp)
@@ -103,7 +144,7 @@ def _worker(rank, world, port, ret, kind):
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
-@pytest.mark.parametrize("kind", ["nccl", "symmetric", "native", "sp", "sp_nccl"])
+@pytest.mark.parametrize("kind", ["nccl", "symmetric", "native", "sp", "sp_nccl", "model"])
 def test_tp2_layer_matches_oracle(kind):
     """kind = "nccl": torch.distributed allreduce; "symmetric": the library's own fused allreduce
     kernel over NVLink peer memory (csrc/comm.cu); "native": additionally the whole-layer C entry points
