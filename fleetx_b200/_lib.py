@@ -38,6 +38,13 @@ class LayerDesc(C.Structure):
                                   "lin1_w", "lin1_b", "lin2_w", "lin2_b")] + [("tp", C.POINTER(TpComm))]
 
 
+class AdamTensor(C.Structure):
+    """fx_adam_tensor (include/fleetx_b200.h)."""
+    _fields_ = [("param", C.c_void_p), ("master", C.c_void_p), ("grad", C.c_void_p), ("m", C.c_void_p), ("v", C.c_void_p),
+                ("n", C.c_int64), ("decay", C.c_float), ("param_f32", C.c_int32), ("grad_f32", C.c_int32),
+                ("is_distributed", C.c_int32)]
+
+
 class LayerGrads(C.Structure):
     """fx_layer_grads (include/fleetx_b200.h)."""
     _fields_ = [(n, C.c_void_p) for n in ("norm1_w", "norm1_b", "norm2_w", "norm2_b", "qkv_w", "qkv_b", "out_w",
@@ -72,6 +79,8 @@ SIGNATURES = {
     "fx_cross_entropy_rescale": (_i, [_vp, _vp, _vp, _vp, C.c_int64]),
     "fx_cross_entropy_loss": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_int64]),
     "fx_cross_entropy_bwd": (_i, [_vp, _vp, _vp, _vp, C.c_int64, C.c_int64, _i, _vp, _vp, _vp, _vp, _vp]),
+    "fx_multi_sq_norm": (_i, [_vp, _vp, _vp, _i, _i, _vp]),
+    "fx_multi_adamw": (_i, [_vp, _vp, _vp, _i, _i, _f, _f, _f, _f, C.c_int64, _vp, _f]),
     "fx_decoder_layer_saved_bytes": (_sz, [C.POINTER(LayerDesc)]),
     "fx_decoder_layer_workspace_bytes": (_sz, [C.POINTER(LayerDesc)]),
     "fx_decoder_layer_fwd": (_i, [_vp, C.POINTER(LayerDesc), _vp, _vp, _vp, _vp]),

@@ -268,6 +268,32 @@ int fx_cross_entropy_bwd(void* stream, const void* logits, void* dlogits, const 
                          int64_t T, int vl, const float* gmax, const float* gsum, const float* loss_mask,
                          const float* out2, const float* dloss);
 
+/* ---- FusedAdamW + ClipGradByGlobalNorm: ppfleetx/optims/optimizer.py:29-50,
+ * pretrain_gpt_base.yaml:69-84. Every parameter of the model in two launches: the host keeps, in DEVICE
+ * memory, a table of tensors and a table of chunks (pairs {tensor index, chunk index}, chunk_elems elements
+ * each, covering every tensor). decay = weight_decay for parameters that decay (names without "bias" /
+ * "norm", optimizer.py:40-44), else 0. master (fp32 copy of a bf16 parameter, multi_precision) may be NULL. */
+typedef struct fx_adam_tensor {
+  void* param;       /* bf16 or fp32 [n] */
+  float* master;     /* fp32 [n] or NULL */
+  const void* grad;  /* bf16 or fp32 [n] */
+  float* m;          /* fp32 [n] first moment  */
+  float* v;          /* fp32 [n] second moment */
+  int64_t n;
+  float decay;
+  int32_t param_f32, grad_f32, is_distributed;
+} fx_adam_tensor;
+/* out_sq2[0] = sum of squared gradients of the mp-distributed parameters, out_sq2[1] = of the replicated
+ * ones (the host allreduces [0] over the mp group: HybridParallelClipGrad). Zeroes out_sq2 first. */
+int fx_multi_sq_norm(void* stream, const fx_adam_tensor* tensors_dev, const int32_t* chunks_dev, int n_chunks,
+                     int chunk_elems, float* out_sq2);
+/* g *= clip_norm / max(sqrt(sq_norm2[0] + sq_norm2[1]), clip_norm) (sq_norm2 NULL or clip_norm <= 0: no
+ * clipping; read on the device, no host sync); p *= 1 - lr*decay; m, v updated; p -= lr/(1-b1^step) *
+ * m / (sqrt(v)/sqrt(1-b2^step) + eps). step counts from 1. */
+int fx_multi_adamw(void* stream, const fx_adam_tensor* tensors_dev, const int32_t* chunks_dev, int n_chunks,
+                   int chunk_elems, float lr, float beta1, float beta2, float eps, int64_t step,
+                   const float* sq_norm2, float clip_norm);
+
 #ifdef __cplusplus
 }
 #endif
