@@ -105,3 +105,28 @@ class FusedAdamW:
     def global_grad_norm(self) -> float:
         """The norm the last step clipped against (host read: for logging and tests)."""
         return float(self._sq.sum().sqrt().item())
+
+
+class CosineAnnealingWithWarmupDecay:
+    """ppfleetx/optims/lr_scheduler.py:20-48 (host arithmetic only): linear warm-up over warmup_rate * decay_steps
+    steps to max_lr, cosine decay to min_lr at decay_steps, min_lr afterwards. step() then get_lr(), as
+    paddle's LRScheduler; last_epoch starts at 0."""
+
+    def __init__(self, max_lr, min_lr, warmup_rate, decay_steps, last_epoch=0, verbose=False, **kwargs):
+        self.decay_steps = decay_steps
+        self.warmup_step = warmup_rate * decay_steps
+        self.max_lr, self.min_lr = max_lr, min_lr
+        self.last_epoch = last_epoch
+
+    def get_lr(self) -> float:
+        import math
+
+        if self.warmup_step > 0 and self.last_epoch <= self.warmup_step:
+            return float(self.max_lr) * self.last_epoch / self.warmup_step
+        if self.last_epoch > self.decay_steps:
+            return self.min_lr
+        ratio = float(self.last_epoch - self.warmup_step) / float(self.decay_steps - self.warmup_step)
+        return self.min_lr + 0.5 * (math.cos(math.pi * ratio) + 1.0) * (self.max_lr - self.min_lr)
+
+    def step(self, epoch=None) -> None:
+        self.last_epoch = self.last_epoch + 1 if epoch is None else epoch

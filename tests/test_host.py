@@ -87,3 +87,23 @@ def test_bench_flop_model_matches_survey():
     # 327.2 MFLOP/token for 1.3B/s2048, 81.8 for 345M/s1024
     assert abs(bench.layer_flops(1, 2048, 2048) / 1e6 - 327.2) < 0.1
     assert abs(bench.layer_flops(1, 1024, 1024) / 1e6 - 81.8) < 0.1
+
+
+def test_lr_scheduler_matches_the_reference_schedule():
+    """lr_scheduler.py:20-48 at pretrain_gpt_base.yaml:75-80 (max 5e-5, min 1e-5, warm-up 1 % of 360000)."""
+    import math
+
+    from fleetx_b200.optim import CosineAnnealingWithWarmupDecay
+
+    sch = CosineAnnealingWithWarmupDecay(5e-5, 1e-5, 0.01, 360000)
+    assert sch.get_lr() == 0.0
+    sch.step(1800)
+    assert abs(sch.get_lr() - 2.5e-5) < 1e-12          # half way through the warm-up
+    sch.step(3600)
+    assert abs(sch.get_lr() - 5e-5) < 1e-12
+    sch.step(3600 + (360000 - 3600) // 2)
+    assert abs(sch.get_lr() - 3e-5) < 1e-9             # middle of the cosine
+    sch.step(360000)
+    assert abs(sch.get_lr() - (1e-5 + 0.5 * (math.cos(math.pi) + 1) * 4e-5)) < 1e-12
+    sch.step(360001)
+    assert sch.get_lr() == 1e-5
