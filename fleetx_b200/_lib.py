@@ -79,6 +79,8 @@ SIGNATURES = {
     "fx_cross_entropy_rescale": (_i, [_vp, _vp, _vp, _vp, C.c_int64]),
     "fx_cross_entropy_loss": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_int64]),
     "fx_cross_entropy_bwd": (_i, [_vp, _vp, _vp, _vp, C.c_int64, C.c_int64, _i, _vp, _vp, _vp, _vp, _vp]),
+    "fx_kv_cache_append": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i]),
+    "fx_attn_decode": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _f]),
     "fx_multi_sq_norm": (_i, [_vp, _vp, _vp, _i, _i, _vp]),
     "fx_multi_adamw": (_i, [_vp, _vp, _vp, _i, _i, _f, _f, _f, _f, C.c_int64, _vp, _f]),
     "fx_decoder_layer_saved_bytes": (_sz, [C.POINTER(LayerDesc)]),

@@ -337,8 +337,10 @@ extern "C" int fx_gemm_bf16(void* stream, int trans_a, int trans_b, int M, int N
                             int ldaux) {
   using namespace fx;
   FX_CHECK_ARG(M > 0 && N > 0 && K > 0, "fx_gemm_bf16: M, N, K must be positive (got %d %d %d)", M, N, K);
-  FX_CHECK_ARG(M % 8 == 0 && N % 8 == 0 && K % 8 == 0,
-               "fx_gemm_bf16: M, N, K must be multiples of 8 (got %d %d %d)", M, N, K);
+  // N, K (and M when A is stored [K, M]) are contiguous dimensions of 16-byte vector / TMA accesses; a plain
+  // row count M may be anything (decoding runs the linears on a handful of token rows)
+  FX_CHECK_ARG(N % 8 == 0 && K % 8 == 0 && (!trans_a || M % 8 == 0),
+               "fx_gemm_bf16: N, K (and M with trans_a) must be multiples of 8 (got M %d N %d K %d)", M, N, K);
   FX_CHECK_ARG(A && B && C, "fx_gemm_bf16: null operand");
   FX_CHECK_ARG(lda % 8 == 0 && ldb % 8 == 0 && ldc % 8 == 0, "fx_gemm_bf16: leading dims must be multiples of 8");
   FX_CHECK_ARG(lda >= (trans_a ? M : K) && ldb >= (trans_b ? K : N) && ldc >= N,

@@ -185,11 +185,66 @@ class MultiHeadAttention(nn.Module):
                                           mp_group=self.model_parallel_group, device=device, dtype=dtype)
 
     def gen_cache(self, key, value=None, type=Cache):
-        raise NotImplementedError("KV-cache inference is the next scope row (SURVEY §8f #4), not built yet")
+        """hybrid_model.py:243-266: an empty incremental cache ([b, nh_local, 0, hd]) for `key`'s batch, or one
+        holding the given k, v. StaticCache (encoder-decoder attention) is outside this model."""
+        if type == MultiHeadAttention.StaticCache:
+            raise NotImplementedError("StaticCache is for encoder-decoder attention; GPT has none")
+        if value is None:
+            b = key.shape[0]
+            mk = lambda: torch.empty(b, self.num_heads, 0, self.head_dim, dtype=torch.bfloat16, device=key.device)  # noqa: E731
+            return self.Cache(mk(), mk())
+        return self.Cache(key, value)
+
+    _CAP_STEP = 256  # cache buffers grow in steps, so appending is in place most of the time
+
+    def _cache_buffers(self, cache, need: int):
+        """The [b, nh, cap, hd] buffers behind cache.k / cache.v (views [:, :, :L] of them) with cap >= need:
+        the ones the cache already lives in when they are large enough, else new ones holding the L old rows."""
+        k, v = cache.k, cache.v
+        L = k.shape[2]
+        bk, bv = k._base, v._base
+        ok = (bk is not None and bv is not None and bk.dim() == 4 and bk.is_contiguous() and bv.is_contiguous()
+              and bk.shape[2] >= need and bk.shape == bv.shape and bk.data_ptr() == k.data_ptr()
+              and bv.data_ptr() == v.data_ptr() and bk.shape[:2] == k.shape[:2] and bk.shape[3] == k.shape[3])
+        if ok:
+            return bk, bv
+        cap = max((need + self._CAP_STEP - 1) // self._CAP_STEP * self._CAP_STEP, 2 * L)
+        nk = torch.empty(k.shape[0], k.shape[1], cap, k.shape[3], dtype=torch.bfloat16, device=k.device)
+        nv = torch.empty_like(nk)
+        if L:
+            nk[:, :, :L].copy_(k)
+            nv[:, :, :L].copy_(v)
+        return nk, nv
+
+    def attend_cached(self, mix: torch.Tensor, cache):
+        """core attention of the t new tokens with an incremental cache (:178-184, :268-298 in eval): the new
+        k, v go behind the cached ones; returns (context [b, t, h/n], Cache with L + t rows)."""
+        from . import ops
+
+        b, t = mix.shape[0], mix.shape[1]
+        L = cache.k.shape[2]
+        bk, bv = self._cache_buffers(cache, L + t)
+        ops.kv_cache_append(mix, bk, bv, self.num_heads, self.head_dim, L)
+        scale = self.head_dim ** -0.5
+        if L == 0 and t >= 64:  # a prompt: the tensor-core kernel
+            ctx = ops.attn_causal_fwd(mix, self.num_heads, self.head_dim, scale)[0]
+        else:
+            ctx = ops.attn_decode(mix, bk, bv, self.num_heads, self.head_dim, L, scale)
+        return ctx, self.Cache(bk[:, :, :L + t], bv[:, :, :L + t])
 
     def forward(self, query, key=None, value=None, attn_mask=None, use_cache=False, cache=None):
         if use_cache or cache is not None:
-            raise NotImplementedError("use_cache/cache (inference) is outside the fwd+bwd path")
+            if self.training and self.dropout > 0:
+                raise NotImplementedError("use_cache is the inference path: call eval() first")
+            from . import ops
+
+            with torch.no_grad():
+                q2 = query.reshape(-1, query.shape[-1]).contiguous()
+                mix = ops.gemm(q2, self.qkv_proj.weight, epilogue=ops.FX_EPI_BIAS, bias=self.qkv_proj.bias)
+                ctx, new_cache = self.attend_cached(mix.view(query.shape[0], query.shape[1], -1),
+                                                    cache if cache is not None else self.gen_cache(query))
+                out = self.out_proj(ctx)
+            return (out, new_cache) if use_cache else out
         if attn_mask is not None:
             raise NotImplementedError("only the causal mask is fused (training passes attn_mask=None, "
                                       "hybrid_model.py:733-734); the model's eval mask is the same causal mask")
@@ -285,9 +340,35 @@ class TransformerDecoderLayer(nn.Module):
                             mask_h1=self._inject_mask1 if p1 > 0 else None,
                             mask_h2=self._inject_mask2 if p2 > 0 else None)
 
+    def _forward_cached(self, tgt, use_cache, cache):
+        """hybrid_model.py:525-566 with use_cache=True (inference, no dropout, no autograd): the same kernels as
+        the training forward, the attention going through the KV cache. Returns (out, incremental_cache)."""
+        from . import ops
+
+        if self.training and (self.dropout1_p > 0 or self.dropout2_p > 0 or self.self_attn.dropout > 0):
+            raise NotImplementedError("use_cache is the inference path: call eval() first")
+        a, g = self.self_attn, self.model_parallel_group
+        b, t, h = tgt.shape
+        with torch.no_grad():
+            x = tgt.reshape(b * t, h).contiguous()
+            pre = self.normalize_before
+            attn_in = ops.layernorm_fwd(x, self.norm1.weight, self.norm1.bias, self.norm1._epsilon)[0] if pre else x
+            mix = ops.gemm(attn_in, a.qkv_proj.weight, epilogue=ops.FX_EPI_BIAS, bias=a.qkv_proj.bias)
+            ctx, new_cache = a.attend_cached(mix.view(b, t, -1), cache if cache is not None else a.gen_cache(tgt))
+            part = ops.gemm(ctx.view(b * t, -1), a.out_proj.weight, out=g.partial_buffer(b * t, h, x.device))
+            r1 = g.all_reduce_bias_dropout_residual(part, a.out_proj.bias, x, 0.0, 0, 0)
+            x1 = r1 if pre else ops.layernorm_fwd(r1, self.norm1.weight, self.norm1.bias, self.norm1._epsilon)[0]
+            ffn_in = ops.layernorm_fwd(x1, self.norm2.weight, self.norm2.bias, self.norm2._epsilon)[0] if pre else x1
+            act = ops.gemm(ffn_in, self.linear1.weight, epilogue=ops.FX_EPI_BIAS_GELU, bias=self.linear1.bias)
+            part = ops.gemm(act, self.linear2.weight, out=g.partial_buffer(b * t, h, x.device))
+            r2 = g.all_reduce_bias_dropout_residual(part, self.linear2.bias, x1, 0.0, 0, 0)
+            out = r2 if pre else ops.layernorm_fwd(r2, self.norm2.weight, self.norm2.bias, self.norm2._epsilon)[0]
+        out = out.view(b, t, h)
+        return (out, new_cache) if use_cache else out
+
     def forward(self, tgt, memory=None, tgt_mask=None, use_cache=False, cache=None):
         if use_cache or cache is not None:
-            raise NotImplementedError("use_cache/cache (inference) is outside the fwd+bwd path")
+            return self._forward_cached(tgt, use_cache, cache)
         if tgt_mask is not None:
             raise NotImplementedError("only the causal mask is fused (training passes tgt_mask=None)")
         if not tgt.is_cuda:

@@ -234,14 +234,23 @@ class TransformerDecoder(nn.Module):
             self.norm = None
 
     def forward(self, tgt, memory=None, tgt_mask=None, memory_mask=None, use_cache=False, cache=None):
-        if use_cache or cache is not None:
-            raise NotImplementedError("use_cache/cache (inference) is outside the fwd+bwd path")
         output = tgt
-        for mod in self.layers:  # 'full' recompute (:406-408) is honoured inside each layer
-            output = mod(output, memory, tgt_mask, use_cache, cache)
+        new_caches = []
+        for i, mod in enumerate(self.layers):  # 'full' recompute (:406-408) is honoured inside each layer
+            if use_cache or cache is not None:  # :396-417
+                output, new_cache = mod(output, memory, tgt_mask=tgt_mask, use_cache=True,
+                                        cache=None if cache is None else cache[i])
+                new_caches.append(new_cache)
+            else:
+                output = mod(output, memory, tgt_mask, use_cache, cache)
         if self.norm is not None:
             output = _LayerNormFunction.apply(output, self.norm.weight, self.norm.bias, self.norm._epsilon)
-        return output
+        return output if not (use_cache or cache is not None) else (output, new_caches)
+
+    def gen_cache(self, memory, do_zip=False):
+        """hybrid_model.py:425-437."""
+        cache = [layer.gen_cache(memory) for layer in self.layers]
+        return list(zip(*cache)) if do_zip else cache
 
 
 class GPTModelHybrid(nn.Module):
@@ -280,12 +289,14 @@ class GPTModelHybrid(nn.Module):
                                           sequence_parallel=sequence_parallel, device=device)
 
     def forward(self, input_ids, position_ids=None, attention_mask=None, use_cache=False, cache=None):
-        if use_cache or cache is not None:
-            raise NotImplementedError("use_cache/cache (inference) is outside the fwd+bwd path")
         if attention_mask is not None:
             raise NotImplementedError("only the causal mask is fused (training passes no attention_mask)")
+        if position_ids is None and cache is not None:  # :697-705: positions continue behind the cached tokens
+            past = cache[0].k.shape[-2]
+            position_ids = torch.arange(past, past + input_ids.shape[-1], dtype=torch.int64, device=input_ids.device)
+            position_ids = position_ids.unsqueeze(0).expand_as(input_ids).contiguous()
         embedding_output = self.embeddings(input_ids=input_ids, position_ids=position_ids)  # :710-711
-        return self.decoder(embedding_output, memory=None, tgt_mask=None, use_cache=False, cache=None)
+        return self.decoder(embedding_output, memory=None, tgt_mask=None, use_cache=use_cache, cache=cache)
 
 
 class GPTForPretrainingHybrid(nn.Module):
@@ -297,10 +308,12 @@ class GPTForPretrainingHybrid(nn.Module):
 
     def forward(self, input_ids, position_ids=None, attention_mask=None, masked_positions=None, use_cache=False,
                 cache=None):
-        encoder_outputs = self.gpt(input_ids, position_ids=position_ids, attention_mask=attention_mask,
-                                   use_cache=use_cache, cache=cache)
-        return parallel_matmul(encoder_outputs, self.gpt.embeddings.word_embeddings.weight, True,
-                               self.gpt.model_parallel_group)
+        outputs = self.gpt(input_ids, position_ids=position_ids, attention_mask=attention_mask,
+                           use_cache=use_cache, cache=cache)
+        encoder_outputs, cached_kvs = outputs if (use_cache or cache is not None) else (outputs, None)  # :771-775
+        logits = parallel_matmul(encoder_outputs, self.gpt.embeddings.word_embeddings.weight, True,
+                                 self.gpt.model_parallel_group)
+        return (logits, cached_kvs) if cached_kvs is not None else logits
 
 
 def load_full_state(model: "GPTForPretrainingHybrid", full: dict) -> None:

@@ -201,3 +201,22 @@ def attn_causal_bwd(dout, qkv, out, lse, mask, nh: int, hd: int, scale: float, p
     check(_lib.lib().fx_attn_causal_bwd(_stream(), _p(dout), _p(qkv), _p(out), _p(lse), _p(mask), _p(dqkv), _p(ws), b,
                                         s, nh, hd, float(scale), float(p_drop)), "fx_attn_causal_bwd")
     return dqkv
+
+
+# ------------------------------------------------------------------------------- KV cache (inference)
+def kv_cache_append(qkv: torch.Tensor, cache_k: torch.Tensor, cache_v: torch.Tensor, nh: int, hd: int, L: int) -> None:
+    """qkv bf16 [b, t, nh*3*hd]; cache_k / cache_v bf16 [b, nh, cap, hd]: write the new k, v into rows [L, L + t)."""
+    _need(qkv, torch.bfloat16, "qkv"), _need(cache_k, torch.bfloat16, "cache_k"), _need(cache_v, torch.bfloat16, "cache_v")
+    b, t = qkv.shape[0], qkv.shape[1]
+    check(_lib.lib().fx_kv_cache_append(_stream(), _p(qkv), _p(cache_k), _p(cache_v), b, t, nh, hd, cache_k.shape[2], int(L)),
+          "fx_kv_cache_append")
+
+
+def attn_decode(qkv: torch.Tensor, cache_k: torch.Tensor, cache_v: torch.Tensor, nh: int, hd: int, L: int, scale: float):
+    """Attention of the t new tokens over cache rows [0, L + i] (after kv_cache_append). -> bf16 [b, t, nh*hd]."""
+    _need(qkv, torch.bfloat16, "qkv"), _need(cache_k, torch.bfloat16, "cache_k"), _need(cache_v, torch.bfloat16, "cache_v")
+    b, t = qkv.shape[0], qkv.shape[1]
+    out = torch.empty(b, t, nh * hd, dtype=torch.bfloat16, device=qkv.device)
+    check(_lib.lib().fx_attn_decode(_stream(), _p(qkv), _p(cache_k), _p(cache_v), _p(out), b, t, nh, hd, cache_k.shape[2], int(L),
+                                    float(scale)), "fx_attn_decode")
+    return out

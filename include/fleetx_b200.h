@@ -110,7 +110,7 @@ int fx_colsum_bf16(void* stream, const void* x, int ldx, void* out, int out_dtyp
  *   trans_b = 0: B stored [K,N] row-major (ldb >= N);  1: B stored [N,K] (ldb >= K)
  * forward y = x·W: (0,0); dgrad dx = dy·W^T: (0,1); wgrad dW = x^T·dy: (1,0).
  * c_dtype FX_BF16 or FX_F32; accumulate != 0 adds into C. bias bf16 [N]; aux bf16 [M,ldaux].
- * All leading dimensions and M, N, K must be multiples of 8; pointers 16-byte aligned. */
+ * All leading dimensions, N, K (and M when trans_a) must be multiples of 8; pointers 16-byte aligned. */
 int fx_gemm_bf16(void* stream, int trans_a, int trans_b, int M, int N, int K, const void* A,
                  int lda, const void* B, int ldb, void* C, int ldc, int c_dtype, int accumulate,
                  int epilogue, const void* bias, void* aux, int ldaux);
@@ -267,6 +267,19 @@ int fx_cross_entropy_loss(void* stream, const float* gmax, const float* gsum, co
 int fx_cross_entropy_bwd(void* stream, const void* logits, void* dlogits, const int64_t* labels, int64_t vocab_start,
                          int64_t T, int vl, const float* gmax, const float* gsum, const float* loss_mask,
                          const float* out2, const float* dloss);
+
+/* ---- KV-cache self-attention in inference: MultiHeadAttention with use_cache=True,
+ * hybrid_model.py:165-186 (k, v of the new tokens concatenated behind cache.k / cache.v) and :268-298 in
+ * eval (no dropout). cache_k / cache_v: bf16 [b, nh, cap, hd], the first L rows per (batch, head) valid — the
+ * reference's Cache(k, v) of shape [b, nh, L, hd] is the [:, :, :L] view. qkv: the packed qkv_proj output of
+ * the t new tokens, bf16 [b, t, nh, 3, hd].
+ *  - fx_kv_cache_append writes the new k, v into rows [L, L + t) (L + t <= cap).
+ *  - fx_attn_decode (after the append): out[b, t, nh*hd]; new token i attends to rows [0, L + i]. Meant for
+ *    small t (decoding); a long prompt runs fx_attn_causal_fwd and then fx_kv_cache_append. */
+int fx_kv_cache_append(void* stream, const void* qkv, void* cache_k, void* cache_v, int b, int t, int nh, int hd,
+                       int cap, int L);
+int fx_attn_decode(void* stream, const void* qkv, const void* cache_k, const void* cache_v, void* out, int b, int t,
+                   int nh, int hd, int cap, int L, float scale);
 
 /* ---- FusedAdamW + ClipGradByGlobalNorm: ppfleetx/optims/optimizer.py:29-50,
  * pretrain_gpt_base.yaml:69-84. Every parameter of the model in two launches: the host keeps, in DEVICE

@@ -149,8 +149,10 @@ def test_standalone_parallel_linears_and_attention_module():
     qq, kk, vv = O.fuse_prepare_qkv(mix, 4, 64)
     ref = O.row_parallel_linear([O.core_attn(qq, kk, vv, 64)], [w["out_proj.weight"]], w["out_proj.bias"])
     assert rel_err(out, ref) < TOL
-    with pytest.raises(NotImplementedError):
-        mha(q.cuda(), use_cache=True)
+    # use_cache (hybrid_model.py:178-184): dropout is 0 here, so the module may serve the inference path as it is;
+    # a prompt through the cache gives the same output and leaves its k, v behind
+    out_c, cache = mha(q.cuda(), use_cache=True)
+    assert rel_err(out_c, ref) < TOL and cache.k.shape == (2, 4, 128, 64)
 
 
 @pytest.mark.parametrize("granularity", ["full", "full_attn", "core_attn"])

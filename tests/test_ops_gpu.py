@@ -90,13 +90,31 @@ def test_gemm_bias_gelu_dgelu_accumulate():
     assert rel_err(c16, base16.float() + a.float() @ w.float()) < BF16_TOL
 
 
+@pytest.mark.parametrize("M", [1, 3, 12, 130])
+def test_gemm_any_row_count(M):
+    """Decoding runs the linears on a handful of token rows: M need not be a multiple of 8 (nor of the tile)."""
+    from fleetx_b200 import ops
+
+    g = torch.Generator().manual_seed(M)
+    a = torch.randn(M, 256, generator=g).to(torch.bfloat16)
+    w = (torch.randn(256, 512, generator=g) * 0.05).to(torch.bfloat16)
+    bias = (torch.randn(512, generator=g) * 0.1).to(torch.bfloat16)
+    out = ops.gemm(a.to(_dev()), w.to(_dev()), epilogue=ops.FX_EPI_BIAS, bias=bias.to(_dev()))
+    assert rel_err(out, a.float() @ w.float() + bias.float()) < BF16_TOL
+    out_t = ops.gemm(a.to(_dev()), w.t().contiguous().to(_dev()), trans_b=True)
+    assert rel_err(out_t, a.float() @ w.float()) < BF16_TOL
+
+
 def test_gemm_rejects_bad_arguments():
     from fleetx_b200 import FleetXError, ops
 
-    a = torch.zeros(12, 16, dtype=torch.bfloat16, device=_dev())  # M = 12 is not a multiple of 8
-    b = torch.zeros(16, 16, dtype=torch.bfloat16, device=_dev())
+    a = torch.zeros(16, 16, dtype=torch.bfloat16, device=_dev())
+    b = torch.zeros(16, 12, dtype=torch.bfloat16, device=_dev())  # N = 12 is not a multiple of 8
     with pytest.raises(FleetXError):
         ops.gemm(a, b)
+    with pytest.raises(FleetXError):  # A stored [K, M]: M is then a contiguous dimension and must be one too
+        ops.gemm(torch.zeros(16, 12, dtype=torch.bfloat16, device=_dev()), torch.zeros(16, 16, dtype=torch.bfloat16, device=_dev()),
+                 trans_a=True)
     with pytest.raises(FleetXError):
         ops.gemm(torch.zeros(16, 16, dtype=torch.bfloat16), torch.zeros(16, 16, dtype=torch.bfloat16))  # CPU tensors
 
