@@ -36,7 +36,7 @@ def test_host_side_helpers_and_argument_validation():
     assert lib.fx_colsum_workspace_bytes(0, 8) == 0
     assert lib.fx_attn_dropout_mask_bytes(2, 100, 3) == 2 * 3 * 100 * 4 * 4  # 1 bit per (row, col), cols padded to 128
     # bad arguments are rejected before any CUDA call, with a message
-    rc = lib.fx_gemm_bf16(None, 0, 0, 12, 16, 16, None, 16, None, 16, None, 16, 0, 0, 0, None, None, 0)
+    rc = lib.fx_gemm_bf16(None, 0, 0, 16, 12, 16, None, 16, None, 16, None, 16, 0, 0, 0, None, None, 0)  # N = 12
     assert rc == -1 and b"multiples of 8" in lib.fx_last_error()
     rc = lib.fx_attn_causal_fwd(None, None, None, None, None, 1, 64, 1, 32, 1.0, 0.0, 0, 0)
     assert rc == -1 and b"head_dim" in lib.fx_last_error()
