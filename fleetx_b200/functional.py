@@ -476,6 +476,23 @@ def _add_bias(y: torch.Tensor, bias: torch.Tensor) -> torch.Tensor:
     return ops.bias_dropout_residual_fwd(y, bias, _zeros_like_cached(y), 0.0, 0, 0)
 
 
+class DropoutFunction(torch.autograd.Function):
+    """nn.Dropout(p, mode="upscale_in_train") on its own (the embedding dropout of the sequence-parallel model,
+    hybrid_model.py:618-619), through the residual kernel with a zero residual; backward regenerates the mask."""
+
+    @staticmethod
+    def forward(ctx, x, p, seed, offset):
+        ctx.cfg = (float(p), int(seed), int(offset))
+        x2 = x.reshape(-1, x.shape[-1]).contiguous()
+        return ops.bias_dropout_residual_fwd(x2, None, _zeros_like_cached(x2), p, seed, offset).view(x.shape)
+
+    @staticmethod
+    def backward(ctx, dout):
+        p, seed, offset = ctx.cfg
+        d2 = dout.reshape(-1, dout.shape[-1]).contiguous()
+        return ops.bias_dropout_residual_bwd(d2, p, seed, offset).view(dout.shape), None, None, None
+
+
 _zero_cache: dict = {}
 
 

@@ -182,8 +182,6 @@ class GPTEmbeddings(nn.Module):
                  type_vocab_size=16, initializer_range=0.02, sequence_parallel=False, mp_group=None, device="cuda",
                  dtype=torch.bfloat16):
         super().__init__()
-        if sequence_parallel:
-            raise NotImplementedError("GPTEmbeddings(sequence_parallel=True) is not built (the decoder layer is)")
         self.sequence_parallel = sequence_parallel
         self.word_embeddings = VocabParallelEmbedding(vocab_size, hidden_size, mp_group=mp_group, device=device, dtype=dtype)
         self.position_embeddings = nn.Embedding(max_position_embeddings, hidden_size, device=device, dtype=dtype)
@@ -193,10 +191,23 @@ class GPTEmbeddings(nn.Module):
 
     def forward(self, input_ids, position_ids=None):
         p = self.dropout_p if self.training else 0.0
+        we = self.word_embeddings
+        if self.sequence_parallel:
+            # :614-619: [b, s, h] -> [s, b, h], keep this rank's sequence shard, then dropout under 'local_seed'
+            # (distinct masks on the mp ranks, each for its own rows)
+            from .dist import ScatterOp
+            from .functional import DropoutFunction
+
+            emb = EmbeddingFunction.apply(we.weight, self.position_embeddings.weight, input_ids, position_ids,
+                                          we.vocab_start_index, 0.0, 0, 0, we.model_parallel_group)
+            emb = ScatterOp.apply(emb.transpose(0, 1).contiguous(), we.model_parallel_group)
+            if p > 0:
+                seed, offset = get_rng_state_tracker().draw("local_seed")
+                emb = DropoutFunction.apply(emb, p, seed, offset)
+            return emb
         # self.dropout(embeddings) runs under Paddle's default generator, which env.py:39 seeds with the same
         # value as the 'global_seed' stream: identical on all mp ranks. Drawn from that stream here.
         seed, offset = get_rng_state_tracker().draw("global_seed") if p > 0 else (0, 0)
-        we = self.word_embeddings
         return EmbeddingFunction.apply(we.weight, self.position_embeddings.weight, input_ids, position_ids,
                                        we.vocab_start_index, p, seed, offset, we.model_parallel_group)
 
@@ -219,7 +230,7 @@ class TransformerDecoder(nn.Module):
     """hybrid_model.py:350-437: the stack of decoder layers and the final LayerNorm."""
 
     def __init__(self, decoder_layers, num_layers, norm=None, hidden_size=None, use_recompute=False,
-                 recompute_granularity="full", sequence_parallel=False, device="cuda"):
+                 recompute_granularity="full", sequence_parallel=False, device="cuda", mp_group=None):
         super().__init__()
         self.num_layers = num_layers
         self.layers = decoder_layers
@@ -228,6 +239,12 @@ class TransformerDecoder(nn.Module):
         self.sequence_parallel = sequence_parallel
         if norm == "LayerNorm":
             self.norm = LayerNorm(hidden_size, epsilon=1e-5, device=device)
+            if sequence_parallel:  # :371-373: the final norm sees only this rank's rows
+                from .dist import all_reduce_gradient_hook, resolve_group
+
+                g = resolve_group(mp_group)
+                self.norm.weight.register_hook(all_reduce_gradient_hook(g))
+                self.norm.bias.register_hook(all_reduce_gradient_hook(g))
         elif norm is not None:
             raise ValueError("Only support LayerNorm")
         else:
@@ -269,9 +286,6 @@ class GPTModelHybrid(nn.Module):
         self.model_parallel_group = resolve_group(mp_group, num_partitions)
         if self.model_parallel_group.nranks <= 1:
             sequence_parallel = False  # :650-652
-        if sequence_parallel:
-            raise NotImplementedError("GPTModelHybrid(sequence_parallel=True): the scatter after the embedding and "
-                                      "the gather before the logits are not wired yet (the decoder layer is built)")
         self.sequence_parallel = sequence_parallel
         self.embeddings = GPTEmbeddings(vocab_size, hidden_size, hidden_dropout_prob, max_position_embeddings,
                                         type_vocab_size, initializer_range, sequence_parallel,
@@ -286,7 +300,8 @@ class GPTModelHybrid(nn.Module):
                 sequence_parallel=sequence_parallel, mp_group=self.model_parallel_group, device=device, dtype=dtype))
         self.decoder = TransformerDecoder(layers, num_layers, norm="LayerNorm", hidden_size=hidden_size,
                                           use_recompute=use_recompute, recompute_granularity=recompute_granularity,
-                                          sequence_parallel=sequence_parallel, device=device)
+                                          sequence_parallel=sequence_parallel, device=device,
+                                          mp_group=self.model_parallel_group)
 
     def forward(self, input_ids, position_ids=None, attention_mask=None, use_cache=False, cache=None):
         if attention_mask is not None:
@@ -296,7 +311,14 @@ class GPTModelHybrid(nn.Module):
             position_ids = torch.arange(past, past + input_ids.shape[-1], dtype=torch.int64, device=input_ids.device)
             position_ids = position_ids.unsqueeze(0).expand_as(input_ids).contiguous()
         embedding_output = self.embeddings(input_ids=input_ids, position_ids=position_ids)  # :710-711
-        return self.decoder(embedding_output, memory=None, tgt_mask=None, use_cache=use_cache, cache=cache)
+        out = self.decoder(embedding_output, memory=None, tgt_mask=None, use_cache=use_cache, cache=cache)
+        if self.sequence_parallel:  # :738-740: [s/n, b, h] shards -> [s, b, h] -> [b, s, h]
+            if use_cache or cache is not None:
+                raise NotImplementedError("use_cache with sequence_parallel is not built")
+            from .dist import GatherOp
+
+            out = GatherOp.apply(out, self.model_parallel_group).transpose(0, 1).contiguous()
+        return out
 
 
 class GPTForPretrainingHybrid(nn.Module):

@@ -108,3 +108,23 @@ def loss_and_grads(input_ids, labels, loss_mask, params, cfg: ModelConfig, masks
     loss = pretraining_loss(gpt_logits(input_ids, ps, cfg, masks), labels, loss_mask)
     loss.backward()
     return loss.detach(), {k: v.grad.detach() for k, v in ps.items()}
+
+
+def make_masks_sp(cfg: ModelConfig, b: int, s: int, seed: int = 1024) -> ModelMasks:
+    """Masks of one training forward of the SEQUENCE-PARALLEL model (hybrid_model.py:614-619, 475-520), stated as
+    full-size masks for the plain oracle model: the embedding dropout runs on each rank's [s/n, b, h] shard under
+    ITS 'local_seed' stream (offset 0; distinct per rank), the attention dropout of layer i takes offset 1 + i of
+    that stream, and dropout1 / dropout2 of layer i take offsets 2i, 2i + 1 of 'global_seed' on the shard — the
+    same shard-sized mask on every rank (decoder_layer.make_masks_sp)."""
+    from . import philox
+
+    n, h = cfg.num_partitions, cfg.hidden_size
+    sl = s // n
+    emb = None
+    if cfg.hidden_dropout_prob > 0:
+        shards = [torch.from_numpy(philox.dropout_mask(L.rng_seeds(seed, r)["local_seed"], 0, sl * b * h,
+                                                       cfg.hidden_dropout_prob)).reshape(sl, b, h) for r in range(n)]
+        emb = L.sp_gather(shards)
+    lc = cfg.layer_cfg()
+    layers = [L.make_masks_sp(lc, b, s, seed, offsets=(1 + i, 2 * i, 2 * i + 1)) for i in range(cfg.num_layers)]
+    return ModelMasks(embedding=emb, layers=layers)

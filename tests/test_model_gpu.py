@@ -86,10 +86,8 @@ def test_cross_entropy_kernels_against_torch():
 
 
 def test_model_rejects_what_is_not_built():
-    from fleetx_b200.model import GPTEmbeddings, GPTModelHybrid
+    from fleetx_b200.model import GPTModelHybrid
 
-    with pytest.raises(NotImplementedError):
-        GPTEmbeddings(512, 128, sequence_parallel=True)
     m = GPTModelHybrid(vocab_size=512, hidden_size=128, num_layers=1, num_attention_heads=2, ffn_hidden_size=512,
                        max_position_embeddings=64)
     with pytest.raises(NotImplementedError):

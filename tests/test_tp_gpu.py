@@ -36,11 +36,11 @@ def _worker(rank, world, port, ret, kind):
         x = torch.randn(b, s, cfg.d_model, generator=g).to(torch.bfloat16)
         dy = torch.randn(b, s, cfg.d_model, generator=g).to(torch.bfloat16)
         set_seed(1024, mp_rank=rank)
-        group = TorchDistGroup() if kind in ("nccl", "sp_nccl", "model") else SymmetricTPGroup(max_elems=b * s * cfg.d_model, num_blocks=32)
+        group = TorchDistGroup() if kind in ("nccl", "sp_nccl", "model", "model_sp") else SymmetricTPGroup(max_elems=b * s * cfg.d_model, num_blocks=32)
         layer = layer_from_oracle_params(cfg, params, group=group, device=f"cuda:{rank}")
         layer.train()
         worst = 0.0
-        if kind == "model":
+        if kind in ("model", "model_sp"):
             # GPTForPretrainingHybrid over 2 mp ranks: vocab-parallel embedding, tensor-parallel layers, split
             # logits and ParallelCrossEntropy, against the single-process model oracle
             from fleetx_b200.model import (GPTForPretrainingHybrid, GPTModelHybrid, GPTPretrainingCriterionHybird,
@@ -57,7 +57,7 @@ def _worker(rank, world, port, ret, kind):
             gpt = GPTModelHybrid(vocab_size=mc.vocab_size, hidden_size=mc.hidden_size, num_layers=mc.num_layers,
                                  num_attention_heads=mc.num_attention_heads, ffn_hidden_size=mc.ffn_hidden_size,
                                  max_position_embeddings=mc.max_position_embeddings, num_partitions=world, mp_group=group,
-                                 device=f"cuda:{rank}")
+                                 sequence_parallel=(kind == "model_sp"), device=f"cuda:{rank}")
             model = GPTForPretrainingHybrid(gpt)
             load_full_state(model, full)
             model.train()
@@ -66,7 +66,8 @@ def _worker(rank, world, port, ret, kind):
             loss = crit(model(ids.cuda()), labels.cuda(), lmask.cuda())
             loss.backward()
             torch.cuda.synchronize()
-            loss_ref, g_ref = G.loss_and_grads(ids, labels, lmask, full, mc, G.make_masks(mc, 2, 64, 1024))
+            masks = G.make_masks_sp(mc, 2, 64, 1024) if kind == "model_sp" else G.make_masks(mc, 2, 64, 1024)
+            loss_ref, g_ref = G.loss_and_grads(ids, labels, lmask, full, mc, masks)
             worst = abs(loss.item() - loss_ref.item()) / abs(loss_ref.item()) * 10  # loss within 2e-3
             we = gpt.embeddings.word_embeddings
             for n, p in model.named_parameters():
@@ -144,7 +145,7 @@ def _worker(rank, world, port, ret, kind):
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
-@pytest.mark.parametrize("kind", ["nccl", "symmetric", "native", "sp", "sp_nccl", "model"])
+@pytest.mark.parametrize("kind", ["nccl", "symmetric", "native", "sp", "sp_nccl", "model", "model_sp"])
 def test_tp2_layer_matches_oracle(kind):
     """kind = "nccl": torch.distributed allreduce; "symmetric": the library's own fused allreduce
     kernel over NVLink peer memory (csrc/comm.cu); "native": additionally the whole-layer C entry points
