@@ -79,6 +79,14 @@ class _GroupOps:
             return y
         return ops.bias_dropout_residual_fwd(y, bias, residual, p, seed, offset, mask_in=mask_in)
 
+    # Split form of the plain reduce-scatter (backward of AllGatherOp): the caller puts the weight-gradient
+    # GEMM that does not depend on it between the two halves. The base version is synchronous.
+    def sp_reduce_scatter_start(self, part, b, s):
+        return self.sp_reduce_scatter(part, b, s)
+
+    def sp_reduce_scatter_finish(self, handle):
+        return handle
+
 
 class SingleGroup(_GroupOps):
     rank = 0
@@ -194,6 +202,31 @@ class SymmetricTPGroup(TorchDistGroup):
 
     def sp_reduce_scatter(self, part, b, s):
         return self.sp_reduce_scatter_bdr(part, b, s, None, None, 0.0, 0, 0)
+
+    def sp_reduce_scatter_start(self, part, b, s):
+        if not self._is_symmetric(part):
+            return super().sp_reduce_scatter_start(part, b, s)
+        h = part.shape[-1]
+        out = torch.empty(s // self.nranks * b, h, dtype=torch.bfloat16, device=part.device)  # on the caller's stream
+        main = torch.cuda.current_stream()
+        ready = torch.cuda.Event()
+        ready.record(main)
+        with torch.cuda.stream(self._comm_stream):
+            self._comm_stream.wait_event(ready)
+            self._epoch += 1
+            self._lib.check(self._lib.lib().fx_tp_reduce_scatter_bdr(
+                self._comm_stream.cuda_stream, self._peer_sigs, self._mc, self.rank, self.nranks, self._epoch,
+                self.num_blocks, out.data_ptr(), b, s, h, None, None, 0.0, 0, 0, None, self._symm_offset(part)),
+                "fx_tp_reduce_scatter_bdr")
+            done = torch.cuda.Event()
+            done.record(self._comm_stream)
+        return ("symm_rs", out, done)
+
+    def sp_reduce_scatter_finish(self, handle):
+        if isinstance(handle, tuple) and len(handle) == 3 and handle[0] == "symm_rs":
+            torch.cuda.current_stream().wait_event(handle[2])
+            return handle[1]
+        return handle
 
     def native_comm(self, rows: int, cols: int, device):
         """fx_tp_comm for the native whole-layer entry points (fleetx_b200.native): this group's symmetric

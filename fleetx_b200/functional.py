@@ -302,6 +302,9 @@ def decoder_layer_fwd_sp(x_shard: torch.Tensor, P: LayerParams, M: LayerMeta, gr
     ln1, mean1, rstd1 = ops.layernorm_fwd(xs, P.norm1_w, P.norm1_b, M.eps)          # :534 on the shard
     a_full = group.sp_all_gather(ln1, b, s)                                          # AllGatherOp, utils:225
     qkv = ops.gemm(a_full, P.qkv_w, epilogue=FX_EPI_BIAS, bias=P.qkv_b)
+    # the gathered tensor is what the weight gradient needs in backward (the reference keeps it too, as the
+    # input of F.linear); it lives in the symmetric buffer, which the next GEMM overwrites: keep a copy
+    a_keep = a_full.clone() if n > 1 else a_full
     ctx, lse, attn_mask = ops.attn_causal_fwd(qkv.view(b, s, -1), M.nh_local, M.hd, scale, M.p_attn, *M.rng_attn)
     ctx2 = ctx.view(T, -1)
     part = ops.gemm(ctx2, P.out_w, out=group.partial_buffer(T, h, dev))
@@ -311,17 +314,18 @@ def decoder_layer_fwd_sp(x_shard: torch.Tensor, P: LayerParams, M: LayerMeta, gr
     f_full = group.sp_all_gather(ln2, b, s)
     z = torch.empty(T, P.lin1_w.shape[1], dtype=torch.bfloat16, device=dev)
     act = ops.gemm(f_full, P.lin1_w, epilogue=FX_EPI_BIAS_GELU, bias=P.lin1_b, aux=z)
+    f_keep = f_full.clone() if n > 1 else f_full
     part = ops.gemm(act, P.lin2_w, out=group.partial_buffer(T, h, dev))
     out = group.sp_reduce_scatter_bdr(part, b, s, P.lin2_b, x1, M.p_hidden2, *M.rng_h2, mask_in=M.mask_h2)
-    saved = dict(x=xs, ln1=ln1, mean1=mean1, rstd1=rstd1, qkv=qkv, ctx=ctx2, lse=lse, attn_mask=attn_mask, x1=x1,
-                 ln2=ln2, mean2=mean2, rstd2=rstd2, z=z, act=act, shape=(b, s, h))
+    saved = dict(x=xs, a_full=a_keep, mean1=mean1, rstd1=rstd1, qkv=qkv, ctx=ctx2, lse=lse, attn_mask=attn_mask, x1=x1,
+                 f_full=f_keep, mean2=mean2, rstd2=rstd2, z=z, act=act, shape=(b, s, h))
     return out.view(sl, b, h), saved
 
 
 def decoder_layer_bwd_sp(dout_shard: torch.Tensor, saved: dict, P: LayerParams, M: LayerMeta, group):
     """Adjoint of decoder_layer_fwd_sp: every all-gather becomes a reduce-scatter and back
-    (sequence_parallel_utils.py:99-126); the gathered LayerNorm outputs are not kept but gathered again for
-    the weight gradients; gradients of parameters that saw only this rank's rows (LayerNorm weight / bias,
+    (sequence_parallel_utils.py:99-126); the two reduce-scatters run on the group's stream underneath the
+    weight-gradient GEMMs of the column-parallel linears; gradients of parameters that saw only this rank's rows (LayerNorm weight / bias,
     out_proj / linear2 bias) are summed over the group (all_reduce_gradient_hook, utils:136-140, :297-298,
     hybrid_model.py:515-520)."""
     b, s, h = saved["shape"]
@@ -338,11 +342,13 @@ def decoder_layer_bwd_sp(dout_shard: torch.Tensor, saved: dict, P: LayerParams, 
     d_z = ops.gemm(d_y2, P.lin2_w, trans_b=True, epilogue=FX_EPI_DGELU, aux=saved["z"])
     g["lin2_w"] = ops.gemm(saved["act"], d_y2, trans_a=True)
     d_ln2_part = ops.gemm(d_z, P.lin1_w, trans_b=True, out=group.partial_buffer(T, h, dev))
-    d_ln2s = group.sp_reduce_scatter(d_ln2_part, b, s)                               # backward of AllGatherOp
+    # backward of AllGatherOp; nothing in linear1's weight gradient depends on it, so the transfer runs on the
+    # group's stream underneath that GEMM
+    pending = group.sp_reduce_scatter_start(d_ln2_part, b, s)
     g["lin1_b"] = ops.colsum(d_z)
-    f_full = group.sp_all_gather(saved["ln2"], b, s)
-    g["lin1_w"] = ops.gemm(f_full, d_z, trans_a=True)
+    g["lin1_w"] = ops.gemm(saved["f_full"], d_z, trans_a=True)
     del d_z
+    d_ln2s = group.sp_reduce_scatter_finish(pending)
     d_x1s, norm2_w, norm2_b = ops.layernorm_bwd(d_ln2s, saved["x1"], P.norm2_w, saved["mean2"], saved["rstd2"],
                                                 dresidual=d)
     d_aos = ops.bias_dropout_residual_bwd(d_x1s, M.p_hidden1, *M.rng_h1, mask_in=M.mask_h1)
@@ -354,11 +360,11 @@ def decoder_layer_bwd_sp(dout_shard: torch.Tensor, saved: dict, P: LayerParams, 
                                 saved["lse"], saved["attn_mask"], M.nh_local, M.hd, scale, M.p_attn).view(T, -1)
     del d_ctx
     d_ln1_part = ops.gemm(d_qkv, P.qkv_w, trans_b=True, out=group.partial_buffer(T, h, dev))
-    d_ln1s = group.sp_reduce_scatter(d_ln1_part, b, s)
+    pending = group.sp_reduce_scatter_start(d_ln1_part, b, s)
     g["qkv_b"] = ops.colsum(d_qkv)
-    a_full = group.sp_all_gather(saved["ln1"], b, s)
-    g["qkv_w"] = ops.gemm(a_full, d_qkv, trans_a=True)
+    g["qkv_w"] = ops.gemm(saved["a_full"], d_qkv, trans_a=True)
     del d_qkv
+    d_ln1s = group.sp_reduce_scatter_finish(pending)
     dxs, norm1_w, norm1_b = ops.layernorm_bwd(d_ln1s, saved["x"], P.norm1_w, saved["mean1"], saved["rstd1"],
                                               dresidual=d_x1s)
     # one small fp32 allreduce for the six shard-local parameter gradients
