@@ -334,8 +334,8 @@ def run_gpu(args):
     # returns its 1/N of the rows. Whole-job host traffic per step is then the same at every N.
     h2d_s, d2h_s = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
     r0, r1 = rank * (T // world), (rank + 1) * (T // world)
-    xs_buf = torch.empty(r1 - r0, H, dtype=torch.bfloat16, device=dev)
-    dys_buf = torch.empty(r1 - r0, H, dtype=torch.bfloat16, device=dev)
+    xs_buf = [torch.empty(r1 - r0, H, dtype=torch.bfloat16, device=dev) for _ in range(2)]
+    dys_buf = [torch.empty(r1 - r0, H, dtype=torch.bfloat16, device=dev) for _ in range(2)]
     xh2, dyh2, dxh2 = x_host.view(T, H), dy_host.view(T, H), dx_host.view(T, H)
     in_shape = (sl, b, H) if sp else (b, s, H)
     xd_buf = [torch.empty(in_shape, dtype=torch.bfloat16, device=dev) for _ in range(2)]
@@ -359,10 +359,8 @@ def run_gpu(args):
                     xd_buf[slot].copy_(x_host, non_blocking=True)
                     dyd_buf[slot].copy_(dy_host, non_blocking=True)
                 else:
-                    xs_buf.copy_(xh2[r0:r1], non_blocking=True)
-                    dys_buf.copy_(dyh2[r0:r1], non_blocking=True)
-                    dist.all_gather_into_tensor(xd_buf[slot].view(-1), xs_buf.view(-1))
-                    dist.all_gather_into_tensor(dyd_buf[slot].view(-1), dys_buf.view(-1))
+                    xs_buf[slot].copy_(xh2[r0:r1], non_blocking=True)
+                    dys_buf[slot].copy_(dyh2[r0:r1], non_blocking=True)
                 ready[slot].record(h2d_s)
 
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -375,6 +373,12 @@ def run_gpu(args):
             if i + 1 < k_steps:
                 h2d(i + 1)
             main.wait_event(ready[slot])
+            if world > 1 and not sp:
+                # The all-gather runs on the MAIN stream, never next to the layer's own collectives: their
+                # blocks spin on each other across ranks and must all be resident, so an NCCL kernel holding SMs
+                # on one rank while waiting for a peer whose SMs are full of spinning blocks would deadlock.
+                dist.all_gather_into_tensor(xd_buf[slot].view(-1), xs_buf[slot].view(-1))
+                dist.all_gather_into_tensor(dyd_buf[slot].view(-1), dys_buf[slot].view(-1))
             flush.zero_()
             xin = xd_buf[slot].detach().requires_grad_(True)
             y = layer(xin)
