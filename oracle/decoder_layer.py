@@ -6,13 +6,16 @@ TransformerDecoderLayer (:439-571) — plus the tensor-parallel linears it is bu
 (fleet.meta_parallel.{Column,Row}ParallelLinear; their in-tree mirrors are
 sequence_parallel_utils.py:150-326 with allreduce in place of reduce-scatter / all-gather).
 
-PARITY UNPINNED: the arithmetic lives in PaddlePaddle (unpinned; Dockerfile:7 installs nightly
-paddlepaddle-gpu==0.0.0.post112, ppfleetx/utils/version.py:18-21 requires >= 2.3.0), which is
-absent from /root/reference and not installable here, and the reference holds no test, golden
-vector or fixture for this path (its only test is codestyle/test_docstring_checker.py). This
-restatement is therefore anchored on the reference's own call sites only; the same math is
-stated three times in-tree (hybrid_model.py, single_model.py:98-116,189-213,397-427,
-auto_model.py:181-206,382-420) and the three agree.
+PARITY: pinned to the reference's own Python, unpinned against Paddle's kernels. The arithmetic of the
+primitives lives in PaddlePaddle (unpinned; Dockerfile:7 installs nightly paddlepaddle-gpu==0.0.0.post112,
+ppfleetx/utils/version.py:18-21 requires >= 2.3.0), which is absent from /root/reference and not
+installable here, and the reference holds no test, golden vector or fixture for this path (its only test
+is codestyle/test_docstring_checker.py). The Python that composes the primitives does run here:
+tools/make_reference_golden.py executes hybrid_model.py / sequence_parallel_utils.py unmodified over the
+torch-backed `paddle` stand-in of oracle/paddle_shim.py (mp 1 / 2 / 4, sequence parallel 2 / 4) and
+tests/test_reference_golden.py holds this restatement to those outputs and gradients (1e-10, fp64). The
+same math is stated three times in-tree (hybrid_model.py, single_model.py:98-116,189-213,397-427,
+auto_model.py:181-206,382-420); the first two are executed and agree bit for bit.
 
 Written in torch-CPU (fp32 / fp64): non-fused, one function per reference op, tensor
 parallelism simulated explicitly (n shards in one process, allreduce = Python sum). Gradients

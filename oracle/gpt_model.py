@@ -1,7 +1,8 @@
 """CPU restatement of the model around the decoder stack — TEST INFRASTRUCTURE ONLY.
 
-PARITY UNPINNED, like oracle/decoder_layer.py: the arithmetic lives in PaddlePaddle (not installable here) and
-the reference holds no test or fixture for it. Restated from
+PARITY as for oracle/decoder_layer.py: held to the reference's own GPTForPretrainingHybrid + criterion executed
+over oracle/paddle_shim.py (tests/golden/ref_model_*.npz, tests/test_reference_golden.py: mp 1 / 2, sequence
+parallel, eval + KV cache); Paddle's kernels for the primitives are not installable here and stay unpinned. Restated from
 ppfleetx/models/language_model/gpt/dygraph/hybrid_model.py:
   GPTEmbeddings.forward            :603-622   word + position embedding, dropout
   TransformerDecoder.forward       :381-423   layers, then the final LayerNorm

@@ -2,7 +2,9 @@
 
 The reference holds no golden vectors for this path and Paddle cannot be imported
 here, so these fixtures pin the ORACLE (regression) and give the GPU tests committed vectors to
-hit; they do not pin the oracle to Paddle ("parity unpinned", see oracle/decoder_layer.py).
+hit. Vectors from the reference's own Python are made by tools/make_reference_golden.py
+(tests/golden/ref_*.npz); tests/test_reference_golden.py also replays the fixtures written here
+through the reference's layer.
 
   python tools/make_golden.py
 """
