@@ -210,3 +210,43 @@ def test_single_card_statement_of_the_layer_agrees_with_the_hybrid_one():
     close(dx, d["out.dx"], "dx", 0.0)
     for k in O.PARAM_NAMES:
         close(grads[k], d["grad." + k], "grad " + k, 0.0)
+
+
+@pytest.mark.skipif(not HAVE_REFERENCE, reason="the reference tree is not on this machine")
+def test_host_mirror_has_the_reference_signatures_and_parameter_names():
+    """The drop-in boundary: every class of the host mirror takes the reference class's arguments, in
+    order, with the same defaults (a mirror may add trailing keyword arguments — device, dtype, mp_group — and may
+    give a default where the reference has none), and holds parameters of the same names and shapes."""
+    import inspect
+
+    from oracle import paddle_shim as S
+
+    S.install("float64")
+    hm, spu = S.load_reference("hybrid_model"), S.load_reference("sequence_parallel_utils")
+    import fleetx_b200.layers as Lm
+    import fleetx_b200.model as Mm
+
+    pairs = [("MultiHeadAttention", hm, Lm), ("TransformerDecoderLayer", hm, Lm), ("TransformerDecoder", hm, Mm),
+             ("GPTEmbeddings", hm, Mm), ("GPTModelHybrid", hm, Mm), ("GPTForPretrainingHybrid", hm, Mm),
+             ("GPTPretrainingCriterionHybird", hm, Mm), ("ColumnSequenceParallelLinear", spu, Lm),
+             ("RowSequenceParallelLinear", spu, Lm)]
+    empty = inspect.Parameter.empty
+    for name, ref_mod, my_mod in pairs:
+        for meth in ("__init__", "forward"):
+            ref = list(inspect.signature(getattr(getattr(ref_mod, name), meth)).parameters.values())
+            mine = list(inspect.signature(getattr(getattr(my_mod, name), meth)).parameters.values())
+            assert [p.name for p in mine[:len(ref)]] == [p.name for p in ref], (name, meth)
+            for r, m in zip(ref, mine):
+                assert r.default is empty or r.default == m.default, (name, meth, r.name, r.default, m.default)
+            assert all(p.default is not empty for p in mine[len(ref):]), (name, meth)
+    # the ops ScatterOp / GatherOp / AllGatherOp / ReduceScatterOp and the hook exist under the reference's names
+    for op in ("ScatterOp", "GatherOp", "AllGatherOp", "ReduceScatterOp", "all_reduce_gradient_hook"):
+        assert hasattr(spu, op) and (hasattr(Lm, op) or hasattr(__import__("fleetx_b200.dist", fromlist=[op]), op)), op
+
+    kw = dict(vocab_size=64, hidden_size=128, num_layers=2, num_attention_heads=2, ffn_hidden_size=512,
+              max_position_embeddings=32)
+    ref_model = S.run_ranks(1, lambda r: hm.GPTForPretrainingHybrid(hm.GPTModelHybrid(**kw)))[0]
+    my_model = Mm.GPTForPretrainingHybrid(Mm.GPTModelHybrid(**kw, device="cpu"))
+    ref_shapes = {k: tuple(v.shape) for k, v in ref_model.named_parameters()}
+    my_shapes = {k: tuple(v.shape) for k, v in my_model.named_parameters()}
+    assert ref_shapes == my_shapes
