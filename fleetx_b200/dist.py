@@ -52,9 +52,9 @@ class _GroupOps:
         n, h = self.nranks, shard.shape[-1]
         if n == 1:
             return shard.view(s, b, h).transpose(0, 1).reshape(b * s, h)
-        full = torch.empty(n, s // n, b, h, dtype=shard.dtype, device=shard.device)
+        full = torch.empty(s, b, h, dtype=shard.dtype, device=shard.device)  # rank-major rows = sequence-first
         self._dist.all_gather_into_tensor(full, shard.contiguous().view(s // n, b, h), group=self.pg)
-        return full.view(s, b, h).transpose(0, 1).reshape(b * s, h)
+        return full.transpose(0, 1).reshape(b * s, h)
 
     def sp_reduce_scatter(self, part: torch.Tensor, b: int, s: int) -> torch.Tensor:
         """partial sums [b * s, h], batch-first -> this rank's rows of the sum, [s/n * b, h] (:58-70)."""

@@ -157,7 +157,7 @@ def decoder_layer_fwd(x: torch.Tensor, P: LayerParams, M: LayerMeta, group):
         x1, mean1, rstd1 = ops.layernorm_fwd(r1, P.norm1_w, P.norm1_b, M.eps)       # :550
         ln2 = mean2 = rstd2 = None
         ffn_in = x1
-    z = torch.empty(T, P.lin1_w.shape[1], dtype=torch.bfloat16, device=x.device)
+    z = torch.empty(T, P.lin1_w.shape[1], dtype=x.dtype, device=x.device)  # bf16: the kernels accept nothing else
     act = ops.gemm(ffn_in, P.lin1_w, epilogue=FX_EPI_BIAS_GELU, bias=P.lin1_b, aux=z)  # :558-559
     y2 = ops.gemm(act, P.lin2_w, out=group.partial_buffer(T, h, x.device))          # :558 local matmul
     # _mp_allreduce, + bias, dropout2 + residual (:556-561)
@@ -312,7 +312,7 @@ def decoder_layer_fwd_sp(x_shard: torch.Tensor, P: LayerParams, M: LayerMeta, gr
     x1 = group.sp_reduce_scatter_bdr(part, b, s, P.out_b, xs, M.p_hidden1, *M.rng_h1, mask_in=M.mask_h1)
     ln2, mean2, rstd2 = ops.layernorm_fwd(x1, P.norm2_w, P.norm2_b, M.eps)           # :554
     f_full = group.sp_all_gather(ln2, b, s)
-    z = torch.empty(T, P.lin1_w.shape[1], dtype=torch.bfloat16, device=dev)
+    z = torch.empty(T, P.lin1_w.shape[1], dtype=x_shard.dtype, device=dev)
     act = ops.gemm(f_full, P.lin1_w, epilogue=FX_EPI_BIAS_GELU, bias=P.lin1_b, aux=z)
     f_keep = f_full.clone() if n > 1 else f_full
     part = ops.gemm(act, P.lin2_w, out=group.partial_buffer(T, h, dev))
@@ -374,7 +374,7 @@ def decoder_layer_bwd_sp(dout_shard: torch.Tensor, saved: dict, P: LayerParams, 
     o = 0
     for name, t in zip(("norm1_w", "norm1_b", "norm2_w", "norm2_b", "out_b", "lin2_b"), parts):
         v = flat[o:o + t.numel()].view(t.shape)
-        g[name] = v if name.startswith("norm") else v.to(torch.bfloat16)
+        g[name] = v if name.startswith("norm") else v.to(P.out_b.dtype)
         o += t.numel()
     return dxs.view(s // n, b, h), g
 
