@@ -200,3 +200,26 @@ def test_tensor_and_sequence_parallel_sequencing_over_gloo(name, world):
         if p.is_alive():
             p.terminate()
     assert dict(ret) == {r: "ok" for r in range(world)}, dict(ret)
+
+
+def test_module_draws_its_dropout_streams_in_the_reference_order():
+    """TransformerDecoderLayer._meta(): one draw per dropout, in the order the executed reference logged them
+    (fixture meta: 'local_seed' for attention, then 'global_seed' twice), nothing drawn in eval mode."""
+    from fleetx_b200.layers import TransformerDecoderLayer
+    from fleetx_b200.rng import get_rng_state_tracker, set_seed
+
+    _, m = load("ref_layer_n1")
+    assert [st for st, _ in m["dropout_streams_rank0"]] == ["local_seed", "global_seed", "global_seed"]
+    layer = TransformerDecoderLayer(128, 2, 512, dropout=0.1, device="cpu")
+    set_seed(1024, mp_rank=3)
+    layer.train()
+    m1, m2 = layer._meta(), layer._meta()
+    assert (m1.rng_attn, m1.rng_h1, m1.rng_h2) == ((1024 + 123 + 30, 0), (1024, 0), (1024, 1))
+    assert (m2.rng_attn, m2.rng_h1, m2.rng_h2) == ((1024 + 123 + 30, 1), (1024, 2), (1024, 3))
+    layer.eval()
+    before = get_rng_state_tracker().get_states_tracker()
+    e = layer._meta()
+    assert (e.p_attn, e.p_hidden1, e.p_hidden2) == (0.0, 0.0, 0.0)
+    assert get_rng_state_tracker().get_states_tracker() == before
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        layer(torch.zeros(1, 8, 128, dtype=torch.bfloat16))
