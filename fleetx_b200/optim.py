@@ -4,8 +4,11 @@ tensor / chunk tables; the clip factor never visits the host.
 
 Same knobs as the reference: learning_rate, parameters, grad_clip (a clip norm or None), weight_decay, beta1,
 beta2, epsilon, multi_precision (fp32 master weights for bf16 parameters, AMP-O2). Parameters whose name
-contains "bias" or "norm" do not decay (optimizer.py:40-44). `tensor_fusion` is accepted and irrelevant here:
-the update is already one launch for all tensors.
+contains "bias" or "norm" do not decay (optimizer.py:40-44). The reference tests `p.name`, which under Paddle is
+the parameter's framework-assigned unique name, not its state-dict key (upstream behaviour, not checkable here);
+this class tests whatever names it is given — `for_model` passes the state-dict keys ("linear1.bias",
+"norm1.weight", ...), a caller that wants other names passes `named_parameters` itself. `tensor_fusion` is
+accepted and irrelevant here: the update is already one launch for all tensors.
 """
 from __future__ import annotations
 

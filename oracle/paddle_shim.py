@@ -600,6 +600,26 @@ class PipelineLayer(Layer):
     """Placeholder base class: pipeline parallelism is outside the path (SURVEY §2 #6)."""
 
 
+class LRScheduler:
+    """[U] paddle.optimizer.lr.LRScheduler: the constructor stores last_epoch and takes one step(); step()
+    advances last_epoch by one (or sets it) and caches get_lr()."""
+
+    def __init__(self, learning_rate=0.1, last_epoch=-1, verbose=False):
+        self.base_lr = self.last_lr = float(learning_rate)
+        self.last_epoch, self.verbose = last_epoch, verbose
+        self.step()
+
+    def __call__(self):
+        return self.last_lr
+
+    def step(self, epoch=None):
+        self.last_epoch = self.last_epoch + 1 if epoch is None else epoch
+        self.last_lr = self.get_lr()
+
+    def get_lr(self):
+        raise NotImplementedError
+
+
 def _recompute(function, *args, **kwargs):
     """[U] fleet.utils.recompute: same values and gradients as calling the function (it only trades memory)."""
     return function(*args, **kwargs)
@@ -741,6 +761,8 @@ def install(default_dtype="float64") -> None:
     _module("paddle.incubate.nn", FusedLinear=Linear)
     _module("paddle.incubate.nn.functional", fused_linear=_linear)
     _module("paddle.common_ops_import", convert_dtype=lambda d: str(d).replace("torch.", ""))
+    _module("paddle.optimizer")
+    _module("paddle.optimizer.lr", LRScheduler=LRScheduler)
     _module("paddle.distributed", get_world_size=world_size, get_rank=current_rank)
     _module("paddle.distributed.collective", _c_identity=lambda x, group=None: _CIdentity.apply(x) if world_size() > 1 else x,
             _c_concat=lambda x, group=None: _CConcat.apply(x),
@@ -763,8 +785,9 @@ def install(default_dtype="float64") -> None:
             pkg, path = pkg + "." + part, os.path.join(path, part)
         m = _module(pkg)
         m.__path__ = [path]
-    u = _module("ppfleetx.utils")
-    u.__path__ = [os.path.join(REFERENCE_ROOT, "ppfleetx", "utils")]
+    for sub in ("utils", "optims"):
+        u = _module("ppfleetx." + sub)
+        u.__path__ = [os.path.join(REFERENCE_ROOT, "ppfleetx", sub)]
     _installed = True
 
 
@@ -775,10 +798,12 @@ def reference_available() -> bool:
 
 def load_reference(name: str = "hybrid_model"):
     """Import one of the reference's files for the path (hybrid_model, single_model, sequence_parallel_utils)
-    straight from REFERENCE_ROOT; `env` gives ppfleetx/utils/env.py."""
+    straight from REFERENCE_ROOT; `env` gives ppfleetx/utils/env.py, `lr_scheduler` ppfleetx/optims/lr_scheduler.py."""
     install(str(_state["default_dtype"]).replace("torch.", ""))
     if name == "env":
         return importlib.import_module("ppfleetx.utils.env")
+    if name == "lr_scheduler":
+        return importlib.import_module("ppfleetx.optims.lr_scheduler")
     return importlib.import_module("ppfleetx.models.language_model.gpt.dygraph." + name)
 
 

@@ -139,6 +139,16 @@ def test_rng_seeds_match_env_py_executed():
         assert [st["global_seed"][0], st["local_seed"][0]] == d["seeds"][r].tolist()
 
 
+def test_lr_schedule_matches_lr_scheduler_py_executed():
+    d, m = load("ref_lr_schedule")
+    from fleetx_b200.optim import CosineAnnealingWithWarmupDecay
+
+    sch = CosineAnnealingWithWarmupDecay(m["max_lr"], m["min_lr"], m["warmup_rate"], m["decay_steps"])
+    for k, want in zip(d["steps"].tolist(), d["lr"].tolist()):
+        sch.step(k)
+        assert sch.get_lr() == want, (k, sch.get_lr(), want)
+
+
 # ------------------------------------------------------------------------------------ live (build container only)
 @pytest.mark.skipif(not HAVE_REFERENCE, reason="the reference tree is not on this machine")
 def test_committed_fixtures_are_what_the_reference_produces_now():

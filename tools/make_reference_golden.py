@@ -302,6 +302,21 @@ def seeds_case(name, check):
           "source": "ppfleetx/utils/env.py set_seed via oracle/paddle_shim.py"}, check)
 
 
+def lr_case(name, check):
+    """ppfleetx/optims/lr_scheduler.py CosineAnnealingWithWarmupDecay.get_lr at pretrain_gpt_base.yaml:75-80
+    (max 5e-5, min 1e-5, warm-up 1 % of 360000 decay steps), evaluated at chosen values of last_epoch."""
+    lr = S.load_reference("lr_scheduler")
+    sch = lr.CosineAnnealingWithWarmupDecay(5e-5, 1e-5, 0.01, 360000)
+    steps = [0, 1, 1800, 3599, 3600, 3601, 100000, 181800, 359999, 360000, 360001, 500000]
+    vals = []
+    for k in steps:
+        sch.last_epoch = k
+        vals.append(sch.get_lr())
+    save(name, {"steps": np.array(steps, dtype=np.int64), "lr": np.array(vals, dtype=np.float64)},
+         {"kind": "lr", "max_lr": 5e-5, "min_lr": 1e-5, "warmup_rate": 0.01, "decay_steps": 360000,
+          "source": "ppfleetx/optims/lr_scheduler.py via oracle/paddle_shim.py"}, check)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--check", action="store_true")
@@ -323,6 +338,7 @@ def main():
     model_case("ref_model_sp2", c, n=2, sp=True)
     cache_case("ref_model_eval_cache", c)
     seeds_case("ref_env_seeds", c)
+    lr_case("ref_lr_schedule", c)
 
 
 if __name__ == "__main__":
