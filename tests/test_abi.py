@@ -67,3 +67,28 @@ def test_product_code_never_imports_the_oracle():
             if f.endswith(".py") and f != "selfcheck.py":  # selfcheck.smoke() is the allowed checker
                 src = open(os.path.join(dirpath, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle", src, flags=re.M), f
+
+
+@pytest.mark.parametrize("fill", [0, 8])
+def test_every_compute_entry_point_rejects_null_and_empty_arguments(fill):
+    """All pointers NULL, every integer `fill`: each entry point must return a negative code with a message (and
+    never touch the pointers); the size helpers return a number. No CUDA call is reached."""
+    lib = _lib.lib()
+    helpers = {"fx_last_error", "fx_version", "fx_launch_count"}
+    for name, (res, args) in sorted(_lib.SIGNATURES.items()):
+        if name in helpers:
+            continue
+        vals = []
+        for a in args:
+            if a in (C.c_void_p, C.c_char_p) or (hasattr(a, "_type_") and not isinstance(a._type_, str)):
+                vals.append(None)
+            elif a in (C.c_float, C.c_double):
+                vals.append(0.0)
+            else:
+                vals.append(fill)
+        rc = getattr(lib, name)(*vals)
+        if name.endswith("_bytes"):
+            assert rc >= 0, name
+        else:
+            assert rc in (-1, -3), (name, rc)
+            assert name.encode() in lib.fx_last_error(), (name, lib.fx_last_error())
