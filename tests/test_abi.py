@@ -92,3 +92,36 @@ def test_every_compute_entry_point_rejects_null_and_empty_arguments(fill):
         else:
             assert rc in (-1, -3), (name, rc)
             assert name.encode() in lib.fx_last_error(), (name, lib.fx_last_error())
+
+
+def test_whole_layer_buffer_plans_on_the_host():
+    """fx_decoder_layer_saved_bytes / _workspace_bytes are pure host arithmetic: the activation memory the native
+    entry points ask the caller for, at the bench shape (GPT-1.3B layer, b 8, s 2048) and its 8-way shard."""
+    lib = _lib.lib()
+    up = lambda n: (n + 255) // 256 * 256  # noqa: E731
+
+    def desc(b, s, h, nh_local, hd, f_local, p_attn, pre=1):
+        d = _lib.LayerDesc()
+        d.b, d.s, d.h, d.nh_local, d.hd, d.f_local, d.normalize_before, d.p_attn = b, s, h, nh_local, hd, f_local, pre, p_attn
+        for name, typ in _lib.LayerDesc._fields_:  # the plans need a complete descriptor; nothing is dereferenced
+            if name.endswith(("_w", "_b")):
+                setattr(d, name, C.cast(0x1000, typ))
+        return d
+
+    for n in (1, 8):
+        b, s, h, nhl, hd, fl = 8, 2048, 2048, 32 // n, 64, 8192 // n
+        T, hl = b * s, nhl * hd
+        d = desc(b, s, h, nhl, hd, fl, 0.1)
+        mask = lib.fx_attn_dropout_mask_bytes(b, s, nhl)
+        want = (3 * up(T * h * 2) + 4 * up(T * 4) + up(T * 3 * hl * 2) + up(T * hl * 2) + up(b * nhl * s * 4) + up(mask)
+                + 2 * up(T * fl * 2))  # ln1, x1, ln2 | 4 statistics rows | qkv | ctx | lse | keep bits | z, act
+        assert lib.fx_decoder_layer_saved_bytes(C.byref(d)) == want
+        d0 = desc(b, s, h, nhl, hd, fl, 0.0)
+        assert lib.fx_decoder_layer_saved_bytes(C.byref(d0)) == want - up(mask)  # no keep bits without dropout
+        ws = lib.fx_decoder_layer_workspace_bytes(C.byref(d))
+        assert ws >= 5 * up(T * h * 2) + up(T * fl * 2) + up(T * hl * 2) + up(T * 3 * hl * 2) and ws % 256 == 0
+    post = desc(8, 2048, 2048, 32, 64, 8192, 0.0, pre=0)  # post-LN keeps r1, r2 and a third pair of statistics
+    pre = desc(8, 2048, 2048, 32, 64, 8192, 0.0, pre=1)
+    assert lib.fx_decoder_layer_saved_bytes(C.byref(post)) == lib.fx_decoder_layer_saved_bytes(C.byref(pre))
+    bad = desc(8, 2048, 2048, 32, 96, 8192, 0.0)
+    assert lib.fx_decoder_layer_saved_bytes(C.byref(bad)) == 0 and b"head_dim" in lib.fx_last_error()
