@@ -260,3 +260,43 @@ def test_host_mirror_has_the_reference_signatures_and_parameter_names():
     ref_shapes = {k: tuple(v.shape) for k, v in ref_model.named_parameters()}
     my_shapes = {k: tuple(v.shape) for k, v in my_model.named_parameters()}
     assert ref_shapes == my_shapes
+
+
+@pytest.mark.skipif(not HAVE_REFERENCE, reason="the reference tree is not on this machine")
+def test_baseline_config_0_through_the_reference_layer():
+    """BASELINE.json configs[0]: GPT-345M decoder layer (h 1024, 16 heads, ffn 4096), seq 1024, micro-batch 1, fp32,
+    forward + backward, dropout 0.1 with the library's Philox masks: the reference's layer (executed over the
+    stand-in, torch-CPU fp32) and the oracle agree to fp32 rounding."""
+    from oracle import paddle_shim as S
+
+    b, s, h, nh, f, seed = 1, 1024, 1024, 16, 4096, 1024
+    cfg = O.LayerConfig(d_model=h, nhead=nh, dim_feedforward=f, dropout=0.1)
+    params = O.init_params(cfg, seed, dtype=torch.float32)
+    g = torch.Generator().manual_seed(seed + 1)
+    x = torch.randn(b, s, h, generator=g)
+    dy = torch.randn(b, s, h, generator=g)
+    masks = O.make_masks(cfg, b, s, seed)
+    y_o, dx_o, g_o = O.decoder_layer_fwd_bwd(x, dy, params, cfg, masks)
+
+    S.install("float32")
+    try:
+        hm = S.load_reference("hybrid_model")
+        order = iter([masks.attn[0], masks.hidden1, masks.hidden2])
+        S.set_dropout_provider(lambda stream, rank, shape, p: next(order))
+
+        def rank_fn(r):
+            layer = hm.TransformerDecoderLayer(h, nh, f, dropout=0.1)
+            layer.train()
+            layer.set_state_dict(params)
+            xt = S._to_tensor(x, stop_gradient=False)
+            y = layer(xt)
+            y.backward(dy)
+            return y.detach(), xt.grad, {k: q.grad for k, q in layer.named_parameters()}
+
+        y, dx, grads = S.run_ranks(1, rank_fn)[0]
+    finally:
+        S.install("float64")
+    rel = lambda a, b_: ((a.double() - b_.double()).abs().max() / b_.double().abs().max()).item()  # noqa: E731
+    assert rel(y, y_o) < 1e-5 and rel(dx, dx_o) < 1e-4
+    for k in O.PARAM_NAMES:
+        assert rel(grads[k], g_o[k]) < 1e-4, k
