@@ -15,7 +15,8 @@ tools/make_reference_golden.py executes hybrid_model.py / sequence_parallel_util
 torch-backed `paddle` stand-in of oracle/paddle_shim.py (mp 1 / 2 / 4, sequence parallel 2 / 4) and
 tests/test_reference_golden.py holds this restatement to those outputs and gradients (1e-10, fp64). The
 same math is stated three times in-tree (hybrid_model.py, single_model.py:98-116,189-213,397-427,
-auto_model.py:181-206,382-420); the first two are executed and agree bit for bit.
+auto_model.py:181-206,382-420); all three are executed there and agree (the auto-parallel one after cutting
+the fused qkv_proj into its separate q / k / v projections).
 
 Written in torch-CPU (fp32 / fp64): non-fused, one function per reference op, tensor
 parallelism simulated explicitly (n shards in one process, allreduce = Python sum). Gradients

@@ -764,6 +764,7 @@ def install(default_dtype="float64") -> None:
     _module("paddle.optimizer")
     _module("paddle.optimizer.lr", LRScheduler=LRScheduler)
     _module("paddle.distributed", get_world_size=world_size, get_rank=current_rank)
+    _module("paddle.distributed.auto_parallel", shard_tensor=lambda x, *a, **k: x, shard_op=lambda f, *a, **k: f)
     _module("paddle.distributed.collective", _c_identity=lambda x, group=None: _CIdentity.apply(x) if world_size() > 1 else x,
             _c_concat=lambda x, group=None: _CConcat.apply(x),
             _mp_allreduce=lambda x, group=None, **kw: _MpAllreduce.apply(x))
@@ -785,6 +786,8 @@ def install(default_dtype="float64") -> None:
             pkg, path = pkg + "." + part, os.path.join(path, part)
         m = _module(pkg)
         m.__path__ = [path]
+    a = _module("ppfleetx.models.language_model.gpt.auto")
+    a.__path__ = [os.path.join(REFERENCE_ROOT, "ppfleetx", "models", "language_model", "gpt", "auto")]
     for sub in ("utils", "optims"):
         u = _module("ppfleetx." + sub)
         u.__path__ = [os.path.join(REFERENCE_ROOT, "ppfleetx", sub)]
@@ -802,6 +805,8 @@ def load_reference(name: str = "hybrid_model"):
     install(str(_state["default_dtype"]).replace("torch.", ""))
     if name == "env":
         return importlib.import_module("ppfleetx.utils.env")
+    if name == "auto_model":
+        return importlib.import_module("ppfleetx.models.language_model.gpt.auto.auto_model")
     if name == "lr_scheduler":
         return importlib.import_module("ppfleetx.optims.lr_scheduler")
     return importlib.import_module("ppfleetx.models.language_model.gpt.dygraph." + name)

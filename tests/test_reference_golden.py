@@ -300,3 +300,53 @@ def test_baseline_config_0_through_the_reference_layer():
     assert rel(y, y_o) < 1e-5 and rel(dx, dx_o) < 1e-4
     for k in O.PARAM_NAMES:
         assert rel(grads[k], g_o[k]) < 1e-4, k
+
+
+@pytest.mark.skipif(not HAVE_REFERENCE, reason="the reference tree is not on this machine")
+def test_auto_parallel_statement_of_the_layer_agrees_after_unfusing_qkv():
+    """auto_model.py:327-420 is the third in-tree statement of the layer, with SEPARATE q / k / v projections. Cut
+    the fused qkv_proj of the hybrid fixture into them — columns of head i are [q_i | k_i | v_i], hybrid_model.py:
+    167-173 — and it reproduces the hybrid layer's outputs and gradients: the packed layout the CUDA attention
+    kernels read (fx_attn_causal_fwd: [b, s, nh, 3, hd]) is the reference's."""
+    from oracle import paddle_shim as S
+
+    d, m = load("ref_layer_n1")
+    h, nh, f = m["h"], m["nh"], m["f"]
+    hd = h // nh
+    S.install("float64")
+    am = S.load_reference("auto_model")
+
+    class Mesh:  # auto-parallel annotations are no-ops here
+        mp = dp = None
+
+        def __getitem__(self, i):
+            return None
+
+    w = d["param.self_attn.qkv_proj.weight"].reshape(h, nh, 3, hd)
+    bq = d["param.self_attn.qkv_proj.bias"].reshape(nh, 3, hd)
+    sd = {k: d["param." + k] for k in O.PARAM_NAMES if "qkv_proj" not in k}
+    for j, name in enumerate(("q_proj", "k_proj", "v_proj")):
+        sd[f"self_attn.{name}.weight"] = w[:, :, j, :].reshape(h, h).contiguous()
+        sd[f"self_attn.{name}.bias"] = bq[:, j, :].reshape(h).contiguous()
+    order = iter([d["mask.attn.0"], d["mask.hidden1"], d["mask.hidden2"]])
+    S.set_dropout_provider(lambda stream, rank, shape, p: next(order))
+
+    def rank_fn(r):
+        layer = am.TransformerDecoderLayer(h, nh, f, dropout=m["dropout"], mesh=Mesh(), mesh_idx=0)
+        layer.train()
+        layer.set_state_dict(sd)
+        x = S._to_tensor(d["in.x"], stop_gradient=False)
+        y = layer(x, None)
+        y.backward(d["in.dy"])
+        return y.detach(), x.grad, {k: q.grad for k, q in layer.named_parameters()}
+
+    y, dx, grads = S.run_ranks(1, rank_fn)[0]
+    close(y, d["out.y"], "y")
+    close(dx, d["out.dx"], "dx")
+    for k in O.PARAM_NAMES:
+        if "qkv_proj" not in k:
+            close(grads[k], d["grad." + k], "grad " + k)
+    gw = torch.stack([grads[f"self_attn.{n}.weight"].reshape(h, nh, hd) for n in ("q_proj", "k_proj", "v_proj")], dim=2)
+    gb = torch.stack([grads[f"self_attn.{n}.bias"].reshape(nh, hd) for n in ("q_proj", "k_proj", "v_proj")], dim=1)
+    close(gw.reshape(h, 3 * h), d["grad.self_attn.qkv_proj.weight"], "grad qkv weight (re-fused)")
+    close(gb.reshape(3 * h), d["grad.self_attn.qkv_proj.bias"], "grad qkv bias (re-fused)")
