@@ -26,6 +26,8 @@
 #include <stdlib.h>
 #include <type_traits>
 
+#include <atomic>
+
 #include "common.cuh"
 #include "philox.cuh"
 #include "tc5.cuh"
@@ -438,7 +440,7 @@ static int make_qkv_map(CUtensorMap* map, const void* qkv, int b, int s, int nh,
 template <int HD>
 static int launch_fwd(cudaStream_t st, const CUtensorMap& map, const FwdParams& p) {
   using C = FwdCfg<HD>;
-  static bool attr_set[64] = {false};
+  static std::atomic<bool> attr_set[64];  // idempotent set-up: an atomic flag per device is enough
   int dev = 0;
   FX_CUDA(cudaGetDevice(&dev));
   if (dev < 64 && !attr_set[dev]) {
@@ -1074,17 +1076,13 @@ static int make_out_map_rows(CUtensorMap* map, const void* out, int b, int s, in
 
 // head_dim 64 runs the single-kernel backward unless FX_ATTN_BWD=split asks for the deterministic pair
 static bool use_fused_bwd(int hd) {
-  static const bool split = [] {
-    const char* e = getenv("FX_ATTN_BWD");
-    return e && e[0] == 's';
-  }();
-  return hd == 64 && !split;
+  return hd == 64 && !knobs().attn_bwd_split;
 }
 
 template <int HD>
 static int launch_bwd(cudaStream_t st, const void* dout, const void* qkv, const void* out, const float* lse,
                       const BwdParams& p, float* lse2, float* delta, float* dq_acc) {
-  static bool attr_set[64] = {false};
+  static std::atomic<bool> attr_set[64];  // idempotent set-up: an atomic flag per device is enough
   int dev = 0;
   FX_CUDA(cudaGetDevice(&dev));
   if (dev < 64 && !attr_set[dev]) {

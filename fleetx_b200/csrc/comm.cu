@@ -442,7 +442,9 @@ extern "C" int fx_tp_allreduce_bdr(void* stream, const uint64_t* peer_bufs, cons
   q.mask_in = mask_in;
   // two ranks: one-shot peer loads beat a trip through the switch; otherwise reduce + multicast in the switch
   q.variant = (world == 2 && out != nullptr) ? 2 : 0;
-  if (const char* e = getenv("FX_COMM_VARIANT")) q.variant = atoi(e);  // tuning knob
+  // tuning / test knob (read once, runtime.cu): force a variant wherever the call admits it
+  const int kv = knobs().comm_variant;
+  if (kv == 0 || (kv == 1 && out != nullptr) || (kv == 2 && out != nullptr && world == 2)) q.variant = kv;
   FX_CHECK_ARG(out != nullptr || q.variant == 0, "fx_tp_allreduce_bdr: in-place result needs the multicast variant");
   FX_CHECK_ARG(q.variant != 2 || world == 2, "fx_tp_allreduce_bdr: the one-shot variant is for 2 ranks");
   comm::tp_allreduce_kernel<<<num_blocks, comm::THREADS, 0, static_cast<cudaStream_t>(stream)>>>(q);

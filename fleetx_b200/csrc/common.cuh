@@ -47,6 +47,16 @@ void set_error(const char* fmt, ...);
 void count_launch();
 int num_sms();
 
+// FX_* environment tuning knobs, read ONCE (thread-safe) the first time any entry point asks; later changes of
+// the environment are ignored, and no launch path calls getenv.
+struct Knobs {
+  int gemm_bn;         // FX_GEMM_BN: 128 / 256 forces the N tile; 0 = heuristic
+  int gemm_group;      // FX_GEMM_GROUP: M-tiles per raster group; 0 = default
+  int comm_variant;    // FX_COMM_VARIANT: 0 / 1 / 2 forces a tp_allreduce_kernel variant where it applies; -1 = default
+  bool attn_bwd_split; // FX_ATTN_BWD=split: the deterministic two-kernel attention backward at head_dim 64
+};
+const Knobs& knobs();
+
 // Encode a bf16 tensor map with 128-byte swizzle. dims/strides innermost first; strides in
 // bytes for dims 1.. (dim 0 is contiguous). Returns 0 or FX_ERR_*.
 int make_tma_bf16(CUtensorMap* map, const void* base, int rank, const uint64_t* dims,

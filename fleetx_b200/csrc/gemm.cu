@@ -15,6 +15,8 @@
 // descriptors carry the difference, so no transposed copies are ever made.
 #include <stdlib.h>
 
+#include <atomic>
+
 #include "common.cuh"
 #include "tc5.cuh"
 
@@ -310,7 +312,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
 template <int BN>
 static int launch(cudaStream_t stream, const CUtensorMap& ta, const CUtensorMap& tb, Params& p) {
   using C = Cfg<BN>;
-  static bool attr_set[64] = {false};
+  static std::atomic<bool> attr_set[64];  // idempotent set-up: an atomic flag per device is enough
   int dev = 0;
   FX_CUDA(cudaGetDevice(&dev));
   if (dev < 64 && !attr_set[dev]) {
@@ -364,8 +366,8 @@ extern "C" int fx_gemm_bf16(void* stream, int trans_a, int trans_b, int M, int N
   };
   int BN = (N > 128 && cost(256) <= cost(128)) ? 256 : 128;
   p.group = 8;
-  if (const char* e = getenv("FX_GEMM_BN")) BN = atoi(e) == 128 ? 128 : 256;      // tuning knobs
-  if (const char* e = getenv("FX_GEMM_GROUP")) p.group = atoi(e) > 0 ? atoi(e) : 8;
+  if (knobs().gemm_bn) BN = knobs().gemm_bn;            // tuning knobs (read once, runtime.cu)
+  if (knobs().gemm_group) p.group = knobs().gemm_group;
 
   CUtensorMap ta, tb;
   int rc;

@@ -1,6 +1,8 @@
 // runtime.cu — process-wide bits of libfleetx_b200.so: error text, launch counter, device
 // properties and the cuTensorMapEncodeTiled entry point (fetched from the driver at run time so
 // the library links against nothing but the CUDA runtime).
+#include <stdlib.h>
+
 #include <atomic>
 #include <mutex>
 
@@ -21,16 +23,29 @@ void set_error(const char* fmt, ...) {
 void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
 int num_sms() {
-  static int cached[64] = {0};
+  static std::atomic<int> cached[64];
   int dev = 0;
   if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
-  if (cached[dev] == 0) {
-    int n = 0;
+  int n = cached[dev].load(std::memory_order_relaxed);
+  if (n == 0) {
     if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
       n = 148;
-    cached[dev] = n;
+    cached[dev].store(n, std::memory_order_relaxed);
   }
-  return cached[dev];
+  return n;
+}
+
+const Knobs& knobs() {
+  static Knobs k;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    k.gemm_bn = 0; k.gemm_group = 0; k.comm_variant = -1; k.attn_bwd_split = false;
+    if (const char* e = getenv("FX_GEMM_BN")) k.gemm_bn = atoi(e) == 128 ? 128 : 256;
+    if (const char* e = getenv("FX_GEMM_GROUP")) k.gemm_group = atoi(e) > 0 ? atoi(e) : 0;
+    if (const char* e = getenv("FX_COMM_VARIANT")) k.comm_variant = atoi(e);
+    if (const char* e = getenv("FX_ATTN_BWD")) k.attn_bwd_split = e[0] == 's';
+  });
+  return k;
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,

@@ -117,6 +117,10 @@ class LayerConfig:
     act_dropout: Optional[float] = None
     normalize_before: bool = True
     num_partitions: int = 1
+    # None: d_model // nhead, as in the reference (:113). An explicit value states ONE mp rank's shard of a larger
+    # layer as a layer of its own (nhead = that rank's heads, dim_feedforward = its FFN columns, weights
+    # [h, 3*nhead*hd] / [nhead*hd, h]): what the full-size tests compare a rank's kernels against.
+    head_dim: Optional[int] = None
 
     def __post_init__(self):
         # hybrid_model.py:469-470
@@ -124,13 +128,13 @@ class LayerConfig:
             self.attn_dropout = self.dropout
         if self.act_dropout is None:
             self.act_dropout = self.dropout
-        assert self.d_model % self.nhead == 0  # :114-115
+        assert self.head_dim is not None or self.d_model % self.nhead == 0  # :114-115
         assert self.nhead % self.num_partitions == 0  # :117-118
         assert self.dim_feedforward % self.num_partitions == 0
 
     @property
     def hd(self) -> int:
-        return self.d_model // self.nhead
+        return self.head_dim if self.head_dim is not None else self.d_model // self.nhead
 
 
 PARAM_NAMES = (

@@ -126,3 +126,37 @@ def test_fullsize_dropout_statistics_and_replay():
     p_eff = round(0.1 * 32768) / 32768  # the threshold is quantised to 15 bits
     sigma = (p_eff * (1 - p_eff) / n) ** 0.5
     assert abs(keep - (1 - p_eff)) < 4 * sigma
+
+
+# One sequence per shape, forward AND backward, dropout 0.1 on all three streams, every tensor against the oracle
+# with the generator's masks restated in numpy (oracle/philox.py). A rank shard of C4 / C5 is stated to the oracle
+# as a layer of its own (LayerConfig.head_dim): same arithmetic as rank 0 of the mp-8 layer before the allreduce.
+@pytest.mark.parametrize("name,b,s,h,nhl,hd,fl", SHAPES)
+def test_fullsize_fwd_bwd_with_dropout_against_the_oracle(name, b, s, h, nhl, hd, fl):
+    from fleetx_b200 import functional as Fn
+    from fleetx_b200.dist import SingleGroup
+
+    p = 0.1
+    P, M = _params(h, nhl, hd, fl), _meta(nhl, hd, p)
+    g = torch.Generator().manual_seed(11)
+    x = torch.randn(1, s, h, generator=g).to(torch.bfloat16)
+    dy = torch.randn(1, s, h, generator=g).to(torch.bfloat16)
+    y, saved = Fn.decoder_layer_fwd(x.cuda(), P, M, SingleGroup())
+    dx, grads = Fn.decoder_layer_bwd(dy.cuda(), saved, P, M, SingleGroup())
+    torch.cuda.synchronize()
+
+    from oracle import philox
+
+    cfg = O.LayerConfig(d_model=h, nhead=nhl, dim_feedforward=fl, dropout=p, head_dim=hd)
+    names = dict(zip(("norm1_w", "norm1_b", "qkv_w", "qkv_b", "out_w", "out_b", "norm2_w", "norm2_b", "lin1_w",
+                      "lin1_b", "lin2_w", "lin2_b"), O.PARAM_NAMES))
+    params = {names[k]: getattr(P, k).float().cpu() for k in names}
+    masks = O.DropoutMasks(
+        attn=[torch.from_numpy(philox.attn_dropout_mask(M.rng_attn[0], M.rng_attn[1], 1, nhl, s, p))],
+        hidden1=torch.from_numpy(philox.dropout_mask(M.rng_h1[0], M.rng_h1[1], s * h, p)).reshape(1, s, h),
+        hidden2=torch.from_numpy(philox.dropout_mask(M.rng_h2[0], M.rng_h2[1], s * h, p)).reshape(1, s, h))
+    y_ref, dx_ref, g_ref = O.decoder_layer_fwd_bwd(x.float(), dy.float(), params, cfg, masks)
+    errs = {"y": rel_err(y, y_ref), "dx": rel_err(dx, dx_ref)}
+    for k, full in names.items():
+        errs[k] = rel_err(grads[k], g_ref[full])
+    assert max(errs.values()) < 2e-2, errs  # north_star: <= 2e-2 relative per tensor for bf16

@@ -27,7 +27,7 @@ def _setup(cfg, b, s, seed=1024):
 
 def _run(cfg, params, x, dy, seed, train=True, inject=None):
     from fleetx_b200.rng import set_seed
-    from fleetx_b200.selfcheck import layer_from_oracle_params
+    from selfcheck import layer_from_oracle_params
 
     set_seed(seed)
     layer = layer_from_oracle_params(cfg, params)
@@ -90,7 +90,7 @@ def test_layer_with_injected_masks():
 
 def test_layer_eval_mode_and_recompute_determinism():
     from fleetx_b200.rng import get_rng_state_tracker, set_seed
-    from fleetx_b200.selfcheck import layer_from_oracle_params
+    from selfcheck import layer_from_oracle_params
 
     b, s, h, nh, f = 2, 128, 256, 4, 1024
     cfg = O.LayerConfig(d_model=h, nhead=nh, dim_feedforward=f, dropout=0.1)
@@ -164,7 +164,7 @@ def test_layer_recompute_matches_plain(granularity, hd128):
     single-kernel attention backward adds dQ partials in no fixed order), and fewer bytes stay pinned."""
     from fleetx_b200 import functional as Fn
     from fleetx_b200.rng import set_seed
-    from fleetx_b200.selfcheck import layer_from_oracle_params
+    from selfcheck import layer_from_oracle_params
 
     b, s, h, f = 2, 256, 256, 1024
     nh = 2 if hd128 else 4
@@ -196,7 +196,7 @@ def test_layer_recompute_matches_plain(granularity, hd128):
 
 
 def test_layer_recompute_rejects_unknown_granularity():
-    from fleetx_b200.selfcheck import layer_from_oracle_params
+    from selfcheck import layer_from_oracle_params
 
     cfg = O.LayerConfig(d_model=128, nhead=2, dim_feedforward=512, dropout=0.0)
     params, x, _ = _setup(cfg, 1, 8)

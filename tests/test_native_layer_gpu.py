@@ -15,7 +15,7 @@ TOL = 2e-2
 def _make(cfg, b, s, p_drop, normalize_before):
     from fleetx_b200 import functional as Fn
     from fleetx_b200.dist import SingleGroup
-    from fleetx_b200.selfcheck import layer_from_oracle_params
+    from selfcheck import layer_from_oracle_params
     from test_layer_gpu import _setup
 
     params, x, dy = _setup(cfg, b, s)

@@ -1,5 +1,5 @@
-"""Tensor-parallel layer on 2 GPUs (NCCL) against the oracle's n=2 simulation. Needs 2 devices;
-skipped on a single-GPU box (the CPU/gloo version of the same logic is tests/test_dist_gloo.py)."""
+"""Tensor-parallel layer on 2 / 4 / 8 GPUs against the oracle's simulation of the same mp degree. Needs that many
+devices; skipped on a smaller box (the CPU/gloo version of the same logic is tests/test_dist_gloo.py)."""
 import os
 import socket
 
@@ -22,33 +22,30 @@ def _free_port():
 def _worker(rank, world, port, ret, kind):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
+    if kind.startswith("symmetric_v"):  # force one variant of tp_allreduce_kernel (read once, when the library loads)
+        os.environ["FX_COMM_VARIANT"] = kind[-1]
     torch.cuda.set_device(rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     try:
         from fleetx_b200.dist import SymmetricTPGroup, TorchDistGroup
         from fleetx_b200.rng import set_seed
-        from fleetx_b200.selfcheck import layer_from_oracle_params, rel_err
+        from selfcheck import layer_from_oracle_params, layer_parity, rel_err
 
         b, s = 2, 256
-        cfg = O.LayerConfig(d_model=512, nhead=8, dim_feedforward=2048, dropout=0.1, num_partitions=world)
-        params = {k: v.to(torch.bfloat16).float() for k, v in O.init_params(cfg, 1024).items()}
-        g = torch.Generator().manual_seed(3)
-        x = torch.randn(b, s, cfg.d_model, generator=g).to(torch.bfloat16)
-        dy = torch.randn(b, s, cfg.d_model, generator=g).to(torch.bfloat16)
-        set_seed(1024, mp_rank=rank)
-        group = TorchDistGroup() if kind in ("nccl", "sp_nccl", "model", "model_sp") else SymmetricTPGroup(max_elems=b * s * cfg.d_model, num_blocks=32)
-        layer = layer_from_oracle_params(cfg, params, group=group, device=f"cuda:{rank}")
-        layer.train()
+        h, nh, ffn = 512, 8, 2048
+        group = (TorchDistGroup() if kind in ("nccl", "sp_nccl", "model", "model_sp")
+                 else SymmetricTPGroup(max_elems=b * s * h, num_blocks=32))
         worst = 0.0
         if kind in ("model", "model_sp"):
-            # GPTForPretrainingHybrid over 2 mp ranks: vocab-parallel embedding, tensor-parallel layers, split
+            # GPTForPretrainingHybrid over the mp ranks: vocab-parallel embedding, tensor-parallel layers, split
             # logits and ParallelCrossEntropy, against the single-process model oracle
             from fleetx_b200.model import (GPTForPretrainingHybrid, GPTModelHybrid, GPTPretrainingCriterionHybird,
                                            load_full_state)
             from oracle import gpt_model as G
 
-            mc = G.ModelConfig(vocab_size=1024, hidden_size=256, num_layers=2, num_attention_heads=4, ffn_hidden_size=1024,
-                               max_position_embeddings=128, num_partitions=world)
+            heads = max(4, world)
+            mc = G.ModelConfig(vocab_size=1024, hidden_size=64 * heads, num_layers=2, num_attention_heads=heads,
+                               ffn_hidden_size=256 * heads, max_position_embeddings=128, num_partitions=world)
             full = {k: v.to(torch.bfloat16).float() for k, v in G.init_params(mc, 1024).items()}
             gg = torch.Generator().manual_seed(5)
             ids = torch.randint(0, mc.vocab_size, (2, 64), generator=gg)
@@ -82,49 +79,24 @@ def _worker(rank, world, port, ret, kind):
                 worst = max(worst, rel_err(p.grad, ref))
             ret[rank] = worst
             return
-        if kind in ("sp", "sp_nccl"):
-            # sequence_parallel=True: this rank feeds / returns its [s/n, b, h] shard; the oracle is the plain
-            # layer with the shard-sized hidden masks repeated over the ranks (oracle.make_masks_sp)
-            layer.sequence_parallel = True
-            masks = O.make_masks_sp(cfg, b, s, 1024)
-            y_ref, dx_ref, g_ref = O.decoder_layer_fwd_bwd(x.float(), dy.float(), params, cfg, masks)
-            g_shard = O.shard_params(g_ref, cfg, rank)
-            for it in range(2):
-                set_seed(1024, mp_rank=rank)
-                for p_ in layer.parameters():
-                    p_.grad = None
-                xs = O.sp_scatter(x, world, rank).cuda().requires_grad_(True)
-                ys = layer(xs)
-                ys.backward(O.sp_scatter(dy, world, rank).cuda())
-                torch.cuda.synchronize()
-                errs = {"y": rel_err(ys, O.sp_scatter(y_ref, world, rank)),
-                        "dx": rel_err(xs.grad, O.sp_scatter(dx_ref, world, rank))}
-                for n, p in layer.named_parameters():
-                    errs[n] = rel_err(p.grad, g_shard[n])
-                worst = max(worst, max(errs.values()))
-            ret[rank] = worst
-            return
-        for it in range(2):  # twice: the second call reuses the symmetric buffer and the epoch flags
-            set_seed(1024, mp_rank=rank)
-            for p_ in layer.parameters():
-                p_.grad = None
-            xd = x.cuda().requires_grad_(True)
-            y = layer(xd)
-            y.backward(dy.cuda())
-            torch.cuda.synchronize()
-            masks = O.make_masks(cfg, b, s, 1024)
-            y_ref, dx_ref, g_ref = O.decoder_layer_fwd_bwd(x.float(), dy.float(), params, cfg, masks)
-            g_shard = O.shard_params(g_ref, cfg, rank)
-            errs = {"y": rel_err(y, y_ref), "dx": rel_err(xd.grad, dx_ref)}
-            for n, p in layer.named_parameters():
-                errs[n] = rel_err(p.grad, g_shard[n])
-            worst = max(worst, max(errs.values()))
+        # the layer, twice (the second call reuses the symmetric buffer and the epoch flags), every tensor against
+        # the oracle's simulation of `world` mp ranks; sequence_parallel: this rank feeds / returns its [s/n, b, h]
+        # shard and the oracle is the plain layer with shard-sized hidden masks repeated over the ranks
+        errs = layer_parity(group, b, s, h, nh, ffn, dropout=0.1, seed=1024, sequence_parallel=kind in ("sp", "sp_nccl"),
+                            device=f"cuda:{rank}", repeats=2)
+        worst = max(errs.values())
         if kind == "native":
             # the same layer through fx_decoder_layer_fwd / _bwd with the group's fx_tp_comm, interleaved with
             # the Python path on the same symmetric buffer and flag epochs: results must agree
             from fleetx_b200 import functional as Fn
             from fleetx_b200.native import NativeLayer
 
+            cfg = O.LayerConfig(d_model=h, nhead=nh, dim_feedforward=ffn, dropout=0.1, num_partitions=world)
+            params = {k: v.to(torch.bfloat16).float() for k, v in O.init_params(cfg, 1024).items()}
+            g = torch.Generator().manual_seed(3)
+            x = torch.randn(b, s, h, generator=g).to(torch.bfloat16)
+            dy = torch.randn(b, s, h, generator=g).to(torch.bfloat16)
+            layer = layer_from_oracle_params(cfg, params, group=group, device=f"cuda:{rank}")
             layer.eval()  # dropout off: module and native entry need no shared draws
             P = Fn.LayerParams(*layer._params())
             M = layer._meta()
@@ -144,17 +116,24 @@ def _worker(rank, world, port, ret, kind):
         dist.destroy_process_group()
 
 
-@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
-@pytest.mark.parametrize("kind", ["nccl", "symmetric", "native", "sp", "sp_nccl", "model", "model_sp"])
-def test_tp2_layer_matches_oracle(kind):
-    """kind = "nccl": torch.distributed allreduce; "symmetric": the library's own fused allreduce
-    kernel over NVLink peer memory (csrc/comm.cu); "native": additionally the whole-layer C entry points
-    (csrc/layer.cu) driving that kernel through an fx_tp_comm; "sp" / "sp_nccl": sequence_parallel=True with
-    the library's all-gather / reduce-scatter kernel, resp. torch.distributed collectives + permutes."""
+KINDS = ["nccl", "symmetric", "symmetric_v0", "symmetric_v1", "native", "sp", "sp_nccl", "model", "model_sp"]
+CASES = [(2, k) for k in KINDS] + [(w, k) for w in (4, 8) for k in ("symmetric", "symmetric_v1", "native", "sp", "model", "model_sp")]
+
+
+@pytest.mark.parametrize("world,kind", CASES)
+def test_tp_layer_matches_oracle(world, kind):
+    """kind = "nccl": torch.distributed allreduce; "symmetric": the library's own fused allreduce kernel over
+    NVLink peer memory (csrc/comm.cu) in its default variant for that world size (one-shot peer loads at 2 ranks,
+    switch reduce + multicast store above), "symmetric_v0" / "_v1": that kernel forced to the multicast resp.
+    owner-keeps variant; "native": additionally the whole-layer C entry points (csrc/layer.cu) driving that kernel
+    through an fx_tp_comm; "sp" / "sp_nccl": sequence_parallel=True with the library's all-gather / reduce-scatter
+    kernel, resp. torch.distributed collectives + permutes; "model" / "model_sp": the whole model."""
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
     ctx = mp.get_context("spawn")
     ret = ctx.Manager().dict()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, ret, kind)) for r in range(2)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, ret, kind)) for r in range(world)]
     for p in procs:
         p.start()
     for p in procs:
@@ -163,4 +142,4 @@ def test_tp2_layer_matches_oracle(kind):
         if p.is_alive():
             p.kill()
             pytest.fail("TP worker hung")
-    assert len(ret) == 2 and all(v < 2e-2 for v in ret.values()), dict(ret)
+    assert len(ret) == world and all(v < 2e-2 for v in ret.values()), dict(ret)
