@@ -272,6 +272,8 @@ class _TraceLib:
             return fn
 
         def wrapped(*a):
+            if not a:
+                return fn()
             st = torch.cuda.ExternalStream(a[0]) if a[0] else torch.cuda.default_stream()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record(st)

@@ -27,6 +27,20 @@ class TpComm(C.Structure):
                 ("num_blocks", C.c_int), ("epoch", C.POINTER(C.c_uint32))]
 
 
+class TpRowsDesc(C.Structure):
+    """fx_tp_rows_desc (include/fleetx_b200.h)."""
+    _fields_ = [("peer_signal_pads", C.POINTER(C.c_uint64)), ("multicast_in", C.c_uint64), ("multicast_out", C.c_uint64),
+                ("rank", C.c_int), ("world", C.c_int), ("num_blocks", C.c_int), ("mode", C.c_int), ("epoch", C.c_uint32),
+                ("rows", C.c_int), ("h", C.c_int), ("bias", C.c_void_p), ("residual", C.c_void_p), ("p", C.c_float),
+                ("seed", C.c_uint64), ("offset", C.c_uint64), ("mask_in", C.c_void_p), ("gamma", C.c_void_p),
+                ("beta", C.c_void_p), ("eps", C.c_float), ("x_own", C.c_void_p), ("x_full", C.c_void_p),
+                ("mean", C.c_void_p), ("rstd", C.c_void_p), ("dres", C.c_void_p), ("dx_own", C.c_void_p),
+                ("acc", C.c_void_p)]
+
+
+FX_ROWS_FWD_LN, FX_ROWS_FWD_OUT, FX_ROWS_BWD_LN_BDR, FX_ROWS_BWD_LN = 0, 1, 2, 3
+
+
 class LayerDesc(C.Structure):
     """fx_layer_desc (include/fleetx_b200.h)."""
     _fields_ = [("b", C.c_int), ("s", C.c_int), ("h", C.c_int), ("nh_local", C.c_int), ("hd", C.c_int),
@@ -65,9 +79,16 @@ SIGNATURES = {
     "fx_colsum_workspace_bytes": (_sz, [_i, _i]),
     "fx_colsum_bf16": (_i, [_vp, _vp, _i, _vp, _i, _vp, _i, _i]),
     "fx_gemm_bf16": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _i, _vp, _i, _vp, _i, _i, _i, _i, _vp, _vp, _i]),
+    "fx_gemm_splitk_splits": (_i, [_i, _i, _i]),
+    "fx_gemm_splitk_workspace_bytes": (_sz, [_i, _i, _i]),
+    "fx_gemm_bf16_splitk": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _i, _vp, _i, _vp, _i, _i, _vp]),
+    "fx_set_sm_budget": (_i, [_i]),
     "fx_tp_allreduce_bdr": (_i, [_vp, _vp, _vp, _u64, _i, _i, C.c_uint32, _i, _vp, _i, _i, _vp, _vp, _f, _u64, _u64, _vp, _u64, _u64]),
     "fx_tp_allgather_rows": (_i, [_vp, _vp, _u64, _i, _i, C.c_uint32, _i, _vp, _i, _i, _i, _u64]),
     "fx_tp_reduce_scatter_bdr": (_i, [_vp, _vp, _u64, _i, _i, C.c_uint32, _i, _vp, _i, _i, _i, _vp, _vp, _f, _u64, _u64, _vp, _u64]),
+    "fx_tp_rows_max_h": (_i, []),
+    "fx_tp_rows_fused": (_i, [_vp, C.POINTER(TpRowsDesc)]),
+    "fx_tp_allreduce_f32": (_i, [_vp, _vp, _u64, _i, _i, C.c_uint32, _vp, _i]),
     "fx_attn_dropout_mask_bytes": (_sz, [_i, _i, _i]),
     "fx_attn_causal_fwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _f, _u64, _u64]),
     "fx_attn_causal_bwd_workspace_bytes": (_sz, [_i, _i, _i, _i]),

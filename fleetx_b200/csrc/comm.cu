@@ -22,26 +22,13 @@
 //
 // so each byte crosses NVLink once in each direction, and the bias/dropout/residual pass costs no
 // extra trip through HBM. Flags and counters are monotonic (epoch-stamped), never reset.
-#include <stdlib.h>
-
-#include "common.cuh"
+#include "comm.cuh"
 #include "philox.cuh"
-#include "tc5.cuh"
 
 namespace fx {
 namespace comm {
 
-using tc5::bf16_hi;
-using tc5::bf16_lo;
-using tc5::pack_bf16;
-
-constexpr int MAX_RANKS = 8;
 constexpr int THREADS = 512;
-// u32 slots inside each rank's signal pad (byte offset 4096 keeps clear of torch's own use)
-constexpr int SLOT_BASE = 1024;            // in u32 units
-constexpr int SLOT_READY = SLOT_BASE;      // [MAX_RANKS] epoch flag written by each source rank
-constexpr int SLOT_RS_DONE = SLOT_BASE + 16;
-constexpr int SLOT_AG_DONE = SLOT_BASE + 17;
 
 struct Params {
   uint64_t sig[MAX_RANKS];   // signal pad of every rank, as mapped on this GPU
@@ -64,85 +51,12 @@ struct Params {
                              // 2: one shot (2 ranks): phase 3 adds the peer copy to the local one; no phases 1-2
 };
 
-__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
-  uint32_t v;
-  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void red_release_sys_add(uint32_t* p, uint32_t v) {
-  asm volatile("red.release.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-// Wait until *p has reached `target` (wrap-safe). A peer that never arrives would hang the GPU, so
-// the spin carries a 5 s watchdog.
-__device__ __forceinline__ void spin_until(const uint32_t* p, uint32_t target, int tag) {
-  uint32_t spins = 0;
-  uint64_t t0 = 0;
-  while (static_cast<int32_t>(ld_acquire_sys(p) - target) < 0) {
-    if ((++spins & 1023u) == 0) {
-      const uint64_t now = tc5::global_ns();
-      if (t0 == 0) t0 = now;
-      if (now - t0 > 5000000000ull) {
-        printf("fleetx_b200: tp allreduce watchdog: block %d tag %d target %u have %u\n", blockIdx.x, tag, target,
-               ld_acquire_sys(p));
-        __trap();
-      }
-    }
-  }
-}
-__device__ __forceinline__ uint4 ld_relaxed_sys_v4(const uint4* ptr) {
-  uint4 v;
-  asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];"
-               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
-               : "l"(ptr)
-               : "memory");
-  return v;
-}
-// plain (weak) 16-byte load that does not allocate in L1: the data was published by the barrier
-__device__ __forceinline__ uint4 ld_weak_v4(const uint4* ptr) {
-  uint4 v;
-  asm volatile("ld.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
-               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
-               : "l"(ptr)
-               : "memory");
-  return v;
-}
-__device__ __forceinline__ void multimem_st_v4(uint64_t mc_addr, const uint4& v) {
-  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc_addr), "r"(v.x), "r"(v.y),
-               "r"(v.z), "r"(v.w)
-               : "memory");
-}
-// 8 bf16 summed over all replicas by the switch, fp32 accumulation
-__device__ __forceinline__ uint4 multimem_ld_reduce_bf16x8(uint64_t mc_addr) {
-  uint4 v;
-  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
-               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
-               : "l"(mc_addr)
-               : "memory");
-  return v;
-}
-
-__device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
-  f[0] = bf16_lo(u.x); f[1] = bf16_hi(u.x); f[2] = bf16_lo(u.y); f[3] = bf16_hi(u.y);
-  f[4] = bf16_lo(u.z); f[5] = bf16_hi(u.z); f[6] = bf16_lo(u.w); f[7] = bf16_hi(u.w);
-}
-__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
-  return make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
-}
-
 __global__ void __launch_bounds__(THREADS)
 tp_allreduce_kernel(const Params p) {
   const int tid = threadIdx.x;
-  uint32_t* my_sig = reinterpret_cast<uint32_t*>(p.sig[p.rank]);
-  const uint32_t nblk = gridDim.x;
 
   // ---- phase 0: everyone's partial result is in place
-  if (blockIdx.x == 0 && tid < p.world)
-    st_release_sys(reinterpret_cast<uint32_t*>(p.sig[tid]) + SLOT_READY + p.rank, p.epoch);
-  if (tid < p.world) spin_until(my_sig + SLOT_READY + tid, p.epoch, 0);
-  __syncthreads();
+  ranks_ready(p);
 
   const int hv = p.h >> 3;                                   // 16-byte vectors per row
   const size_t stride = static_cast<size_t>(gridDim.x) * THREADS;
@@ -167,15 +81,11 @@ tp_allreduce_kernel(const Params p) {
   }
 
   // ---- phase 2: all blocks of all ranks have stored their reduced slices
-  __threadfence_system();
-  __syncthreads();
-  if (tid < p.world) red_release_sys_add(reinterpret_cast<uint32_t*>(p.sig[tid]) + SLOT_RS_DONE, 1u);
-  if (tid == 0) spin_until(my_sig + SLOT_RS_DONE, p.epoch * nblk * p.world, 1);
-  __syncthreads();
+  rank_barrier(p, SLOT_RS_DONE, SLOT_TICKET_A, true, true, 1);
   } else {
     // the one-shot variant has no reduce-scatter barrier, but it still counts itself in, so that calls of
     // different variants can be mixed on one set of flag pages (every counter advances on every call)
-    if (tid < p.world) red_release_sys_add(reinterpret_cast<uint32_t*>(p.sig[tid]) + SLOT_RS_DONE, 1u);
+    rank_barrier(p, SLOT_RS_DONE, SLOT_TICKET_A, false, false, 1);
   }
 
   // ---- phase 3: epilogue over the complete sum; fused bias + dropout + residual.
@@ -243,9 +153,7 @@ tp_allreduce_kernel(const Params p) {
   }
 
   // ---- phase 4: every rank has finished reading every copy
-  __syncthreads();
-  if (tid < p.world) red_release_sys_add(reinterpret_cast<uint32_t*>(p.sig[tid]) + SLOT_AG_DONE, 1u);
-  if (blockIdx.x == 0 && tid == 0) spin_until(my_sig + SLOT_AG_DONE, p.epoch * nblk * p.world, 2);
+  rank_barrier(p, SLOT_AG_DONE, SLOT_TICKET_B, true, false, 2);
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -281,16 +189,11 @@ struct SeqParParams {
 __global__ void __launch_bounds__(THREADS)
 tp_seqpar_kernel(const SeqParParams p) {
   const int tid = threadIdx.x;
-  uint32_t* my_sig = reinterpret_cast<uint32_t*>(p.sig[p.rank]);
-  const uint32_t nblk = gridDim.x;
-  // every call advances every flag and counter, whichever kernel or mode it is (epochs stay in lockstep)
-  if (blockIdx.x == 0 && tid < p.world)
-    st_release_sys(reinterpret_cast<uint32_t*>(p.sig[tid]) + SLOT_READY + p.rank, p.epoch);
+  // every call advances every flag and counter, whichever kernel or mode it is (epochs stay in lockstep).
   // Every rank has reached this call, i.e. (stream order) finished everything before it: mode 1 — all
   // partial sums are in place before the switch reads them; mode 0 — nobody still reads the previous
   // contents of its copy (a GEMM over an earlier gather) when the multicast stores arrive.
-  if (tid < p.world) spin_until(my_sig + SLOT_READY + tid, p.epoch, 0);
-  __syncthreads();
+  ranks_ready(p);
   const int hv = p.h >> 3;
   const int sl = p.s / p.world;                       // sequence positions per rank
   const size_t total = static_cast<size_t>(sl) * p.b * hv;  // 16-byte vectors of the local shard
@@ -335,15 +238,10 @@ tp_seqpar_kernel(const SeqParParams p) {
       reinterpret_cast<uint4*>(p.out)[v] = res;
     }
   }
-  __threadfence_system();
-  __syncthreads();
-  if (tid < p.world) red_release_sys_add(reinterpret_cast<uint32_t*>(p.sig[tid]) + SLOT_RS_DONE, 1u);
   // mode 0: the gathered tensor is complete once every block of every rank has stored its rows
-  if (p.mode == 0 && tid == 0) spin_until(my_sig + SLOT_RS_DONE, p.epoch * nblk * p.world, 1);
-  __syncthreads();
-  if (tid < p.world) red_release_sys_add(reinterpret_cast<uint32_t*>(p.sig[tid]) + SLOT_AG_DONE, 1u);
+  rank_barrier(p, SLOT_RS_DONE, SLOT_TICKET_A, p.mode == 0, true, 1);
   // mode 1: nobody may overwrite the buffer while a peer's switch reduction still reads it
-  if (p.mode == 1 && blockIdx.x == 0 && tid == 0) spin_until(my_sig + SLOT_AG_DONE, p.epoch * nblk * p.world, 2);
+  rank_barrier(p, SLOT_AG_DONE, SLOT_TICKET_B, p.mode == 1, false, 2);
 }
 
 static int launch_seqpar(void* stream, const uint64_t* peer_signal_pads, uint64_t multicast_ptr, int rank, int world,

@@ -46,6 +46,8 @@ void set_error(const char* fmt, ...);
 
 void count_launch();
 int num_sms();
+// CTAs the persistent kernels launched by THIS thread may use: #SMs, or less after fx_set_sm_budget()
+int sm_budget();
 
 // FX_* environment tuning knobs, read ONCE (thread-safe) the first time any entry point asks; later changes of
 // the environment are ignored, and no launch path calls getenv.

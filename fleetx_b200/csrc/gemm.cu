@@ -46,6 +46,10 @@ struct Params {
   int ldaux;
   int num_m, num_n, num_tiles, num_kb;
   int group;  // M-blocks per rasterisation group
+  // split-K: a work item is (tile, split); split s covers k-blocks [s * kb_per_split, ...) and writes its fp32
+  // partial tile to C + s * split_stride (a [splits, M, ldc] workspace that a second kernel sums)
+  int splits, kb_per_split;
+  size_t split_stride;
 };
 
 template <int BN>
@@ -94,7 +98,7 @@ __device__ __forceinline__ float gelu_tanh_grad(float z) {
 // shared-memory staging tile: lane l owns columns [cl, cl+4) (cl = 4*(l%8)) of rows l/8 + 4*i,
 // so every global access of the warp covers whole 32-byte sectors of 4 consecutive rows.
 __device__ __forceinline__ void epilogue_block(const Params& p, const float* stg, int row0, int col0,
-                                               int lane) {
+                                               int lane, size_t c_off) {
   const int cl = (lane & 7) * 4;
   const int col = col0 + cl;
   if (col >= p.N) return;  // N % 8 == 0, so a 4-column group is entirely in or out
@@ -137,7 +141,7 @@ __device__ __forceinline__ void epilogue_block(const Params& p, const float* stg
     }
 
     if (p.c_f32) {
-      float4* cp = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.C) + (size_t)row * p.ldc + col);
+      float4* cp = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.C) + c_off + (size_t)row * p.ldc + col);
       float4 o = make_float4(v[0], v[1], v[2], v[3]);
       if (p.accumulate) {
         const float4 old = *cp;
@@ -201,16 +205,18 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+      for (int item = blockIdx.x; item < p.num_tiles * p.splits; item += gridDim.x) {
         int m_blk, n_blk;
-        tile_coords(p, tile, m_blk, n_blk);
+        tile_coords(p, item / p.splits, m_blk, n_blk);
         const int m0 = m_blk * BM, n0 = n_blk * BN;
-        for (int kb = 0; kb < p.num_kb; ++kb) {
+        const int kb0 = (item % p.splits) * p.kb_per_split;
+        const int kbn = min(p.kb_per_split, p.num_kb - kb0);
+        for (int kb = 0; kb < kbn; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1, 1);
           mbar_expect_tx(&full[stage], C::STAGE_BYTES);
           uint8_t* sa = smem + stage * C::STAGE_BYTES;
           uint8_t* sb = sa + A_STAGE_BYTES;
-          const int k0 = kb * BK;
+          const int k0 = (kb0 + kb) * BK;
           if (!p.a_mn) {
             tma_load_2d(sa, &tma_a, &full[stage], k0, m0);
           } else {
@@ -245,11 +251,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
     uint32_t phase = 0;
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+    for (int item = blockIdx.x; item < p.num_tiles * p.splits; item += gridDim.x) {
       mbar_wait(&tempty[acc], acc_phase ^ 1, 2);
       tc_fence_after();
       const uint32_t tmem_d = tmem_base + acc * BN;
-      for (int kb = 0; kb < p.num_kb; ++kb) {
+      const int kbn = min(p.kb_per_split, p.num_kb - (item % p.splits) * p.kb_per_split);
+      for (int kb = 0; kb < kbn; ++kb) {
         mbar_wait(&full[stage], phase, 3);
         tc_fence_after();
         if (elect_one()) {
@@ -259,7 +266,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
           umma_ss_lo<1>(tmem_d, a_lo + 2 * a_k, b_lo + 2 * b_k, idesc);
           umma_ss_lo<1>(tmem_d, a_lo + 3 * a_k, b_lo + 3 * b_k, idesc);
           umma_commit(&empty[stage]);
-          if (kb == p.num_kb - 1) umma_commit(&tfull[acc]);
+          if (kb == kbn - 1) umma_commit(&tfull[acc]);
         }
         __syncwarp();
         if (++stage == C::STAGES) {
@@ -276,9 +283,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
     float* stg = staging + warp * (32 * 33);
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+    for (int item = blockIdx.x; item < p.num_tiles * p.splits; item += gridDim.x) {
       int m_blk, n_blk;
-      tile_coords(p, tile, m_blk, n_blk);
+      tile_coords(p, item / p.splits, m_blk, n_blk);
+      const size_t c_off = static_cast<size_t>(item % p.splits) * p.split_stride;
       const int row0 = m_blk * BM + q * 32;
       const int n0 = n_blk * BN;
       mbar_wait(&tfull[acc], acc_phase, 4);
@@ -293,7 +301,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
 #pragma unroll
         for (int i = 0; i < 32; ++i) stg[lane * 33 + i] = __uint_as_float(r[i]);
         __syncwarp();
-        epilogue_block(p, stg, row0, n0 + c * 32, lane);
+        epilogue_block(p, stg, row0, n0 + c * 32, lane, c_off);
         __syncwarp();
       }
       tc_fence_before();
@@ -324,7 +332,11 @@ static int launch(cudaStream_t stream, const CUtensorMap& ta, const CUtensorMap&
   p.num_n = ceil_div(p.N, BN);
   p.num_tiles = p.num_m * p.num_n;
   p.num_kb = ceil_div(p.K, BK);
-  const int grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();
+  if (p.splits < 1) p.splits = 1;
+  p.kb_per_split = ceil_div(p.num_kb, p.splits);
+  p.splits = ceil_div(p.num_kb, p.kb_per_split);  // no empty split
+  const int items = p.num_tiles * p.splits;
+  const int grid = items < sm_budget() ? items : sm_budget();
   gemm_kernel<BN><<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(ta, tb, p);
   FX_LAUNCH_CHECK();
   return FX_OK;
@@ -333,10 +345,43 @@ static int launch(cudaStream_t stream, const CUtensorMap& ta, const CUtensorMap&
 }  // namespace gemm
 }  // namespace fx
 
-extern "C" int fx_gemm_bf16(void* stream, int trans_a, int trans_b, int M, int N, int K,
-                            const void* A, int lda, const void* B, int ldb, void* C, int ldc,
-                            int c_dtype, int accumulate, int epilogue, const void* bias, void* aux,
-                            int ldaux) {
+namespace fx {
+namespace gemm {
+
+// out[i] = sum over splits of ws[s][i] (fp32 partial tiles of a split-K GEMM), as fp32 or bf16
+__global__ void __launch_bounds__(256)
+splitk_reduce_kernel(const float* __restrict__ ws, void* __restrict__ out, int out_f32, size_t n4, size_t stride4,
+                     int splits) {
+  for (size_t i = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x; i < n4; i += static_cast<size_t>(gridDim.x) * 256) {
+    float4 a = __ldg(reinterpret_cast<const float4*>(ws) + i);
+    for (int sp = 1; sp < splits; ++sp) {
+      const float4 b = __ldg(reinterpret_cast<const float4*>(ws) + sp * stride4 + i);
+      a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+    }
+    if (out_f32) reinterpret_cast<float4*>(out)[i] = a;
+    else reinterpret_cast<uint2*>(out)[i] = make_uint2(pack_bf16(a.x, a.y), pack_bf16(a.z, a.w));
+  }
+}
+
+// How many k-ranges a GEMM with few output tiles should be cut into so that its work items fill the machine
+// (the weight gradients at a high mp degree: e.g. 256 x 2048 x 16384 is 16 tiles for 148 SMs).
+static int auto_splits(int M, int N, int K) {
+  const int sms = sm_budget();
+  const long tiles = (long)ceil_div(M, BM) * ceil_div(N, 256);
+  if (tiles * 2 > sms || K < 4096) return 1;
+  int sp = static_cast<int>(sms / tiles);
+  const int max_by_k = K / 2048;  // keep >= 32 k-blocks per split: the drain + fp32 partial store must stay small
+  if (sp > max_by_k) sp = max_by_k;
+  if (sp > 8) sp = 8;
+  return sp < 1 ? 1 : sp;
+}
+
+}  // namespace gemm
+}  // namespace fx
+
+static int gemm_entry(void* stream, int trans_a, int trans_b, int M, int N, int K, const void* A, int lda,
+                      const void* B, int ldb, void* C, int ldc, int c_dtype, int accumulate, int epilogue,
+                      const void* bias, void* aux, int ldaux, int splits, void* split_ws) {
   using namespace fx;
   FX_CHECK_ARG(M > 0 && N > 0 && K > 0, "fx_gemm_bf16: M, N, K must be positive (got %d %d %d)", M, N, K);
   // N, K (and M when A is stored [K, M]) are contiguous dimensions of 16-byte vector / TMA accesses; a plain
@@ -357,7 +402,7 @@ extern "C" int fx_gemm_bf16(void* stream, int trans_a, int trans_b, int M, int N
                "fx_gemm_bf16: pointers must be 16-byte aligned");
 
   gemm::Params p{};
-  const int sms = num_sms();
+  const int sms = sm_budget();
   // Tile time is bound by L2->SM operand traffic per k-block: (128 + BN) * 64 * 2 bytes, i.e.
   // 48 KB for BN = 256 and 32 KB for BN = 128 (for half the flops) — weigh waves by that.
   auto cost = [&](int bn) {
@@ -365,6 +410,7 @@ extern "C" int fx_gemm_bf16(void* stream, int trans_a, int trans_b, int M, int N
     return ((tiles + sms - 1) / sms) * (bn == 256 ? 48 : 32);
   };
   int BN = (N > 128 && cost(256) <= cost(128)) ? 256 : 128;
+  if (splits > 1 && N > 128) BN = 256;  // the split count was chosen for 256-wide tiles
   p.group = 8;
   if (knobs().gemm_bn) BN = knobs().gemm_bn;            // tuning knobs (read once, runtime.cu)
   if (knobs().gemm_group) p.group = knobs().gemm_group;
@@ -386,6 +432,50 @@ extern "C" int fx_gemm_bf16(void* stream, int trans_a, int trans_b, int M, int N
   p.bias = static_cast<const __nv_bfloat16*>(bias);
   p.aux = static_cast<__nv_bfloat16*>(aux);
   p.ldaux = ldaux;
+  p.splits = 1;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (splits > 1) {
+    // every split writes its fp32 partial tiles into its own [M, N] slab of the workspace; a second kernel sums them
+    p.C = split_ws; p.ldc = N; p.c_f32 = 1; p.accumulate = 0;
+    p.splits = splits;
+    p.split_stride = static_cast<size_t>(M) * N;
+    rc = BN == 256 ? gemm::launch<256>(st, ta, tb, p) : gemm::launch<128>(st, ta, tb, p);
+    if (rc) return rc;
+    const size_t n4 = static_cast<size_t>(M) * N / 4;
+    const int blocks = static_cast<int>(n4 / 256 + 1 < (size_t)(4 * num_sms()) ? n4 / 256 + 1 : 4 * num_sms());
+    gemm::splitk_reduce_kernel<<<blocks, 256, 0, st>>>(static_cast<const float*>(split_ws), C, c_dtype == FX_F32, n4, n4,
+                                                       p.splits);
+    FX_LAUNCH_CHECK();
+    return FX_OK;
+  }
   return BN == 256 ? gemm::launch<256>(st, ta, tb, p) : gemm::launch<128>(st, ta, tb, p);
+}
+
+extern "C" int fx_gemm_bf16(void* stream, int trans_a, int trans_b, int M, int N, int K,
+                            const void* A, int lda, const void* B, int ldb, void* C, int ldc,
+                            int c_dtype, int accumulate, int epilogue, const void* bias, void* aux,
+                            int ldaux) {
+  return gemm_entry(stream, trans_a, trans_b, M, N, K, A, lda, B, ldb, C, ldc, c_dtype, accumulate, epilogue, bias, aux,
+                    ldaux, 1, nullptr);
+}
+
+extern "C" int fx_gemm_splitk_splits(int M, int N, int K) {
+  if (M <= 0 || N <= 0 || K <= 0) return 1;
+  return fx::gemm::auto_splits(M, N, K);
+}
+
+extern "C" size_t fx_gemm_splitk_workspace_bytes(int M, int N, int splits) {
+  if (M <= 0 || N <= 0 || splits <= 1) return 0;
+  return static_cast<size_t>(splits) * M * N * sizeof(float);
+}
+
+extern "C" int fx_gemm_bf16_splitk(void* stream, int trans_a, int trans_b, int M, int N, int K, const void* A, int lda,
+                                   const void* B, int ldb, void* C, int c_dtype, int splits, void* workspace) {
+  using namespace fx;
+  FX_CHECK_ARG(splits >= 1 && splits <= 16, "fx_gemm_bf16_splitk: splits must be in [1, 16] (got %d)", splits);
+  FX_CHECK_ARG(splits == 1 || (workspace != nullptr && (uintptr_t)workspace % 16 == 0),
+               "fx_gemm_bf16_splitk: null or misaligned workspace");
+  FX_CHECK_ARG(M > 0 && N > 0 && ((long)M * N) % 4 == 0, "fx_gemm_bf16_splitk: M * N must be a positive multiple of 4");
+  return gemm_entry(stream, trans_a, trans_b, M, N, K, A, lda, B, ldb, C, N, c_dtype, 0, FX_EPI_NONE, nullptr, nullptr, 0,
+                    splits, workspace);
 }

@@ -35,6 +35,12 @@ int num_sms() {
   return n;
 }
 
+static thread_local int g_sm_budget = 0;
+int sm_budget() {
+  const int n = num_sms();
+  return (g_sm_budget > 0 && g_sm_budget < n) ? g_sm_budget : n;
+}
+
 const Knobs& knobs() {
   static Knobs k;
   static std::once_flag once;
@@ -126,5 +132,10 @@ extern "C" {
 const char* fx_last_error(void) { return fx::g_err; }
 int fx_version(void) { return 100; }
 uint64_t fx_launch_count(void) { return fx::g_launches.load(std::memory_order_relaxed); }
+int fx_set_sm_budget(int ctas) {
+  const int old = fx::g_sm_budget;
+  fx::g_sm_budget = ctas > 0 ? ctas : 0;
+  return old;
+}
 
 }  // extern "C"

@@ -88,6 +88,101 @@ class _GroupOps:
         return handle
 
 
+
+    # ---- row-owner form of the allreduce (csrc/comm_rows.cu): rank r owns rows [r0, r1) of the [T, h] tensor and
+    # does the row-wise work that follows the allreduce on them only; the tensor every rank needs next comes back
+    # complete. The base versions state the same contract with all_reduce_() and the library's row-wise kernels
+    # (the plumbing backend; what the CPU tests of the host sequencing run over gloo).
+    row_owner = False  # whether decoder_layer_fwd / _bwd take the row-owner path on this group
+
+    def own_rows(self, rows: int):
+        per = (rows + self.nranks - 1) // self.nranks
+        r0 = min(self.rank * per, rows)
+        return r0, min(r0 + per, rows)
+
+    def acc_buffer(self, h: int, device, dtype=torch.float32) -> torch.Tensor:
+        """[6, h] (fp32 on the GPU): partial sums over the own rows of dgamma2 | dbeta2 | d(out_proj.bias) | dgamma1 |
+        dbeta1 | d(linear2.bias), summed over the ranks by all_reduce_acc() at the end of backward."""
+        return torch.zeros(6, h, dtype=dtype, device=device)
+
+    def all_reduce_acc(self, acc: torch.Tensor) -> torch.Tensor:
+        return self.all_reduce_(acc.clone())
+
+    def fused_fwd_ln(self, part, bias, residual_full, p, seed, offset, mask_in, gamma, beta, eps):
+        """allreduce(part) + bias -> dropout -> + residual = x1; LayerNorm(x1). Returns (x1_own, mean_own,
+        rstd_own, ln_full)."""
+        from . import ops
+
+        r0, r1 = self.own_rows(part.shape[0])
+        x1 = self.all_reduce_bias_dropout_residual(part, bias, residual_full, p, seed, offset, mask_in=mask_in)
+        ln, mean, rstd = ops.layernorm_fwd(x1, gamma, beta, eps)
+        return x1[r0:r1].contiguous(), mean[r0:r1].contiguous(), rstd[r0:r1].contiguous(), ln
+
+    def keep_copy(self, t: torch.Tensor) -> torch.Tensor:
+        """A tensor returned by a fused_* call that must outlive the next call (it may be a view of a
+        communication buffer)."""
+        return t
+
+    def fused_fwd_out(self, part, bias, residual_own, p, seed, offset, mask_in):
+        """allreduce(part) + bias -> dropout -> + residual (own rows given) -> full result on every rank."""
+        from . import ops
+
+        # the dropout mask is indexed by position in the whole tensor: gather the residual rows and apply the
+        # row-wise kernel to the full tensor (this is the plumbing statement, not the fast path)
+        residual_full = self._gather_rows(residual_own, part.shape[0])
+        return self.all_reduce_bias_dropout_residual(part, bias, residual_full, p, seed, offset, mask_in=mask_in)
+
+    def _gather_rows(self, own: torch.Tensor, rows: int) -> torch.Tensor:
+        n, h = self.nranks, own.shape[-1]
+        per = (rows + n - 1) // n
+        if per * n != rows:
+            raise ValueError(f"row-owner path needs rows ({rows}) divisible by the mp degree ({n})")
+        full = torch.empty(rows, h, dtype=own.dtype, device=own.device)
+        self._dist.all_gather_into_tensor(full, own.contiguous(), group=self.pg)
+        return full
+
+    def fused_bwd_ln_bdr_start(self, part, x_own, mean_own, rstd_own, gamma, dres_full, p, seed, offset, mask_in, acc):
+        """d_x1 = LayerNorm'(allreduce(part)) + dres on the own rows; d_ao = dropout'(d_x1) gathered for every rank;
+        acc[0:3] = dgamma | dbeta | column sums of d_ao over the own rows. finish -> (d_x1_own, d_ao_full)."""
+        from . import ops
+
+        rows, h = part.shape
+        r0, r1 = self.own_rows(rows)
+        self.all_reduce_(part)
+        d_x1, dg, db = ops.layernorm_bwd(part[r0:r1].contiguous(), x_own, gamma, mean_own, rstd_own,
+                                         dresidual=dres_full[r0:r1].contiguous())
+        d_ao = ops.bias_dropout_residual_bwd(self._gather_rows(d_x1, rows), p, seed, offset, mask_in=mask_in)
+        acc[0].copy_(dg)
+        acc[1].copy_(db)
+        acc[2].copy_(ops.colsum(d_ao[r0:r1].contiguous(), out_dtype=torch.float32))
+        return (d_x1, d_ao)
+
+    def fused_bwd_ln_bdr_finish(self, handle):
+        return handle
+
+    def fused_bwd_ln_start(self, part, x_full, mean_full, rstd_full, gamma, dres_own, acc):
+        """dx = LayerNorm'(allreduce(part)) + dres on the own rows, gathered for every rank; acc[3:5] = dgamma |
+        dbeta over the own rows. finish -> dx_full."""
+        from . import ops
+
+        rows, h = part.shape
+        r0, r1 = self.own_rows(rows)
+        self.all_reduce_(part)
+        dx, dg, db = ops.layernorm_bwd(part[r0:r1].contiguous(), x_full[r0:r1].contiguous(), gamma,
+                                       mean_full[r0:r1].contiguous(), rstd_full[r0:r1].contiguous(), dresidual=dres_own)
+        acc[3].copy_(dg)
+        acc[4].copy_(db)
+        return (self._gather_rows(dx, rows), self.all_reduce_acc(acc))
+
+    def fused_bwd_ln_finish(self, handle):
+        """-> (dx_full, acc summed over the ranks: the last accumulation into acc has just happened)."""
+        return handle
+
+    def free_sms(self) -> int:
+        """SMs left to the compute kernels while one of this group's collectives runs on another stream (0: all)."""
+        return 0
+
+
 class SingleGroup(_GroupOps):
     rank = 0
     nranks = 1
@@ -164,6 +259,29 @@ class SymmetricTPGroup(TorchDistGroup):
         self._comm_stream = torch.cuda.Stream(device=dev, priority=-1)  # high priority: its blocks go first
         self.num_blocks = num_blocks
         self.max_elems = max_elems
+        # row-owner allreduce (csrc/comm_rows.cu): two more symmetric buffers receive the gathered results (B0: LayerNorm
+        # output / d(attention out), B1: layer output / dx) and a small fp32 one holds the parameter-gradient partial sums.
+        # The flag pages of the first buffer serve every kernel (one epoch sequence).
+        import os
+
+        self.row_owner = os.environ.get("FX_TP_ROWS", "1") != "0"
+        self.rows_blocks = int(os.environ.get("FX_TP_ROWS_BLOCKS", "32"))
+        self._acc_h = min(8192, int(_lib.lib().fx_tp_rows_max_h()))
+        if self.row_owner:
+            self._bufB, self._mcB = [], []
+            for _ in range(2):
+                t = symm_mem.empty(max_elems, dtype=torch.bfloat16, device=dev)
+                hd_ = symm_mem.rendezvous(t, pg.group_name)
+                if not hd_.multicast_ptr:
+                    raise RuntimeError("NVSwitch multicast is not available for this group")
+                self._bufB.append(t)
+                self._mcB.append(int(hd_.multicast_ptr))
+                self._keep_handles = getattr(self, "_keep_handles", []) + [hd_]
+            self._bufC = symm_mem.empty(6 * self._acc_h, dtype=torch.float32, device=dev)
+            hc = symm_mem.rendezvous(self._bufC, pg.group_name)
+            self._mcC = int(hc.multicast_ptr)
+            self._keep_handles.append(hc)
+            self._b0_copy_done = None
         # the flag page must start at zero on every rank before the first call
         pad = self._hdl.get_signal_pad(self.rank, (self._hdl.signal_pad_size // 4,), torch.int32)
         pad.zero_()
@@ -247,6 +365,138 @@ class SymmetricTPGroup(TorchDistGroup):
             multicast_ptr=self._mc, local_buf=self._buf.data_ptr(), rank=self.rank, world=self.nranks,
             num_blocks=self.num_blocks, epoch=ctypes.pointer(c.epoch))
         return c
+
+    # ---- row-owner allreduce: one kernel per site (csrc/comm_rows.cu)
+    def _rows_ok(self, part: torch.Tensor) -> bool:
+        return (self.row_owner and self._is_symmetric(part) and part.shape[0] % self.nranks == 0
+                and part.shape[1] <= self._acc_h)
+
+    def acc_buffer(self, h: int, device, dtype=torch.float32) -> torch.Tensor:
+        if not self.row_owner or h > self._acc_h or dtype != torch.float32:
+            return super().acc_buffer(h, device, dtype)
+        return self._bufC[: 6 * h].view(6, h)  # zeroed slice by slice by the kernels that accumulate into it
+
+    def all_reduce_acc(self, acc: torch.Tensor) -> torch.Tensor:
+        if acc.data_ptr() != self._bufC.data_ptr():
+            return super().all_reduce_acc(acc)
+        out = torch.empty_like(acc)
+        self._epoch += 1
+        self._lib.check(self._lib.lib().fx_tp_allreduce_f32(
+            torch.cuda.current_stream().cuda_stream, self._peer_sigs, self._mcC, self.rank, self.nranks, self._epoch,
+            out.data_ptr(), acc.numel()), "fx_tp_allreduce_f32")
+        return out
+
+    def _rows_call(self, stream, mode, part, out_region, **kw):
+        import ctypes
+
+        rows, h = part.shape
+        d = self._lib.TpRowsDesc()
+        d.peer_signal_pads = ctypes.cast(self._peer_sigs, ctypes.POINTER(ctypes.c_uint64))
+        d.multicast_in = self._mc + self._symm_offset(part) * 2
+        d.multicast_out = self._mcB[out_region]
+        d.rank, d.world, d.num_blocks, d.mode = self.rank, self.nranks, self.rows_blocks, mode
+        self._epoch += 1
+        d.epoch = self._epoch
+        d.rows, d.h = rows, h
+        for k, v in kw.items():
+            setattr(d, k, v.data_ptr() if isinstance(v, torch.Tensor) else v)
+        self._lib.check(self._lib.lib().fx_tp_rows_fused(stream.cuda_stream, ctypes.byref(d)), "fx_tp_rows_fused")
+        return self._bufB[out_region][: rows * h].view(rows, h)
+
+    def fused_fwd_ln(self, part, bias, residual_full, p, seed, offset, mask_in, gamma, beta, eps):
+        if not self._rows_ok(part):
+            return super().fused_fwd_ln(part, bias, residual_full, p, seed, offset, mask_in, gamma, beta, eps)
+        rows, h = part.shape
+        r0, r1 = self.own_rows(rows)
+        dev = part.device
+        x1 = torch.empty(r1 - r0, h, dtype=torch.bfloat16, device=dev)
+        mean = torch.empty(r1 - r0, dtype=torch.float32, device=dev)
+        rstd = torch.empty_like(mean)
+        st = torch.cuda.current_stream()
+        if self._b0_copy_done is not None:
+            st.wait_event(self._b0_copy_done)  # the saved copy of the previous B0 contents has been taken
+        ln = self._rows_call(st, self._lib.FX_ROWS_FWD_LN, part, 0, bias=bias, residual=residual_full, p=float(p),
+                             seed=int(seed), offset=int(offset), mask_in=mask_in, gamma=gamma, beta=beta, eps=float(eps),
+                             x_own=x1, mean=mean, rstd=rstd)
+        return x1, mean, rstd, ln
+
+    def keep_copy(self, t: torch.Tensor) -> torch.Tensor:
+        """Copy a gathered result out of its communication buffer on the group's stream (underneath whatever the
+        caller launches next); consumers wait through wait_kept()."""
+        if not any(t.data_ptr() == b_.data_ptr() for b_ in getattr(self, "_bufB", [])):
+            return t
+        keep = torch.empty_like(t)
+        main = torch.cuda.current_stream()
+        ready = torch.cuda.Event()
+        ready.record(main)
+        with torch.cuda.stream(self._comm_stream):
+            self._comm_stream.wait_event(ready)
+            keep.copy_(t, non_blocking=True)
+            done = torch.cuda.Event()
+            done.record(self._comm_stream)
+        self._b0_copy_done = done
+        keep._fx_ready = done
+        return keep
+
+    def fused_fwd_out(self, part, bias, residual_own, p, seed, offset, mask_in):
+        if not self._rows_ok(part):
+            return super().fused_fwd_out(part, bias, residual_own, p, seed, offset, mask_in)
+        out = self._rows_call(torch.cuda.current_stream(), self._lib.FX_ROWS_FWD_OUT, part, 1, bias=bias,
+                              residual=residual_own, p=float(p), seed=int(seed), offset=int(offset), mask_in=mask_in)
+        return out.clone()  # the caller owns its result; B1 is rewritten by the next call
+
+    def _on_comm_stream(self, fn):
+        main = torch.cuda.current_stream()
+        ready = torch.cuda.Event()
+        ready.record(main)
+        with torch.cuda.stream(self._comm_stream):
+            self._comm_stream.wait_event(ready)
+            res = fn(self._comm_stream)
+            done = torch.cuda.Event()
+            done.record(self._comm_stream)
+        return res, done
+
+    def fused_bwd_ln_bdr_start(self, part, x_own, mean_own, rstd_own, gamma, dres_full, p, seed, offset, mask_in, acc):
+        if not self._rows_ok(part) or acc.data_ptr() != self._bufC.data_ptr():
+            return super().fused_bwd_ln_bdr_start(part, x_own, mean_own, rstd_own, gamma, dres_full, p, seed, offset,
+                                                  mask_in, acc)
+        d_x1 = torch.empty_like(x_own)  # allocated on the caller's stream
+        d_ao, done = self._on_comm_stream(lambda st: self._rows_call(
+            st, self._lib.FX_ROWS_BWD_LN_BDR, part, 0, p=float(p), seed=int(seed), offset=int(offset), mask_in=mask_in,
+            gamma=gamma, x_own=x_own, mean=mean_own, rstd=rstd_own, dres=dres_full, dx_own=d_x1, acc=acc[0:3]))
+        return ("rows", (d_x1, d_ao), done)
+
+    def fused_bwd_ln_bdr_finish(self, handle):
+        if isinstance(handle, tuple) and len(handle) == 3 and handle[0] == "rows":
+            torch.cuda.current_stream().wait_event(handle[2])
+            return handle[1]
+        return handle
+
+    def fused_bwd_ln_start(self, part, x_full, mean_full, rstd_full, gamma, dres_own, acc):
+        if not self._rows_ok(part) or acc.data_ptr() != self._bufC.data_ptr():
+            return super().fused_bwd_ln_start(part, x_full, mean_full, rstd_full, gamma, dres_own, acc)
+        def run(st):
+            dx_ = self._rows_call(st, self._lib.FX_ROWS_BWD_LN, part, 1, gamma=gamma, x_full=x_full, mean=mean_full,
+                                  rstd=rstd_full, dres=dres_own, acc=acc[3:5])
+            with torch.cuda.stream(st):
+                return dx_, self.all_reduce_acc(acc)  # every partial sum is in: the small allreduce rides along
+
+        (dx, tot), done = self._on_comm_stream(run)
+        return ("rows", (dx, tot), done)
+
+    def fused_bwd_ln_finish(self, handle):
+        if isinstance(handle, tuple) and len(handle) == 3 and handle[0] == "rows":
+            torch.cuda.current_stream().wait_event(handle[2])
+            dx, tot = handle[1]
+            tot.record_stream(torch.cuda.current_stream())  # allocated on the group's stream, used on the caller's
+            return dx.clone(), tot  # the caller owns dx; B1 is rewritten by the next call
+        return handle
+
+    def free_sms(self) -> int:
+        import torch as _t
+
+        n = _t.cuda.get_device_properties(_t.cuda.current_device()).multi_processor_count
+        return max(n - self.rows_blocks, 1) if self.row_owner else 0
 
     def _symm_offset(self, t: torch.Tensor):
         """Element offset of t inside the symmetric buffer, or None if t is not a contiguous view of it."""

@@ -125,10 +125,93 @@ def _fwd_pipelined(x: torch.Tensor, P: LayerParams, M: LayerMeta, group, nchunks
     return out.view(b, s, h), saved
 
 
+def _row_owner_path(T: int, h: int, M: LayerMeta, group) -> bool:
+    return bool(group.nranks > 1 and getattr(group, "row_owner", False) and M.normalize_before and T % group.nranks == 0)
+
+
+def decoder_layer_fwd_rows(x: torch.Tensor, P: LayerParams, M: LayerMeta, group):
+    """decoder_layer_fwd for mp degree > 1 with the row-wise work behind each allreduce done by the rank that owns the
+    rows (group.fused_*; csrc/comm_rows.cu): dropout1 + residual + LayerNorm2 and dropout2 + residual run on T/n rows
+    per rank inside the collective, x1 and its statistics exist only as this rank's rows. Same tensors, same
+    (seed, offset) draws — the masks are indexed by position in the whole [T, h] tensor — as the replicated order."""
+    b, s, h = x.shape
+    T = b * s
+    x2 = x.reshape(T, h)
+    scale = M.hd ** -0.5
+    ln1, mean1, rstd1 = ops.layernorm_fwd(x2, P.norm1_w, P.norm1_b, M.eps)          # :534 (replicated: HBM is cheaper than NVLink)
+    qkv = ops.gemm(ln1, P.qkv_w, epilogue=FX_EPI_BIAS, bias=P.qkv_b)                # :166
+    ctx, lse, attn_mask = ops.attn_causal_fwd(qkv.view(b, s, -1), M.nh_local, M.hd, scale, M.p_attn, *M.rng_attn)
+    ctx2 = ctx.view(T, -1)
+    part = ops.gemm(ctx2, P.out_w, out=group.partial_buffer(T, h, x.device))        # :340 local matmul
+    # _mp_allreduce + bias, dropout1 + residual (:546-547), norm2 (:554)
+    x1_own, mean2, rstd2, ln2 = group.fused_fwd_ln(part, P.out_b, x2, M.p_hidden1, *M.rng_h1, M.mask_h1,
+                                                   P.norm2_w, P.norm2_b, M.eps)
+    ln2_keep = group.keep_copy(ln2)  # linear1's weight gradient needs it in backward
+    z = torch.empty(T, P.lin1_w.shape[1], dtype=x.dtype, device=x.device)
+    act = ops.gemm(ln2, P.lin1_w, epilogue=FX_EPI_BIAS_GELU, bias=P.lin1_b, aux=z)  # :558-559
+    part = ops.gemm(act, P.lin2_w, out=group.partial_buffer(T, h, x.device))        # :558 local matmul
+    out = group.fused_fwd_out(part, P.lin2_b, x1_own, M.p_hidden2, *M.rng_h2, M.mask_h2)  # :556-561
+    saved = dict(x=x2, ln1=ln1, mean1=mean1, rstd1=rstd1, qkv=qkv, ctx=ctx2, lse=lse, attn_mask=attn_mask, x1_own=x1_own,
+                 ln2=ln2_keep, mean2=mean2, rstd2=rstd2, z=z, act=act, shape=(b, s, h), rows=True)
+    return out.view(b, s, h), saved
+
+
+def _wait_kept(t: torch.Tensor) -> torch.Tensor:
+    ev = getattr(t, "_fx_ready", None)
+    if ev is not None:
+        torch.cuda.current_stream().wait_event(ev)
+    return t
+
+
+def decoder_layer_bwd_rows(dout: torch.Tensor, saved: dict, P: LayerParams, M: LayerMeta, group):
+    """Adjoint of decoder_layer_fwd_rows. The two allreduces of dX (backward of _c_identity) carry LayerNorm backward,
+    the skip-path adds and dropout1's backward on the owner's rows, and run on the group's stream underneath the
+    weight-gradient GEMMs; gradients of parameters whose kernels saw only this rank's rows (LayerNorm weight / bias,
+    out_proj / linear2 bias) are summed over the ranks in one small fp32 allreduce at the end."""
+    b, s, h = saved["shape"]
+    T = b * s
+    d = dout.reshape(T, h)
+    scale = M.hd ** -0.5
+    g = {}
+    r0, r1 = group.own_rows(T)
+    acc = group.acc_buffer(h, d.device, P.norm1_w.dtype)  # fp32 [6, h]: dgamma2 | dbeta2 | d out_b | dgamma1 | dbeta1 | d lin2_b
+
+    d_y2 = ops.bias_dropout_residual_bwd(d, M.p_hidden2, *M.rng_h2, mask_in=M.mask_h2)   # replicated: the GEMMs need all rows
+    d_z = ops.gemm(d_y2, P.lin2_w, trans_b=True, epilogue=FX_EPI_DGELU, aux=saved["z"])
+    part = ops.gemm(d_z, P.lin1_w, trans_b=True, out=group.partial_buffer(T, h, d.device))
+    pending = group.fused_bwd_ln_bdr_start(part, saved["x1_own"], saved["mean2"], saved["rstd2"], P.norm2_w, d,
+                                           M.p_hidden1, *M.rng_h1, M.mask_h1, acc)
+    with ops.sm_budget(group.free_sms()):  # the collective holds its SMs until every rank is through
+        ops.colsum(d_y2[r0:r1], out=acc[5])                                          # own rows; summed over ranks below
+        g["lin2_w"] = ops.gemm(saved["act"], d_y2, trans_a=True, split_k=True)
+        del d_y2
+        g["lin1_b"] = ops.colsum(d_z)
+        g["lin1_w"] = ops.gemm(_wait_kept(saved["ln2"]), d_z, trans_a=True, split_k=True)
+        del d_z
+    d_x1_own, d_ao = group.fused_bwd_ln_bdr_finish(pending)
+    d_ctx = ops.gemm(d_ao, P.out_w, trans_b=True)
+    d_qkv = ops.attn_causal_bwd(d_ctx.view(b, s, -1), saved["qkv"].view(b, s, -1), saved["ctx"].view(b, s, -1),
+                                saved["lse"], saved["attn_mask"], M.nh_local, M.hd, scale, M.p_attn).view(T, -1)
+    del d_ctx
+    part = ops.gemm(d_qkv, P.qkv_w, trans_b=True, out=group.partial_buffer(T, h, d.device))
+    pending = group.fused_bwd_ln_start(part, saved["x"], saved["mean1"], saved["rstd1"], P.norm1_w, d_x1_own, acc)
+    with ops.sm_budget(group.free_sms()):
+        g["out_w"] = ops.gemm(saved["ctx"], d_ao, trans_a=True, split_k=True)
+        g["qkv_b"] = ops.colsum(d_qkv)
+        g["qkv_w"] = ops.gemm(saved["ln1"], d_qkv, trans_a=True, split_k=True)
+        del d_qkv
+    dx, tot = group.fused_bwd_ln_finish(pending)
+    g["norm2_w"], g["norm2_b"], g["norm1_w"], g["norm1_b"] = tot[0], tot[1], tot[3], tot[4]
+    g["out_b"], g["lin2_b"] = tot[2].to(P.out_b.dtype), tot[5].to(P.lin2_b.dtype)
+    return dx.view(b, s, h), g
+
+
 def decoder_layer_fwd(x: torch.Tensor, P: LayerParams, M: LayerMeta, group):
     """x: bf16 [b, s, h] -> (out bf16 [b, s, h], saved activations for backward)."""
     b, s, h = x.shape
     T = b * s
+    if _row_owner_path(T, h, M, group):
+        return decoder_layer_fwd_rows(x, P, M, group)
     if (_PIPELINE_FWD and getattr(group, "supports_chunks", False) and group.nranks > 1 and M.normalize_before and b % 2 == 0
             and group.partial_buffer(T, h, x.device).data_ptr() == group.partial_buffer(1, h, x.device).data_ptr()
             and T * h <= group.max_elems):
@@ -176,6 +259,8 @@ def decoder_layer_fwd(x: torch.Tensor, P: LayerParams, M: LayerMeta, group):
 
 def decoder_layer_bwd(dout: torch.Tensor, saved: dict, P: LayerParams, M: LayerMeta, group):
     """dout bf16 [b, s, h] -> (dx, dict of per-rank parameter gradients, keyed like LayerParams)."""
+    if saved.get("rows"):
+        return decoder_layer_bwd_rows(dout, saved, P, M, group)
     b, s, h = saved["shape"]
     T = b * s
     d = dout.reshape(T, h)
@@ -193,11 +278,11 @@ def decoder_layer_bwd(dout: torch.Tensor, saved: dict, P: LayerParams, M: LayerM
     # transfer runs on the group's own stream underneath those GEMMs.
     pending = group.all_reduce_start(d_ffn_in)
     g["lin2_b"] = ops.colsum(d_y2)
-    g["lin2_w"] = ops.gemm(saved["act"], d_y2, trans_a=True)                       # dW2 = act^T · dY
+    g["lin2_w"] = ops.gemm(saved["act"], d_y2, trans_a=True, split_k=True)                       # dW2 = act^T · dY
     del d_y2
     g["lin1_b"] = ops.colsum(d_z)
     ffn_in = saved["ln2"] if M.normalize_before else saved["x1"]
-    g["lin1_w"] = ops.gemm(ffn_in, d_z, trans_a=True)
+    g["lin1_w"] = ops.gemm(ffn_in, d_z, trans_a=True, split_k=True)
     del d_z
     d_ffn_in = group.all_reduce_finish(pending)
     if M.normalize_before:
@@ -219,11 +304,11 @@ def decoder_layer_bwd(dout: torch.Tensor, saved: dict, P: LayerParams, M: LayerM
     d_attn_in = ops.gemm(d_qkv, P.qkv_w, trans_b=True, out=group.partial_buffer(T, h, d.device))
     pending = group.all_reduce_start(d_attn_in)                                     # backward of _c_identity
     g["out_b"] = ops.colsum(d_ao)
-    g["out_w"] = ops.gemm(saved["ctx"], d_ao, trans_a=True)
+    g["out_w"] = ops.gemm(saved["ctx"], d_ao, trans_a=True, split_k=True)
     del d_ao
     g["qkv_b"] = ops.colsum(d_qkv)
     attn_in = saved["ln1"] if M.normalize_before else saved["x"]
-    g["qkv_w"] = ops.gemm(attn_in, d_qkv, trans_a=True)
+    g["qkv_w"] = ops.gemm(attn_in, d_qkv, trans_a=True, split_k=True)
     del d_qkv
     d_attn_in = group.all_reduce_finish(pending)
     if M.normalize_before:
@@ -340,13 +425,13 @@ def decoder_layer_bwd_sp(dout_shard: torch.Tensor, saved: dict, P: LayerParams, 
     lin2_b = ops.colsum(d_y2s, out_dtype=torch.float32)
     d_y2 = group.sp_all_gather(d_y2s, b, s)                                          # backward of ReduceScatterOp
     d_z = ops.gemm(d_y2, P.lin2_w, trans_b=True, epilogue=FX_EPI_DGELU, aux=saved["z"])
-    g["lin2_w"] = ops.gemm(saved["act"], d_y2, trans_a=True)
+    g["lin2_w"] = ops.gemm(saved["act"], d_y2, trans_a=True, split_k=True)
     d_ln2_part = ops.gemm(d_z, P.lin1_w, trans_b=True, out=group.partial_buffer(T, h, dev))
     # backward of AllGatherOp; nothing in linear1's weight gradient depends on it, so the transfer runs on the
     # group's stream underneath that GEMM
     pending = group.sp_reduce_scatter_start(d_ln2_part, b, s)
     g["lin1_b"] = ops.colsum(d_z)
-    g["lin1_w"] = ops.gemm(saved["f_full"], d_z, trans_a=True)
+    g["lin1_w"] = ops.gemm(saved["f_full"], d_z, trans_a=True, split_k=True)
     del d_z
     d_ln2s = group.sp_reduce_scatter_finish(pending)
     d_x1s, norm2_w, norm2_b = ops.layernorm_bwd(d_ln2s, saved["x1"], P.norm2_w, saved["mean2"], saved["rstd2"],
@@ -355,14 +440,14 @@ def decoder_layer_bwd_sp(dout_shard: torch.Tensor, saved: dict, P: LayerParams, 
     out_b = ops.colsum(d_aos, out_dtype=torch.float32)
     d_ao = group.sp_all_gather(d_aos, b, s)
     d_ctx = ops.gemm(d_ao, P.out_w, trans_b=True)
-    g["out_w"] = ops.gemm(saved["ctx"], d_ao, trans_a=True)
+    g["out_w"] = ops.gemm(saved["ctx"], d_ao, trans_a=True, split_k=True)
     d_qkv = ops.attn_causal_bwd(d_ctx.view(b, s, -1), saved["qkv"].view(b, s, -1), saved["ctx"].view(b, s, -1),
                                 saved["lse"], saved["attn_mask"], M.nh_local, M.hd, scale, M.p_attn).view(T, -1)
     del d_ctx
     d_ln1_part = ops.gemm(d_qkv, P.qkv_w, trans_b=True, out=group.partial_buffer(T, h, dev))
     pending = group.sp_reduce_scatter_start(d_ln1_part, b, s)
     g["qkv_b"] = ops.colsum(d_qkv)
-    g["qkv_w"] = ops.gemm(saved["a_full"], d_qkv, trans_a=True)
+    g["qkv_w"] = ops.gemm(saved["a_full"], d_qkv, trans_a=True, split_k=True)
     del d_qkv
     d_ln1s = group.sp_reduce_scatter_finish(pending)
     dxs, norm1_w, norm1_b = ops.layernorm_bwd(d_ln1s, saved["x"], P.norm1_w, saved["mean1"], saved["rstd1"],
@@ -429,7 +514,7 @@ class ColumnParallelLinearFunction(torch.autograd.Function):
     def backward(ctx, dy):
         x2, weight = ctx.saved_tensors
         dy2 = dy.reshape(-1, dy.shape[-1]).contiguous()
-        dw = ops.gemm(x2, dy2, trans_a=True)
+        dw = ops.gemm(x2, dy2, trans_a=True, split_k=True)
         db = ops.colsum(dy2) if ctx.has_bias else None
         dx = ops.gemm(dy2, weight, trans_b=True)
         ctx.group.all_reduce_(dx)
@@ -457,7 +542,7 @@ class RowParallelLinearFunction(torch.autograd.Function):
     def backward(ctx, dy):
         x2, weight = ctx.saved_tensors
         dy2 = dy.reshape(-1, dy.shape[-1]).contiguous()
-        dw = ops.gemm(x2, dy2, trans_a=True)
+        dw = ops.gemm(x2, dy2, trans_a=True, split_k=True)
         db = ops.colsum(dy2) if ctx.has_bias else None
         dx = ops.gemm(dy2, weight, trans_b=True)
         return dx.view(ctx.in_shape), dw, db, None

@@ -113,11 +113,16 @@ def bias_dropout_residual_bwd(dout, p: float, seed: int, offset: int, mask_in=No
     return dy.view(dout.shape)
 
 
-def colsum(x: torch.Tensor, out_dtype=torch.bfloat16) -> torch.Tensor:
+def colsum(x: torch.Tensor, out_dtype=torch.bfloat16, out: torch.Tensor | None = None) -> torch.Tensor:
     n = x.shape[-1]
     x2 = _need(x, torch.bfloat16, "x").view(-1, n)
     rows = x2.shape[0]
-    out = torch.empty(n, dtype=out_dtype, device=x.device)
+    if out is None:
+        out = torch.empty(n, dtype=out_dtype, device=x.device)
+    else:
+        out_dtype = out.dtype
+        if out.numel() != n or not out.is_contiguous() or out_dtype not in (torch.float32, torch.bfloat16):
+            raise _lib.FleetXError("colsum: bad output tensor")
     ws = _workspace(_lib.lib().fx_colsum_workspace_bytes(rows, n), x.device)
     check(_lib.lib().fx_colsum_bf16(_stream(), _p(x2), n, _p(out), FX_F32 if out_dtype == torch.float32 else FX_BF16,
                                     _p(ws), rows, n), "fx_colsum_bf16")
@@ -139,10 +144,26 @@ def profile_gemm(enable: bool):
     return rec or []
 
 
+import contextlib
+
+
+@contextlib.contextmanager
+def sm_budget(ctas: int):
+    """While active, the persistent GEMM kernels launched by this thread use at most `ctas` CTAs (0: no limit) —
+    for the stretch of a step where a cross-rank collective holds some SMs on another stream."""
+    old = _lib.lib().fx_set_sm_budget(int(ctas))
+    try:
+        yield
+    finally:
+        _lib.lib().fx_set_sm_budget(old)
+
+
 def gemm(a: torch.Tensor, b: torch.Tensor, *, trans_a: bool = False, trans_b: bool = False,
          out: torch.Tensor | None = None, out_dtype=torch.bfloat16, accumulate: bool = False,
-         epilogue: int = FX_EPI_NONE, bias=None, aux=None) -> torch.Tensor:
-    """C[M,N] = op(A) · op(B); a, b are 2-D contiguous bf16 (see fx_gemm_bf16 for the layouts)."""
+         epilogue: int = FX_EPI_NONE, bias=None, aux=None, split_k: bool = False) -> torch.Tensor:
+    """C[M,N] = op(A) · op(B); a, b are 2-D contiguous bf16 (see fx_gemm_bf16 for the layouts). split_k: let the
+    library cut K into ranges when the output has too few tiles to fill the machine (weight gradients at a high
+    mp degree; fx_gemm_bf16_splitk)."""
     for name, t in (("a", a), ("b", b)):
         if not t.is_cuda or t.dtype != torch.bfloat16 or t.dim() != 2 or t.stride(1) != 1:
             raise _lib.FleetXError(f"gemm: {name} must be a 2-D CUDA bf16 tensor with unit column stride")
@@ -164,9 +185,17 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, trans_a: bool = False, trans_b: bo
     if _gemm_profile is not None:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-    check(_lib.lib().fx_gemm_bf16(_stream(), int(trans_a), int(trans_b), M, N, K, _p(a), a.stride(0), _p(b),
-                                  b.stride(0), _p(out), N, c_dtype, int(accumulate), int(epilogue), _p(bias),
-                                  _p(aux), N if aux is not None else 0), "fx_gemm_bf16")
+    splits = 1
+    if split_k and not accumulate and epilogue == FX_EPI_NONE:
+        splits = _lib.lib().fx_gemm_splitk_splits(M, N, K)
+    if splits > 1:
+        ws = _workspace(_lib.lib().fx_gemm_splitk_workspace_bytes(M, N, splits), a.device)
+        check(_lib.lib().fx_gemm_bf16_splitk(_stream(), int(trans_a), int(trans_b), M, N, K, _p(a), a.stride(0), _p(b),
+                                             b.stride(0), _p(out), c_dtype, splits, _p(ws)), "fx_gemm_bf16_splitk")
+    else:
+        check(_lib.lib().fx_gemm_bf16(_stream(), int(trans_a), int(trans_b), M, N, K, _p(a), a.stride(0), _p(b),
+                                      b.stride(0), _p(out), N, c_dtype, int(accumulate), int(epilogue), _p(bias),
+                                      _p(aux), N if aux is not None else 0), "fx_gemm_bf16")
     if _gemm_profile is not None:
         e1.record()
         _gemm_profile.append((2.0 * M * N * K, e0, e1))

@@ -115,6 +115,21 @@ int fx_gemm_bf16(void* stream, int trans_a, int trans_b, int M, int N, int K, co
                  int lda, const void* B, int ldb, void* C, int ldc, int c_dtype, int accumulate,
                  int epilogue, const void* bias, void* aux, int ldaux);
 
+/* The same product for outputs with few tiles and a long K (the weight gradients dW = x^T·dy at a high mp
+ * degree: 256 x 2048 x 16384 is 16 tiles for 148 SMs): K is cut into `splits` ranges whose fp32 partial tiles
+ * go to `workspace` (fx_gemm_splitk_workspace_bytes) and are summed — in a fixed order, so the result is
+ * deterministic — into C (ldc = N, bf16 or fp32, overwritten). fx_gemm_splitk_splits proposes a split count for
+ * a shape (1: use fx_gemm_bf16). No epilogue, no accumulate. */
+int fx_gemm_splitk_splits(int M, int N, int K);
+size_t fx_gemm_splitk_workspace_bytes(int M, int N, int splits);
+int fx_gemm_bf16_splitk(void* stream, int trans_a, int trans_b, int M, int N, int K, const void* A, int lda,
+                        const void* B, int ldb, void* C, int c_dtype, int splits, void* workspace);
+/* The persistent GEMM kernels launched by the calling thread use at most `ctas` CTAs from now on (0: one per SM).
+ * For a host that runs one of the cross-rank collectives on another stream at the same time: those kernels hold
+ * their SMs until every rank is done, and a persistent GEMM CTA waiting for such an SM would hold its tiles back.
+ * Returns the previous value. Host-side state only; no counterpart in the reference. */
+int fx_set_sm_budget(int ctas);
+
 /* ---- fused causal self-attention: hybrid_model.py:165-186 (_fuse_prepare_qkv) + :268-298 ------
  * qkv is the UNTOUCHED output of qkv_proj, bf16 [b, s, nh_local, 3, hd] (per head q|k|v, as the
  * reshape/transpose/split at :167-173 reads it); out is bf16 [b, s, nh_local*hd], i.e. already
@@ -183,6 +198,60 @@ int fx_tp_reduce_scatter_bdr(void* stream, const uint64_t* peer_signal_pads, uin
                              int world, uint32_t epoch, int num_blocks, void* out_shard, int b, int s, int h,
                              const void* bias, const void* residual_shard, float p, uint64_t seed, uint64_t offset,
                              const uint8_t* mask_in, uint64_t buf_elem_offset);
+
+/* ---- the allreduce with the row-wise work done by the OWNER of each row -----------------------------------
+ * Same reference sites as fx_tp_allreduce_bdr (RowParallelLinear `_mp_allreduce` + bias, hybrid_model.py:157-163,
+ * 505-511; dropout + residual :546-547, :556-561; the backward of `_c_identity`), plus what the layer does to the
+ * summed tensor next: the LayerNorm of :553-554 in forward; LayerNorm backward, the skip-path add and dropout1's
+ * backward (Paddle autograd of :531-554) in backward. Rank r owns rows [r*ceil(rows/world), ...). It pulls its
+ * rows of the partial sums (symmetric buffer behind multicast_in) summed by the switch, applies the chain named
+ * by `mode`, keeps the owner-only results in ordinary local memory and multicasts the tensor every rank needs
+ * next into every rank's copy of a SECOND symmetric buffer (multicast_out); on return (stream order) that copy
+ * is complete on this GPU. Flag pages / epoch / num_blocks rules as fx_tp_allreduce_bdr; h <= fx_tp_rows_max_h().
+ * Tensors marked [rows, h] are indexed by global row, [own, h] by row - first own row.
+ *   FX_ROWS_FWD_LN      x1 = residual[rows,h] + dropout(sum + bias) -> x_own[own,h]; mean, rstd [own];
+ *                       LayerNorm(x1; gamma, beta, eps) -> multicast_out
+ *   FX_ROWS_FWD_OUT     residual[own,h] + dropout(sum + bias) -> multicast_out
+ *   FX_ROWS_BWD_LN_BDR  d_x1 = LayerNorm'(sum; x_own, mean, rstd [own], gamma) + dres[rows,h] -> dx_own[own,h];
+ *                       dropout'(d_x1) -> multicast_out; acc[3,h] (fp32) += dgamma | dbeta | column sums of the
+ *                       multicast tensor, over the own rows
+ *   FX_ROWS_BWD_LN      LayerNorm'(sum; x_full[rows,h], mean, rstd [rows], gamma) + dres[own,h] -> multicast_out;
+ *                       acc[2,h] += dgamma | dbeta over the own rows
+ * Dropout masks are indexed by position in the whole [rows, h] tensor (the 'global_seed' stream: identical on all
+ * ranks). acc is zeroed by the call. No counterpart for the sharing of rows exists in the reference: there every
+ * rank repeats the row-wise ops on the replicated tensor; the results are the same tensors. */
+enum { FX_ROWS_FWD_LN = 0, FX_ROWS_FWD_OUT = 1, FX_ROWS_BWD_LN_BDR = 2, FX_ROWS_BWD_LN = 3 };
+typedef struct fx_tp_rows_desc {
+  const uint64_t* peer_signal_pads; /* host array [world]                                                  */
+  uint64_t multicast_in;            /* NVSwitch multicast address of the partial sums, bf16 [rows, h]      */
+  uint64_t multicast_out;           /* ... of the buffer that receives the gathered result, bf16 [rows, h] */
+  int rank, world, num_blocks, mode;
+  uint32_t epoch;
+  int rows, h;
+  const void* bias;                 /* bf16 [h] or NULL (FWD modes)                                        */
+  const void* residual;             /* bf16, see mode                                                      */
+  float p;                          /* dropout probability (FWD modes, BWD_LN_BDR)                         */
+  uint64_t seed, offset;
+  const uint8_t* mask_in;           /* optional injected keep flags, uint8 [rows, h] (test hook)           */
+  const float* gamma;               /* fp32 [h]                                                            */
+  const float* beta;                /* fp32 [h] (FWD_LN)                                                   */
+  float eps;
+  void* x_own;                      /* bf16 [own, h]: FWD_LN out, BWD_LN_BDR in                            */
+  const void* x_full;               /* bf16 [rows, h]: BWD_LN in                                           */
+  float* mean;                      /* FWD_LN out / BWD_LN_BDR in: [own]; BWD_LN in: [rows]                */
+  float* rstd;
+  const void* dres;                 /* bf16, see mode                                                      */
+  void* dx_own;                     /* bf16 [own, h]: BWD_LN_BDR out                                       */
+  float* acc;                       /* fp32 [3, h] / [2, h] (BWD modes)                                    */
+} fx_tp_rows_desc;
+int fx_tp_rows_max_h(void);
+int fx_tp_rows_fused(void* stream, const fx_tp_rows_desc* desc);
+/* Sum over the ranks of a small fp32 vector that sits in a symmetric buffer (multicast_ptr; n a multiple of 4):
+ * every rank gets the sums in `out` (ordinary local memory). Stands in for all_reduce_gradient_hook
+ * (sequence_parallel_utils.py:136-140) and, with the row-owner kernels above, for the replicated computation of
+ * the LayerNorm / row-parallel-bias gradients. Counts as one epoch on the flag pages. */
+int fx_tp_allreduce_f32(void* stream, const uint64_t* peer_signal_pads, uint64_t multicast_ptr, int rank, int world,
+                        uint32_t epoch, float* out, int n);
 
 /* ---- the whole decoder layer: TransformerDecoderLayer.forward, hybrid_model.py:525-566 -------------
  * One call runs every kernel above in the order of the reference forward (LN -> qkv_proj -> core_attn

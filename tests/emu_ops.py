@@ -91,14 +91,26 @@ def bias_dropout_residual_bwd(dout, p, seed, offset, mask_in=None):
     return dout.clone() if keep is None else dout * keep.to(dout.dtype) / (1.0 - p)
 
 
-def colsum(x, out_dtype=None):
+def colsum(x, out_dtype=None, out=None):
     CALLS.append("colsum")
-    return x.reshape(-1, x.shape[-1]).sum(0)
+    r = x.reshape(-1, x.shape[-1]).sum(0)
+    if out is not None:
+        out.copy_(r)
+        return out
+    return r
 
 
 # ------------------------------------------------------------------------------- fx_gemm_bf16
+import contextlib
+
+
+@contextlib.contextmanager
+def sm_budget(ctas):
+    yield
+
+
 def gemm(a, b, *, trans_a=False, trans_b=False, out=None, out_dtype=None, accumulate=False, epilogue=FX_EPI_NONE,
-         bias=None, aux=None):
+         bias=None, aux=None, split_k=False):
     CALLS.append("gemm")
     acc = (a.t() if trans_a else a) @ (b.t() if trans_b else b)
     if epilogue == FX_EPI_BIAS:

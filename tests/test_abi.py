@@ -74,7 +74,10 @@ def test_every_compute_entry_point_rejects_null_and_empty_arguments(fill):
     """All pointers NULL, every integer `fill`: each entry point must return a negative code with a message (and
     never touch the pointers); the size helpers return a number. No CUDA call is reached."""
     lib = _lib.lib()
-    helpers = {"fx_last_error", "fx_version", "fx_launch_count"}
+    # host-side helpers that compute nothing on the device: version / counters, a split proposal, a size limit,
+    # the CTA budget of the calling thread
+    helpers = {"fx_last_error", "fx_version", "fx_launch_count", "fx_gemm_splitk_splits", "fx_tp_rows_max_h",
+               "fx_set_sm_budget"}
     for name, (res, args) in sorted(_lib.SIGNATURES.items()):
         if name in helpers:
             continue

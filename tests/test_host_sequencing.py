@@ -141,7 +141,7 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _worker(rank, world, port, name, ret):
+def _worker(rank, world, port, name, ret, rows=False):
     import torch.distributed as dist
 
     os.environ["MASTER_ADDR"] = "127.0.0.1"
@@ -157,6 +157,7 @@ def _worker(rank, world, port, name, ret):
         assert m["n"] == world
         P, M = params_and_meta(d, m, rank)
         group = _cpu_group(TorchDistGroup)()
+        group.row_owner = rows  # the row-owner order of the layer over the plumbing statement of its collectives
         if m["dropout"] > 0:
             emu_ops.ATTN_KEEP_QUEUE.append(d[f"mask.attn.{rank}"])
         x, dy = d["in.x"], d["in.dy"]
@@ -169,6 +170,7 @@ def _worker(rank, world, port, name, ret):
             check(dx, cut(d["out.dx"]), "dx shard")
         else:
             y, saved = Fn.decoder_layer_fwd(x, P, M, group)
+            assert bool(saved.get("rows")) == rows
             dx, g = Fn.decoder_layer_bwd(dy, saved, P, M, group)
             check(y, d["out.y"], "y")
             check(dx, d["out.dx"], "dx")
@@ -181,17 +183,20 @@ def _worker(rank, world, port, name, ret):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("name,world", [("ref_layer_tp2", 2), ("ref_layer_tp4", 4), ("ref_layer_sp2", 2),
-                                        ("ref_layer_sp4", 4)])
-def test_tensor_and_sequence_parallel_sequencing_over_gloo(name, world):
+@pytest.mark.parametrize("name,world,rows", [("ref_layer_tp2", 2, False), ("ref_layer_tp4", 4, False),
+                                             ("ref_layer_sp2", 2, False), ("ref_layer_sp4", 4, False),
+                                             ("ref_layer_tp2", 2, True), ("ref_layer_tp4", 4, True)])
+def test_tensor_and_sequence_parallel_sequencing_over_gloo(name, world, rows):
     """Each process runs ONE mp rank of the product's own forward / backward (allreduce after the row-parallel
     matmuls, allreduce of dX in front of the column-parallel ones; sequence parallel: all-gather / reduce-scatter,
     shard-local dropout, summed LayerNorm / bias gradients) and must land on the reference's numbers, which came
-    from n simulated ranks of hybrid_model.py / sequence_parallel_utils.py."""
+    from n simulated ranks of hybrid_model.py / sequence_parallel_utils.py. rows = True: the row-owner order
+    (functional.decoder_layer_fwd_rows / _bwd_rows: each rank does the row-wise work behind every allreduce on its
+    own T/n rows, gathered results, parameter-gradient partial sums summed at the end)."""
     ctx = mp.get_context("spawn")
     ret = ctx.Manager().dict()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, name, ret)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, name, ret, rows)) for r in range(world)]
     for p in procs:
         p.start()
     for p in procs:

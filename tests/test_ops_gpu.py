@@ -105,6 +105,54 @@ def test_gemm_any_row_count(M):
     assert rel_err(out_t, a.float() @ w.float()) < BF16_TOL
 
 
+@pytest.mark.parametrize("M,N,K,splits", [(256, 2048, 16384, 0), (2048, 768, 16384, 0), (264, 520, 4096 + 64, 3),
+                                          (128, 256, 1024, 16), (2048, 1024, 16384, 0)])
+def test_gemm_split_k(M, N, K, splits):
+    """Weight-gradient shapes of a high mp degree (few output tiles, long K): K cut into ranges, fp32 partial tiles
+    summed in a fixed order. splits = 0: the library's own proposal for the shape (must be > 1 for these). Also a
+    ragged case (M, N not multiples of the tile, K not a multiple of splits * 64) and more splits than k-blocks / 4."""
+    from fleetx_b200 import _lib, ops
+
+    lib = _lib.lib()
+    a = _randn(K, M, seed=21)       # wgrad layout: both operands stored [K, *]
+    b = _randn(K, N, seed=22)
+    ref = a.float().t() @ b.float()
+    ad, bd = a.to(_dev()), b.to(_dev())
+    if splits == 0:
+        assert lib.fx_gemm_splitk_splits(M, N, K) > 1
+        c = ops.gemm(ad, bd, trans_a=True, split_k=True)
+        c32 = ops.gemm(ad, bd, trans_a=True, split_k=True, out_dtype=torch.float32)
+    else:
+        ws = torch.empty(lib.fx_gemm_splitk_workspace_bytes(M, N, splits), dtype=torch.uint8, device=_dev())
+        st = torch.cuda.current_stream().cuda_stream
+        c = torch.empty(M, N, dtype=torch.bfloat16, device=_dev())
+        c32 = torch.empty(M, N, dtype=torch.float32, device=_dev())
+        for out, dt in ((c, _lib.FX_BF16), (c32, _lib.FX_F32)):
+            _lib.check(lib.fx_gemm_bf16_splitk(st, 1, 0, M, N, K, ad.data_ptr(), M, bd.data_ptr(), N, out.data_ptr(), dt,
+                                               splits, ws.data_ptr()), "fx_gemm_bf16_splitk")
+    torch.cuda.synchronize()
+    assert rel_err(c, ref) < BF16_TOL
+    assert rel_err(c32, ref) < 2e-4
+    # deterministic: the same call again gives the same bits
+    c2 = ops.gemm(ad, bd, trans_a=True, split_k=True) if splits == 0 else None
+    if c2 is not None:
+        assert torch.equal(c, c2)
+    # and the plain kernel agrees to bf16 rounding
+    assert rel_err(ops.gemm(ad, bd, trans_a=True), ref) < BF16_TOL
+
+
+def test_gemm_under_an_sm_budget():
+    """fx_set_sm_budget: the persistent grid shrinks, the result does not change."""
+    from fleetx_b200 import ops
+
+    a, b = _randn(4096, 1024, seed=31).to(_dev()), _randn(1024, 2048, seed=32).to(_dev())
+    full = ops.gemm(a, b)
+    with ops.sm_budget(100):
+        part = ops.gemm(a, b)
+    assert torch.equal(full, part)
+    assert torch.equal(ops.gemm(a, b), full)  # and the budget is gone again
+
+
 def test_gemm_rejects_bad_arguments():
     from fleetx_b200 import FleetXError, ops
 

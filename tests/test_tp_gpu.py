@@ -24,6 +24,7 @@ def _worker(rank, world, port, ret, kind):
     os.environ["MASTER_PORT"] = str(port)
     if kind.startswith("symmetric_v"):  # force one variant of tp_allreduce_kernel (read once, when the library loads)
         os.environ["FX_COMM_VARIANT"] = kind[-1]
+        os.environ["FX_TP_ROWS"] = "0"  # ... on the replicated order of the layer, which is what uses that kernel
     torch.cuda.set_device(rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     try:
@@ -122,10 +123,10 @@ CASES = [(2, k) for k in KINDS] + [(w, k) for w in (4, 8) for k in ("symmetric",
 
 @pytest.mark.parametrize("world,kind", CASES)
 def test_tp_layer_matches_oracle(world, kind):
-    """kind = "nccl": torch.distributed allreduce; "symmetric": the library's own fused allreduce kernel over
-    NVLink peer memory (csrc/comm.cu) in its default variant for that world size (one-shot peer loads at 2 ranks,
-    switch reduce + multicast store above), "symmetric_v0" / "_v1": that kernel forced to the multicast resp.
-    owner-keeps variant; "native": additionally the whole-layer C entry points (csrc/layer.cu) driving that kernel
+    """kind = "nccl": torch.distributed allreduce; "symmetric": the library's own collectives over NVLink / NVSwitch
+    peer memory in the default, row-owner order of the layer (csrc/comm_rows.cu: each rank does the row-wise work
+    behind every allreduce on its own rows); "symmetric_v0" / "_v1": the replicated order over the fused allreduce
+    kernel of csrc/comm.cu, forced to its multicast resp. owner-keeps variant; "native": additionally the whole-layer C entry points (csrc/layer.cu) driving that kernel
     through an fx_tp_comm; "sp" / "sp_nccl": sequence_parallel=True with the library's all-gather / reduce-scatter
     kernel, resp. torch.distributed collectives + permutes; "model" / "model_sp": the whole model."""
     if torch.cuda.device_count() < world:

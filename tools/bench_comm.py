@@ -34,11 +34,29 @@ def nccl_bdr():
 t_nccl_ar = timeit(lambda: nccl.all_reduce_(y))
 t_nccl = timeit(nccl_bdr)
 if rank == 0: print(json.dumps({"world": world, "nccl_allreduce_ms": round(t_nccl_ar, 4), "nccl_plus_bdr_ms": round(t_nccl, 4)}), flush=True)
-for nb in (64, 96, 128, 148):
-    sym = SymmetricTPGroup(max_elems=rows * h, num_blocks=nb)  # the barrier counters assume a fixed grid per group
-    buf = sym.partial_buffer(rows, h, dev)
-    buf.copy_(y)
+sym = SymmetricTPGroup(max_elems=rows * h)
+buf = sym.partial_buffer(rows, h, dev)
+buf.copy_(y)
+for nb in (16, 32, 64, 96, 148):
+    sym.num_blocks = nb  # the rank barriers do not depend on the grid, so one group serves every block count
     t_f = timeit(lambda: sym.all_reduce_bias_dropout_residual(buf, bias, res, 0.1, 1, 0))
     t_p = timeit(lambda: sym.all_reduce(buf))
-    if rank == 0: print(json.dumps({"world": world, "blocks": nb, "fused_bdr_ms": round(t_f, 4), "fused_plain_ms": round(t_p, 4)}), flush=True)
+    t_ag = timeit(lambda: sym.sp_all_gather(res[: rows // world], 1, rows))
+    t_rs = timeit(lambda: sym.sp_reduce_scatter(buf, 1, rows))
+    if rank == 0: print(json.dumps({"world": world, "blocks": nb, "fused_bdr_ms": round(t_f, 4), "fused_plain_ms": round(t_p, 4),
+                                    "allgather_ms": round(t_ag, 4), "reduce_scatter_ms": round(t_rs, 4)}), flush=True)
+# row-owner kernels (csrc/comm_rows.cu): allreduce with bias + dropout + residual (+ LayerNorm) on the owner's rows
+gamma = torch.ones(h, device=dev); beta = torch.zeros(h, device=dev)
+r0, r1 = sym.own_rows(rows)
+x_own = res[r0:r1].contiguous()
+mean = torch.zeros(r1 - r0, device=dev); rstd = torch.ones(r1 - r0, device=dev)
+acc = sym.acc_buffer(h, dev)
+for nb in (16, 24, 32, 48, 64, 96, 128):
+    sym.rows_blocks = nb
+    t_ln = timeit(lambda: sym.fused_fwd_ln(buf, bias, res, 0.1, 1, 0, None, gamma, beta, 1e-5))
+    t_out = timeit(lambda: sym.fused_fwd_out(buf, bias, x_own, 0.1, 1, 0, None))
+    t_b1 = timeit(lambda: sym.fused_bwd_ln_bdr_finish(sym.fused_bwd_ln_bdr_start(buf, x_own, mean, rstd, gamma, res, 0.1, 1, 0, None, acc)))
+    t_b2 = timeit(lambda: sym.fused_bwd_ln_finish(sym.fused_bwd_ln_start(buf, res, torch.zeros(rows, device=dev), torch.ones(rows, device=dev), gamma, x_own, acc)))
+    if rank == 0: print(json.dumps({"world": world, "rows_blocks": nb, "fwd_ln_ms": round(t_ln, 4), "fwd_out_ms(+clone)": round(t_out, 4),
+                                    "bwd_ln_bdr_ms": round(t_b1, 4), "bwd_ln_ms(+clone)": round(t_b2, 4)}), flush=True)
 dist.destroy_process_group()
