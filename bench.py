@@ -268,7 +268,9 @@ class _TraceLib:
         import torch
 
         fn = getattr(self._real, name)
-        if not name.startswith("fx_") or name.endswith("_bytes") or name in ("fx_last_error", "fx_version", "fx_launch_count"):
+        if (not name.startswith("fx_") or name.endswith("_bytes")
+                or name in ("fx_last_error", "fx_version", "fx_launch_count", "fx_set_sm_budget", "fx_gemm_splitk_splits",
+                            "fx_tp_rows_max_h")):  # host-side helpers: no stream argument
             return fn
 
         def wrapped(*a):

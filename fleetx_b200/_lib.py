@@ -32,10 +32,12 @@ class TpRowsDesc(C.Structure):
     _fields_ = [("peer_signal_pads", C.POINTER(C.c_uint64)), ("multicast_in", C.c_uint64), ("multicast_out", C.c_uint64),
                 ("rank", C.c_int), ("world", C.c_int), ("num_blocks", C.c_int), ("mode", C.c_int), ("epoch", C.c_uint32),
                 ("rows", C.c_int), ("h", C.c_int), ("bias", C.c_void_p), ("residual", C.c_void_p), ("p", C.c_float),
-                ("seed", C.c_uint64), ("offset", C.c_uint64), ("mask_in", C.c_void_p), ("gamma", C.c_void_p),
+                ("seed", C.c_uint64), ("offset", C.c_uint64), ("dropout_elem_offset", C.c_uint64), ("mask_in", C.c_void_p),
+                ("gamma", C.c_void_p),
                 ("beta", C.c_void_p), ("eps", C.c_float), ("x_own", C.c_void_p), ("x_full", C.c_void_p),
                 ("mean", C.c_void_p), ("rstd", C.c_void_p), ("dres", C.c_void_p), ("dx_own", C.c_void_p),
-                ("acc", C.c_void_p)]
+                ("acc", C.c_void_p), ("acc_accumulate", C.c_int), ("multicast_sum", C.c_uint64), ("sum_out", C.c_void_p),
+                ("sum_n", C.c_int)]
 
 
 FX_ROWS_FWD_LN, FX_ROWS_FWD_OUT, FX_ROWS_BWD_LN_BDR, FX_ROWS_BWD_LN = 0, 1, 2, 3
@@ -91,6 +93,7 @@ SIGNATURES = {
     "fx_tp_allreduce_f32": (_i, [_vp, _vp, _u64, _i, _i, C.c_uint32, _vp, _i]),
     "fx_attn_dropout_mask_bytes": (_sz, [_i, _i, _i]),
     "fx_attn_causal_fwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _f, _u64, _u64]),
+    "fx_attn_causal_fwd_at": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _f, _u64, _u64, _i]),
     "fx_attn_causal_bwd_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "fx_attn_causal_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _f]),
     "fx_embedding_fwd": (_i, [_vp, _vp, _vp, _vp, C.c_int64, C.c_int64, _vp, _vp, _vp, C.c_int64, _i, _i, _f, _u64, _u64]),

@@ -78,6 +78,7 @@ struct MaskParams {
   uint32_t* mask;
   int b, s, nh, wpr;
   uint32_t thresh2, off_lo, off_hi;
+  uint64_t bh0;  // (batch, head) index of this call's first pair inside the batch the mask is defined on
   PhiloxKeys keys;
 };
 
@@ -91,7 +92,7 @@ attn_dropout_mask_kernel(const MaskParams p) {
   const int n_words = min(p.wpr, (blockIdx.x * 32 / 128 + 1) * 4);
   const uint64_t bh = blockIdx.y;
   const uint64_t s8 = static_cast<uint64_t>((p.s + 7) / 8);
-  const uint64_t grp_row = (bh * p.s + q) * s8;
+  const uint64_t grp_row = ((p.bh0 + bh) * p.s + q) * s8;
   uint32_t* out_row = p.mask + (bh * p.s + q) * p.wpr;
   for (int w = warp; w < n_words; w += 8) {
     uint32_t word = 0;
@@ -1138,7 +1139,14 @@ extern "C" size_t fx_attn_dropout_mask_bytes(int b, int s, int nh) {
 
 extern "C" int fx_attn_causal_fwd(void* stream, const void* qkv, void* out, float* lse, void* dropout_mask, int b,
                                   int s, int nh, int hd, float scale, float p_drop, uint64_t seed, uint64_t offset) {
+  return fx_attn_causal_fwd_at(stream, qkv, out, lse, dropout_mask, b, s, nh, hd, scale, p_drop, seed, offset, 0);
+}
+
+extern "C" int fx_attn_causal_fwd_at(void* stream, const void* qkv, void* out, float* lse, void* dropout_mask, int b,
+                                     int s, int nh, int hd, float scale, float p_drop, uint64_t seed, uint64_t offset,
+                                     int batch0) {
   using namespace fx;
+  FX_CHECK_ARG(batch0 >= 0, "fx_attn_causal_fwd: negative batch offset");
   FX_CHECK_ARG(b > 0 && s > 0 && nh > 0, "fx_attn_causal_fwd: empty input (b %d, s %d, nh %d)", b, s, nh);
   FX_CHECK_ARG(hd == 64 || hd == 128, "fx_attn_causal_fwd: head_dim must be 64 or 128 (got %d)", hd);
   FX_CHECK_ARG(nh <= 65535 && b * nh <= 65535, "fx_attn_causal_fwd: nh and b*nh must be <= 65535");
@@ -1157,6 +1165,7 @@ extern "C" int fx_attn_causal_fwd(void* stream, const void* qkv, void* out, floa
     m.thresh2 = dropout_threshold(p_drop) * 0x10001u;
     m.off_lo = static_cast<uint32_t>(offset); m.off_hi = static_cast<uint32_t>(offset >> 32);
     m.keys = philox_round_keys(seed);
+    m.bh0 = static_cast<uint64_t>(batch0) * nh;
     dim3 grid((s + 31) / 32, b * nh);
     attn::attn_dropout_mask_kernel<<<grid, 256, 0, st>>>(m);
     FX_LAUNCH_CHECK();

@@ -40,6 +40,7 @@ struct RowsParams {
   float p_drop, scale;
   uint32_t thresh;
   uint64_t seed, offset;
+  uint64_t drop_vec0;              // index, in the whole tensor the mask is defined on, of this call's first 16-byte vector
   const uint8_t* mask_in;          // [rows, h] keep flags (test hook), global row
   const float* gamma;
   const float* beta;
@@ -51,6 +52,9 @@ struct RowsParams {
   const __nv_bfloat16* dres;       // BWD_LN_BDR: [rows, h] (global row); BWD_LN: [own, h] (local row)
   __nv_bfloat16* dx_own;           // BWD_LN_BDR: out d_x1 [own, h]
   float* acc;                      // BWD: fp32 [3, h] dgamma | dbeta | dbias accumulators (atomics; host zeroes)
+  uint64_t mc_sum;                 // BWD_LN, optional: multicast address of a small fp32 vector to sum over the ranks ...
+  float* sum_out;                  // ... into this local vector of sum_n floats once every rank's rows are done
+  int sum_n;
 };
 
 __device__ __forceinline__ float warp_sum(float v) {
@@ -96,7 +100,7 @@ __device__ __forceinline__ uint32_t keep8(const RowsParams& p, size_t gv) {
     return k;
   }
   if (p.p_drop > 0.f) {
-    const Philox8 rnd = philox4x32_10(p.seed, p.offset, gv);
+    const Philox8 rnd = philox4x32_10(p.seed, p.offset, p.drop_vec0 + gv);
     uint32_t k = 0;
 #pragma unroll
     for (int j = 0; j < 8; ++j) k |= philox_keep(rnd, j, p.thresh) ? (1u << j) : 0u;
@@ -282,7 +286,14 @@ tp_rows_kernel(const RowsParams p) {
   }
   // every rank's rows have landed in every copy of the output buffer; nobody still reads the partial sums
   rank_barrier(p, SLOT_RS_DONE, SLOT_TICKET_A, true, true, 1);
-  rank_barrier(p, SLOT_AG_DONE, SLOT_TICKET_B, false, false, 2);
+  const bool sum_tail = MODE == MODE_BWD_LN && p.sum_out != nullptr;
+  if (sum_tail) {
+    // ... and every rank's parameter-gradient partial sums are final: each rank pulls the whole (small) vector
+    // through the switch. Nobody may touch its copy again while a peer still reads it: barrier B waits.
+    for (int i = (blockIdx.x * ROWS_THREADS + tid) * 4; i < p.sum_n; i += gridDim.x * ROWS_THREADS * 4)
+      *reinterpret_cast<float4*>(p.sum_out + i) = multimem_ld_reduce_f32x4(p.mc_sum + static_cast<uint64_t>(i) * 4);
+  }
+  rank_barrier(p, SLOT_AG_DONE, SLOT_TICKET_B, sum_tail, false, 2);
 }
 
 // Sum of a small fp32 vector over the ranks (the parameter-gradient partial sums each rank made over its own
@@ -360,6 +371,8 @@ extern "C" int fx_tp_rows_fused(void* stream, const fx_tp_rows_desc* d) {
   q.p_drop = d->p; q.scale = 1.0f / (1.0f - d->p);
   q.thresh = dropout_threshold(d->p);
   q.seed = d->seed; q.offset = d->offset;
+  FX_CHECK_ARG(d->dropout_elem_offset % 8 == 0, "fx_tp_rows_fused: dropout_elem_offset must be a multiple of 8");
+  q.drop_vec0 = d->dropout_elem_offset / 8;
   q.mask_in = d->mask_in;
   q.gamma = d->gamma; q.beta = d->beta; q.eps = d->eps;
   q.x_own = static_cast<__nv_bfloat16*>(d->x_own);
@@ -368,6 +381,10 @@ extern "C" int fx_tp_rows_fused(void* stream, const fx_tp_rows_desc* d) {
   q.dres = static_cast<const __nv_bfloat16*>(d->dres);
   q.dx_own = static_cast<__nv_bfloat16*>(d->dx_own);
   q.acc = d->acc;
+  q.mc_sum = d->multicast_sum; q.sum_out = d->sum_out; q.sum_n = d->sum_n;
+  FX_CHECK_ARG(q.sum_out == nullptr || (d->mode == comm::MODE_BWD_LN && q.mc_sum && q.sum_n > 0 && q.sum_n % 4 == 0 &&
+                                        (uintptr_t)q.sum_out % 16 == 0),
+               "fx_tp_rows_fused: the trailing sum needs mode BWD_LN, a multicast address and a multiple of 4 floats");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   switch (d->mode) {
     case comm::MODE_FWD_LN:
@@ -379,11 +396,11 @@ extern "C" int fx_tp_rows_fused(void* stream, const fx_tp_rows_desc* d) {
     case comm::MODE_BWD_LN_BDR:
       FX_CHECK_ARG(q.x_own && q.mean && q.rstd && q.gamma && q.dres && q.dx_own && q.acc,
                    "fx_tp_rows_fused(BWD_LN_BDR): null pointer");
-      FX_CUDA(cudaMemsetAsync(q.acc, 0, sizeof(float) * 3 * q.h, st));
+      if (!d->acc_accumulate) FX_CUDA(cudaMemsetAsync(q.acc, 0, sizeof(float) * 3 * q.h, st));
       return comm::launch_rows<comm::MODE_BWD_LN_BDR>(st, d->num_blocks, q);
     default:
       FX_CHECK_ARG(q.x_full && q.mean && q.rstd && q.gamma && q.dres && q.acc, "fx_tp_rows_fused(BWD_LN): null pointer");
-      FX_CUDA(cudaMemsetAsync(q.acc, 0, sizeof(float) * 2 * q.h, st));
+      if (!d->acc_accumulate) FX_CUDA(cudaMemsetAsync(q.acc, 0, sizeof(float) * 2 * q.h, st));
       return comm::launch_rows<comm::MODE_BWD_LN>(st, d->num_blocks, q);
   }
 }

@@ -366,14 +366,22 @@ splitk_reduce_kernel(const float* __restrict__ ws, void* __restrict__ out, int o
 // How many k-ranges a GEMM with few output tiles should be cut into so that its work items fill the machine
 // (the weight gradients at a high mp degree: e.g. 256 x 2048 x 16384 is 16 tiles for 148 SMs).
 static int auto_splits(int M, int N, int K) {
-  const int sms = sm_budget();
+  const int ctas = sm_budget();
   const long tiles = (long)ceil_div(M, BM) * ceil_div(N, 256);
-  if (tiles * 2 > sms || K < 4096) return 1;
-  int sp = static_cast<int>(sms / tiles);
-  const int max_by_k = K / 2048;  // keep >= 32 k-blocks per split: the drain + fp32 partial store must stay small
-  if (sp > max_by_k) sp = max_by_k;
-  if (sp > 8) sp = 8;
-  return sp < 1 ? 1 : sp;
+  if (tiles >= ctas || K < 4096) return 1;
+  // time ~ waves of work items / splits (+ a little per split for the fp32 partial tiles and their sum);
+  // keep >= 16 k-blocks per split so that the drain of a tile stays small next to its main loop
+  int best = 1;
+  float best_cost = 1e30f;
+  for (int sp = 1; sp <= 8 && K / sp >= 1024; ++sp) {
+    const long waves = (tiles * sp + ctas - 1) / ctas;
+    const float cost = static_cast<float>(waves) / sp + 0.03f * (sp - 1);
+    if (cost < best_cost - 1e-6f) {
+      best_cost = cost;
+      best = sp;
+    }
+  }
+  return best;
 }
 
 }  // namespace gemm

@@ -89,11 +89,16 @@ class _GroupOps:
 
 
 
-    # ---- row-owner form of the allreduce (csrc/comm_rows.cu): rank r owns rows [r0, r1) of the [T, h] tensor and
-    # does the row-wise work that follows the allreduce on them only; the tensor every rank needs next comes back
-    # complete. The base versions state the same contract with all_reduce_() and the library's row-wise kernels
-    # (the plumbing backend; what the CPU tests of the host sequencing run over gloo).
-    row_owner = False  # whether decoder_layer_fwd / _bwd take the row-owner path on this group
+    # ---- row-owner form of the allreduce (csrc/comm_rows.cu): rank r owns rows [r0, r1) of the [rows, h] tensor of a
+    # call and does the row-wise work that follows the allreduce on them only; the tensor every rank needs next comes
+    # back complete. Every operation is split into start / finish so that the caller can put independent work (the
+    # other batch chunk, the weight-gradient GEMMs) in between. The base versions state the same contract with
+    # all_reduce_() and the library's row-wise kernels (the plumbing backend; what the CPU tests of the host
+    # sequencing run over gloo). `part` may be a row slice [rows, h] of a larger [T, h] tensor (batch chunks);
+    # mask_in / residual / dres are then the matching slices and drop_off is the element offset of the slice inside
+    # [T, h] (the dropout mask is indexed by position in the whole tensor).
+    row_owner = False     # whether decoder_layer_fwd / _bwd take the row-owner path on this group
+    pipeline_chunks = 1   # batch chunks that path pipelines through the collectives
 
     def own_rows(self, rows: int):
         per = (rows + self.nranks - 1) // self.nranks
@@ -108,29 +113,22 @@ class _GroupOps:
     def all_reduce_acc(self, acc: torch.Tensor) -> torch.Tensor:
         return self.all_reduce_(acc.clone())
 
-    def fused_fwd_ln(self, part, bias, residual_full, p, seed, offset, mask_in, gamma, beta, eps):
-        """allreduce(part) + bias -> dropout -> + residual = x1; LayerNorm(x1). Returns (x1_own, mean_own,
-        rstd_own, ln_full)."""
-        from . import ops
+    def free_sms(self) -> int:
+        """SMs left to the compute kernels while one of this group's collectives runs on another stream (0: all)."""
+        return 0
 
-        r0, r1 = self.own_rows(part.shape[0])
-        x1 = self.all_reduce_bias_dropout_residual(part, bias, residual_full, p, seed, offset, mask_in=mask_in)
-        ln, mean, rstd = ops.layernorm_fwd(x1, gamma, beta, eps)
-        return x1[r0:r1].contiguous(), mean[r0:r1].contiguous(), rstd[r0:r1].contiguous(), ln
+    def keep_copy(self, t: torch.Tensor, dst: torch.Tensor) -> None:
+        """dst <- t, where t came back from a fused call and may be a view of a communication buffer that the next
+        call rewrites (dst must be waited for with wait_kept before it is read)."""
+        dst.copy_(t)
 
-    def keep_copy(self, t: torch.Tensor) -> torch.Tensor:
-        """A tensor returned by a fused_* call that must outlive the next call (it may be a view of a
-        communication buffer)."""
+    def wait_kept(self, t: torch.Tensor) -> torch.Tensor:
         return t
 
-    def fused_fwd_out(self, part, bias, residual_own, p, seed, offset, mask_in):
-        """allreduce(part) + bias -> dropout -> + residual (own rows given) -> full result on every rank."""
-        from . import ops
-
-        # the dropout mask is indexed by position in the whole tensor: gather the residual rows and apply the
-        # row-wise kernel to the full tensor (this is the plumbing statement, not the fast path)
-        residual_full = self._gather_rows(residual_own, part.shape[0])
-        return self.all_reduce_bias_dropout_residual(part, bias, residual_full, p, seed, offset, mask_in=mask_in)
+    def _no_generated_mask_in_chunks(self, p, mask_in, drop_off):
+        if p > 0 and mask_in is None and drop_off:
+            raise NotImplementedError("the plumbing statement of the row-owner collectives draws dropout masks from "
+                                      "element 0: batch chunks need injected masks (or pipeline_chunks = 1)")
 
     def _gather_rows(self, own: torch.Tensor, rows: int) -> torch.Tensor:
         n, h = self.nranks, own.shape[-1]
@@ -141,46 +139,70 @@ class _GroupOps:
         self._dist.all_gather_into_tensor(full, own.contiguous(), group=self.pg)
         return full
 
-    def fused_bwd_ln_bdr_start(self, part, x_own, mean_own, rstd_own, gamma, dres_full, p, seed, offset, mask_in, acc):
-        """d_x1 = LayerNorm'(allreduce(part)) + dres on the own rows; d_ao = dropout'(d_x1) gathered for every rank;
-        acc[0:3] = dgamma | dbeta | column sums of d_ao over the own rows. finish -> (d_x1_own, d_ao_full)."""
+    def fwd_ln_start(self, part, bias, residual, p, seed, offset, mask_in, gamma, beta, eps, drop_off=0):
+        """allreduce(part) + bias -> dropout -> + residual = x1; LayerNorm(x1).
+        finish -> (x1_own, mean_own, rstd_own, ln_full)."""
         from . import ops
 
+        self._no_generated_mask_in_chunks(p, mask_in, drop_off)
+        r0, r1 = self.own_rows(part.shape[0])
+        x1 = self.all_reduce_bias_dropout_residual(part, bias, residual, p, seed, offset, mask_in=mask_in)
+        ln, mean, rstd = ops.layernorm_fwd(x1, gamma, beta, eps)
+        return x1[r0:r1].contiguous(), mean[r0:r1].contiguous(), rstd[r0:r1].contiguous(), ln
+
+    def fwd_ln_finish(self, handle):
+        return handle
+
+    def fwd_out_start(self, part, bias, residual_own, p, seed, offset, mask_in, drop_off=0):
+        """allreduce(part) + bias -> dropout -> + residual (own rows given). finish(handle, out) writes the full
+        result into `out` (a [rows, h] destination owned by the caller)."""
+        self._no_generated_mask_in_chunks(p, mask_in, drop_off)
+        # the dropout mask is indexed by position in the whole tensor: gather the residual rows and apply the
+        # row-wise kernel to the full tensor (this is the plumbing statement, not the fast path)
+        residual_full = self._gather_rows(residual_own, part.shape[0])
+        return self.all_reduce_bias_dropout_residual(part, bias, residual_full, p, seed, offset, mask_in=mask_in)
+
+    def fwd_out_finish(self, handle, out):
+        out.copy_(handle)
+
+    def bwd_ln_bdr_start(self, part, x_own, mean_own, rstd_own, gamma, dres, p, seed, offset, mask_in, acc,
+                         drop_off=0, accumulate=False):
+        """d_x1 = LayerNorm'(allreduce(part)) + dres on the own rows; d_ao = dropout'(d_x1) gathered for every rank;
+        acc[0:3] (+)= dgamma | dbeta | column sums of d_ao over the own rows. finish -> (d_x1_own, d_ao_full)."""
+        from . import ops
+
+        self._no_generated_mask_in_chunks(p, mask_in, drop_off)
         rows, h = part.shape
         r0, r1 = self.own_rows(rows)
         self.all_reduce_(part)
         d_x1, dg, db = ops.layernorm_bwd(part[r0:r1].contiguous(), x_own, gamma, mean_own, rstd_own,
-                                         dresidual=dres_full[r0:r1].contiguous())
+                                         dresidual=dres[r0:r1].contiguous())
         d_ao = ops.bias_dropout_residual_bwd(self._gather_rows(d_x1, rows), p, seed, offset, mask_in=mask_in)
-        acc[0].copy_(dg)
-        acc[1].copy_(db)
-        acc[2].copy_(ops.colsum(d_ao[r0:r1].contiguous(), out_dtype=torch.float32))
+        for i, v in enumerate((dg, db, ops.colsum(d_ao[r0:r1].contiguous(), out_dtype=acc.dtype))):
+            acc[i].copy_(acc[i] + v.to(acc.dtype) if accumulate else v)
         return (d_x1, d_ao)
 
-    def fused_bwd_ln_bdr_finish(self, handle):
+    def bwd_ln_bdr_finish(self, handle):
         return handle
 
-    def fused_bwd_ln_start(self, part, x_full, mean_full, rstd_full, gamma, dres_own, acc):
-        """dx = LayerNorm'(allreduce(part)) + dres on the own rows, gathered for every rank; acc[3:5] = dgamma |
-        dbeta over the own rows. finish -> dx_full."""
+    def bwd_ln_start(self, part, x, mean, rstd, gamma, dres_own, acc, accumulate=False, last=True):
+        """dx = LayerNorm'(allreduce(part)) + dres on the own rows, gathered for every rank; acc[3:5] (+)= dgamma |
+        dbeta over the own rows. last: this is the final accumulation into acc of the backward pass, so the sum of
+        acc over the ranks rides along. finish(handle, out) writes dx into `out`; -> summed acc or None."""
         from . import ops
 
         rows, h = part.shape
         r0, r1 = self.own_rows(rows)
         self.all_reduce_(part)
-        dx, dg, db = ops.layernorm_bwd(part[r0:r1].contiguous(), x_full[r0:r1].contiguous(), gamma,
-                                       mean_full[r0:r1].contiguous(), rstd_full[r0:r1].contiguous(), dresidual=dres_own)
-        acc[3].copy_(dg)
-        acc[4].copy_(db)
-        return (self._gather_rows(dx, rows), self.all_reduce_acc(acc))
+        dx, dg, db = ops.layernorm_bwd(part[r0:r1].contiguous(), x[r0:r1].contiguous(), gamma,
+                                       mean[r0:r1].contiguous(), rstd[r0:r1].contiguous(), dresidual=dres_own)
+        for i, v in ((3, dg), (4, db)):
+            acc[i].copy_(acc[i] + v.to(acc.dtype) if accumulate else v)
+        return (self._gather_rows(dx, rows), self.all_reduce_acc(acc) if last else None)
 
-    def fused_bwd_ln_finish(self, handle):
-        """-> (dx_full, acc summed over the ranks: the last accumulation into acc has just happened)."""
-        return handle
-
-    def free_sms(self) -> int:
-        """SMs left to the compute kernels while one of this group's collectives runs on another stream (0: all)."""
-        return 0
+    def bwd_ln_finish(self, handle, out):
+        out.copy_(handle[0])
+        return handle[1]
 
 
 class SingleGroup(_GroupOps):
@@ -281,7 +303,12 @@ class SymmetricTPGroup(TorchDistGroup):
             hc = symm_mem.rendezvous(self._bufC, pg.group_name)
             self._mcC = int(hc.multicast_ptr)
             self._keep_handles.append(hc)
-            self._b0_copy_done = None
+            self._b0_copies = []   # events of copies still being taken out of B0
+            self._kept = {}        # data_ptr of a keep_copy destination -> event its readers wait for
+            self._copy_stream = torch.cuda.Stream(device=dev)
+            # batch chunks pipelined through the collectives: measured slower than one pass at 2 and 8 GPUs (half-size
+            # collectives take 0.7x the time of whole ones, the GEMMs beside them quantise worse), so 1 by default
+            self.pipeline_chunks = int(os.environ.get("FX_TP_CHUNKS", "1"))
         # the flag page must start at zero on every rank before the first call
         pad = self._hdl.get_signal_pad(self.rank, (self._hdl.signal_pad_size // 4,), torch.int32)
         pad.zero_()
@@ -366,7 +393,7 @@ class SymmetricTPGroup(TorchDistGroup):
             num_blocks=self.num_blocks, epoch=ctypes.pointer(c.epoch))
         return c
 
-    # ---- row-owner allreduce: one kernel per site (csrc/comm_rows.cu)
+    # ---- row-owner allreduce: one kernel per site (csrc/comm_rows.cu), always launched on the group's stream
     def _rows_ok(self, part: torch.Tensor) -> bool:
         return (self.row_owner and self._is_symmetric(part) and part.shape[0] % self.nranks == 0
                 and part.shape[1] <= self._acc_h)
@@ -386,14 +413,19 @@ class SymmetricTPGroup(TorchDistGroup):
             out.data_ptr(), acc.numel()), "fx_tp_allreduce_f32")
         return out
 
+    def free_sms(self) -> int:
+        n = torch.cuda.get_device_properties(torch.cuda.current_device()).multi_processor_count
+        return max(n - self.rows_blocks, 1) if self.row_owner else 0
+
     def _rows_call(self, stream, mode, part, out_region, **kw):
         import ctypes
 
         rows, h = part.shape
+        off = self._symm_offset(part)  # a row slice of partial_buffer(T, h): the result lands on the same rows
         d = self._lib.TpRowsDesc()
         d.peer_signal_pads = ctypes.cast(self._peer_sigs, ctypes.POINTER(ctypes.c_uint64))
-        d.multicast_in = self._mc + self._symm_offset(part) * 2
-        d.multicast_out = self._mcB[out_region]
+        d.multicast_in = self._mc + off * 2
+        d.multicast_out = self._mcB[out_region] + off * 2
         d.rank, d.world, d.num_blocks, d.mode = self.rank, self.nranks, self.rows_blocks, mode
         self._epoch += 1
         d.epoch = self._epoch
@@ -401,102 +433,125 @@ class SymmetricTPGroup(TorchDistGroup):
         for k, v in kw.items():
             setattr(d, k, v.data_ptr() if isinstance(v, torch.Tensor) else v)
         self._lib.check(self._lib.lib().fx_tp_rows_fused(stream.cuda_stream, ctypes.byref(d)), "fx_tp_rows_fused")
-        return self._bufB[out_region][: rows * h].view(rows, h)
+        return self._bufB[out_region][off: off + rows * h].view(rows, h)
 
-    def fused_fwd_ln(self, part, bias, residual_full, p, seed, offset, mask_in, gamma, beta, eps):
-        if not self._rows_ok(part):
-            return super().fused_fwd_ln(part, bias, residual_full, p, seed, offset, mask_in, gamma, beta, eps)
-        rows, h = part.shape
-        r0, r1 = self.own_rows(rows)
-        dev = part.device
-        x1 = torch.empty(r1 - r0, h, dtype=torch.bfloat16, device=dev)
-        mean = torch.empty(r1 - r0, dtype=torch.float32, device=dev)
-        rstd = torch.empty_like(mean)
-        st = torch.cuda.current_stream()
-        if self._b0_copy_done is not None:
-            st.wait_event(self._b0_copy_done)  # the saved copy of the previous B0 contents has been taken
-        ln = self._rows_call(st, self._lib.FX_ROWS_FWD_LN, part, 0, bias=bias, residual=residual_full, p=float(p),
-                             seed=int(seed), offset=int(offset), mask_in=mask_in, gamma=gamma, beta=beta, eps=float(eps),
-                             x_own=x1, mean=mean, rstd=rstd)
-        return x1, mean, rstd, ln
-
-    def keep_copy(self, t: torch.Tensor) -> torch.Tensor:
-        """Copy a gathered result out of its communication buffer on the group's stream (underneath whatever the
-        caller launches next); consumers wait through wait_kept()."""
-        if not any(t.data_ptr() == b_.data_ptr() for b_ in getattr(self, "_bufB", [])):
-            return t
-        keep = torch.empty_like(t)
+    def _on_comm_stream(self, fn, writes_b0=False):
+        """Run fn(stream) on the group's stream behind everything the caller's stream holds so far."""
         main = torch.cuda.current_stream()
         ready = torch.cuda.Event()
         ready.record(main)
         with torch.cuda.stream(self._comm_stream):
             self._comm_stream.wait_event(ready)
-            keep.copy_(t, non_blocking=True)
-            done = torch.cuda.Event()
-            done.record(self._comm_stream)
-        self._b0_copy_done = done
-        keep._fx_ready = done
-        return keep
-
-    def fused_fwd_out(self, part, bias, residual_own, p, seed, offset, mask_in):
-        if not self._rows_ok(part):
-            return super().fused_fwd_out(part, bias, residual_own, p, seed, offset, mask_in)
-        out = self._rows_call(torch.cuda.current_stream(), self._lib.FX_ROWS_FWD_OUT, part, 1, bias=bias,
-                              residual=residual_own, p=float(p), seed=int(seed), offset=int(offset), mask_in=mask_in)
-        return out.clone()  # the caller owns its result; B1 is rewritten by the next call
-
-    def _on_comm_stream(self, fn):
-        main = torch.cuda.current_stream()
-        ready = torch.cuda.Event()
-        ready.record(main)
-        with torch.cuda.stream(self._comm_stream):
-            self._comm_stream.wait_event(ready)
+            if writes_b0:  # copies still being taken out of B0 (keep_copy) go first
+                for ev in self._b0_copies:
+                    self._comm_stream.wait_event(ev)
+                self._b0_copies = []
             res = fn(self._comm_stream)
             done = torch.cuda.Event()
             done.record(self._comm_stream)
-        return res, done
+        return ("rows", res, done)
 
-    def fused_bwd_ln_bdr_start(self, part, x_own, mean_own, rstd_own, gamma, dres_full, p, seed, offset, mask_in, acc):
+    @staticmethod
+    def _is_handle(handle) -> bool:
+        return isinstance(handle, tuple) and len(handle) == 3 and isinstance(handle[0], str) and handle[0] == "rows"
+
+    def fwd_ln_start(self, part, bias, residual, p, seed, offset, mask_in, gamma, beta, eps, drop_off=0):
+        if not self._rows_ok(part):
+            return super().fwd_ln_start(part, bias, residual, p, seed, offset, mask_in, gamma, beta, eps, drop_off)
+        rows, h = part.shape
+        r0, r1 = self.own_rows(rows)
+        x1 = torch.empty(r1 - r0, h, dtype=torch.bfloat16, device=part.device)  # allocated on the caller's stream
+        mean = torch.empty(r1 - r0, dtype=torch.float32, device=part.device)
+        rstd = torch.empty_like(mean)
+        return self._on_comm_stream(lambda st: (x1, mean, rstd, self._rows_call(
+            st, self._lib.FX_ROWS_FWD_LN, part, 0, bias=bias, residual=residual, p=float(p), seed=int(seed),
+            offset=int(offset), dropout_elem_offset=int(drop_off), mask_in=mask_in, gamma=gamma, beta=beta,
+            eps=float(eps), x_own=x1, mean=mean, rstd=rstd)), writes_b0=True)
+
+    def fwd_ln_finish(self, handle):
+        if not self._is_handle(handle):
+            return super().fwd_ln_finish(handle)
+        torch.cuda.current_stream().wait_event(handle[2])
+        return handle[1]
+
+    def keep_copy(self, t: torch.Tensor, dst: torch.Tensor) -> None:
+        """The copy runs on a third stream, underneath whatever the caller launches next; the next kernel that
+        rewrites B0 waits for it, readers of dst go through wait_kept()."""
+        if not self.row_owner or self._symm_offset_in(t, self._bufB[0]) is None:
+            return super().keep_copy(t, dst)
+        ready = torch.cuda.Event()
+        ready.record(torch.cuda.current_stream())
+        with torch.cuda.stream(self._copy_stream):
+            self._copy_stream.wait_event(ready)
+            dst.copy_(t, non_blocking=True)
+            done = torch.cuda.Event()
+            done.record(self._copy_stream)
+        self._b0_copies.append(done)
+        self._kept[dst.data_ptr()] = done
+
+    def wait_kept(self, t: torch.Tensor) -> torch.Tensor:
+        ev = self._kept.pop(t.data_ptr(), None) if self.row_owner else None
+        if ev is not None:
+            torch.cuda.current_stream().wait_event(ev)
+        return t
+
+    def fwd_out_start(self, part, bias, residual_own, p, seed, offset, mask_in, drop_off=0):
+        if not self._rows_ok(part):
+            return super().fwd_out_start(part, bias, residual_own, p, seed, offset, mask_in, drop_off)
+        return self._on_comm_stream(lambda st: self._rows_call(
+            st, self._lib.FX_ROWS_FWD_OUT, part, 1, bias=bias, residual=residual_own, p=float(p), seed=int(seed),
+            offset=int(offset), dropout_elem_offset=int(drop_off), mask_in=mask_in))
+
+    def fwd_out_finish(self, handle, out):
+        if not self._is_handle(handle):
+            return super().fwd_out_finish(handle, out)
+        torch.cuda.current_stream().wait_event(handle[2])
+        out.copy_(handle[1])  # the caller owns its result; B1 is rewritten by a later call
+
+    def bwd_ln_bdr_start(self, part, x_own, mean_own, rstd_own, gamma, dres, p, seed, offset, mask_in, acc,
+                         drop_off=0, accumulate=False):
         if not self._rows_ok(part) or acc.data_ptr() != self._bufC.data_ptr():
-            return super().fused_bwd_ln_bdr_start(part, x_own, mean_own, rstd_own, gamma, dres_full, p, seed, offset,
-                                                  mask_in, acc)
+            return super().bwd_ln_bdr_start(part, x_own, mean_own, rstd_own, gamma, dres, p, seed, offset, mask_in, acc,
+                                            drop_off, accumulate)
         d_x1 = torch.empty_like(x_own)  # allocated on the caller's stream
-        d_ao, done = self._on_comm_stream(lambda st: self._rows_call(
-            st, self._lib.FX_ROWS_BWD_LN_BDR, part, 0, p=float(p), seed=int(seed), offset=int(offset), mask_in=mask_in,
-            gamma=gamma, x_own=x_own, mean=mean_own, rstd=rstd_own, dres=dres_full, dx_own=d_x1, acc=acc[0:3]))
-        return ("rows", (d_x1, d_ao), done)
+        return self._on_comm_stream(lambda st: (d_x1, self._rows_call(
+            st, self._lib.FX_ROWS_BWD_LN_BDR, part, 0, p=float(p), seed=int(seed), offset=int(offset),
+            dropout_elem_offset=int(drop_off), mask_in=mask_in, gamma=gamma, x_own=x_own, mean=mean_own, rstd=rstd_own,
+            dres=dres, dx_own=d_x1, acc=acc[0:3], acc_accumulate=int(accumulate))), writes_b0=True)
 
-    def fused_bwd_ln_bdr_finish(self, handle):
-        if isinstance(handle, tuple) and len(handle) == 3 and handle[0] == "rows":
-            torch.cuda.current_stream().wait_event(handle[2])
-            return handle[1]
-        return handle
+    def bwd_ln_bdr_finish(self, handle):
+        if not self._is_handle(handle):
+            return super().bwd_ln_bdr_finish(handle)
+        torch.cuda.current_stream().wait_event(handle[2])
+        return handle[1]
 
-    def fused_bwd_ln_start(self, part, x_full, mean_full, rstd_full, gamma, dres_own, acc):
+    def bwd_ln_start(self, part, x, mean, rstd, gamma, dres_own, acc, accumulate=False, last=True):
         if not self._rows_ok(part) or acc.data_ptr() != self._bufC.data_ptr():
-            return super().fused_bwd_ln_start(part, x_full, mean_full, rstd_full, gamma, dres_own, acc)
-        def run(st):
-            dx_ = self._rows_call(st, self._lib.FX_ROWS_BWD_LN, part, 1, gamma=gamma, x_full=x_full, mean=mean_full,
-                                  rstd=rstd_full, dres=dres_own, acc=acc[3:5])
-            with torch.cuda.stream(st):
-                return dx_, self.all_reduce_acc(acc)  # every partial sum is in: the small allreduce rides along
+            return super().bwd_ln_start(part, x, mean, rstd, gamma, dres_own, acc, accumulate, last)
 
-        (dx, tot), done = self._on_comm_stream(run)
-        return ("rows", (dx, tot), done)
+        # last: every partial sum is in once this kernel's rows are done, so the sum of acc over the ranks is its tail
+        tot = torch.empty_like(acc) if last else None  # allocated on the caller's stream
+        extra = dict(multicast_sum=self._mcC, sum_out=tot, sum_n=acc.numel()) if last else {}
+        return self._on_comm_stream(lambda st: (self._rows_call(
+            st, self._lib.FX_ROWS_BWD_LN, part, 1, gamma=gamma, x_full=x, mean=mean, rstd=rstd, dres=dres_own,
+            acc=acc[3:5], acc_accumulate=int(accumulate), **extra), tot))
 
-    def fused_bwd_ln_finish(self, handle):
-        if isinstance(handle, tuple) and len(handle) == 3 and handle[0] == "rows":
-            torch.cuda.current_stream().wait_event(handle[2])
-            dx, tot = handle[1]
-            tot.record_stream(torch.cuda.current_stream())  # allocated on the group's stream, used on the caller's
-            return dx.clone(), tot  # the caller owns dx; B1 is rewritten by the next call
-        return handle
+    def bwd_ln_finish(self, handle, out):
+        if not self._is_handle(handle):
+            return super().bwd_ln_finish(handle, out)
+        main = torch.cuda.current_stream()
+        main.wait_event(handle[2])
+        dx, tot = handle[1]
+        out.copy_(dx)  # the caller owns dx; B1 is rewritten by a later call
+        return tot
 
-    def free_sms(self) -> int:
-        import torch as _t
-
-        n = _t.cuda.get_device_properties(_t.cuda.current_device()).multi_processor_count
-        return max(n - self.rows_blocks, 1) if self.row_owner else 0
+    def _symm_offset_in(self, t: torch.Tensor, buf: torch.Tensor):
+        if t.dtype != buf.dtype or not t.is_contiguous():
+            return None
+        off = t.data_ptr() - buf.data_ptr()
+        if off < 0 or off // 2 + t.numel() > buf.numel():
+            return None
+        return off // 2
 
     def _symm_offset(self, t: torch.Tensor):
         """Element offset of t inside the symmetric buffer, or None if t is not a contiguous view of it."""

@@ -129,78 +129,146 @@ def _row_owner_path(T: int, h: int, M: LayerMeta, group) -> bool:
     return bool(group.nranks > 1 and getattr(group, "row_owner", False) and M.normalize_before and T % group.nranks == 0)
 
 
+def _chunks(b: int, group) -> int:
+    nc = int(getattr(group, "pipeline_chunks", 1))
+    return nc if nc > 1 and b % nc == 0 else 1
+
+
+def _batch_slice(t, b: int, c: int, bc: int):
+    """Sequences [c*bc, (c+1)*bc) of a per-batch tensor (lse [b, nh, s]; the keep bits: a flat byte buffer of b equal
+    parts from the kernel, or a list of per-chunk buffers)."""
+    if t is None:
+        return None
+    if isinstance(t, (list, tuple)):
+        return t[c]
+    m = t.reshape(b, -1)[c * bc:(c + 1) * bc]
+    return m.reshape((bc,) + tuple(t.shape[1:])) if t.dim() > 1 else m.reshape(-1)
+
+
+def _rows_cat(parts):
+    """Row chunks back to back in memory (views of one communication buffer) as one tensor; else concatenated."""
+    if len(parts) == 1:
+        return parts[0]
+    p0 = parts[0]
+    step = p0.numel() * p0.element_size()
+    if all(t.is_contiguous() and t.data_ptr() == p0.data_ptr() + i * step and t.shape == p0.shape for i, t in enumerate(parts)):
+        return p0.as_strided((p0.shape[0] * len(parts), p0.shape[1]), (p0.shape[1], 1))
+    return torch.cat(parts, dim=0)
+
+
 def decoder_layer_fwd_rows(x: torch.Tensor, P: LayerParams, M: LayerMeta, group):
     """decoder_layer_fwd for mp degree > 1 with the row-wise work behind each allreduce done by the rank that owns the
-    rows (group.fused_*; csrc/comm_rows.cu): dropout1 + residual + LayerNorm2 and dropout2 + residual run on T/n rows
-    per rank inside the collective, x1 and its statistics exist only as this rank's rows. Same tensors, same
-    (seed, offset) draws — the masks are indexed by position in the whole [T, h] tensor — as the replicated order."""
+    rows (group.fwd_ln_* / fwd_out_*; csrc/comm_rows.cu): dropout1 + residual + LayerNorm2 and dropout2 + residual run
+    on T/n rows per rank inside the collective, x1 and its statistics exist only as this rank's rows. The batch goes
+    through in group.pipeline_chunks chunks, so that one chunk's collective (on the group's stream) runs underneath
+    the other chunk's GEMMs and attention. Same tensors, same (seed, offset) draws — the masks are indexed by position
+    in the whole tensor / batch — as the replicated order."""
     b, s, h = x.shape
     T = b * s
+    nc = _chunks(b, group)
+    bc, Tc = b // nc, (b // nc) * s
+    dev, dt = x.device, x.dtype
     x2 = x.reshape(T, h)
     scale = M.hd ** -0.5
     ln1, mean1, rstd1 = ops.layernorm_fwd(x2, P.norm1_w, P.norm1_b, M.eps)          # :534 (replicated: HBM is cheaper than NVLink)
-    qkv = ops.gemm(ln1, P.qkv_w, epilogue=FX_EPI_BIAS, bias=P.qkv_b)                # :166
-    ctx, lse, attn_mask = ops.attn_causal_fwd(qkv.view(b, s, -1), M.nh_local, M.hd, scale, M.p_attn, *M.rng_attn)
-    ctx2 = ctx.view(T, -1)
-    part = ops.gemm(ctx2, P.out_w, out=group.partial_buffer(T, h, x.device))        # :340 local matmul
-    # _mp_allreduce + bias, dropout1 + residual (:546-547), norm2 (:554)
-    x1_own, mean2, rstd2, ln2 = group.fused_fwd_ln(part, P.out_b, x2, M.p_hidden1, *M.rng_h1, M.mask_h1,
-                                                   P.norm2_w, P.norm2_b, M.eps)
-    ln2_keep = group.keep_copy(ln2)  # linear1's weight gradient needs it in backward
-    z = torch.empty(T, P.lin1_w.shape[1], dtype=x.dtype, device=x.device)
-    act = ops.gemm(ln2, P.lin1_w, epilogue=FX_EPI_BIAS_GELU, bias=P.lin1_b, aux=z)  # :558-559
-    part = ops.gemm(act, P.lin2_w, out=group.partial_buffer(T, h, x.device))        # :558 local matmul
-    out = group.fused_fwd_out(part, P.lin2_b, x1_own, M.p_hidden2, *M.rng_h2, M.mask_h2)  # :556-561
-    saved = dict(x=x2, ln1=ln1, mean1=mean1, rstd1=rstd1, qkv=qkv, ctx=ctx2, lse=lse, attn_mask=attn_mask, x1_own=x1_own,
-                 ln2=ln2_keep, mean2=mean2, rstd2=rstd2, z=z, act=act, shape=(b, s, h), rows=True)
+    A = group.partial_buffer(T, h, dev)
+    qkv = torch.empty(T, P.qkv_w.shape[1], dtype=dt, device=dev)
+    ctx = torch.empty(T, P.out_w.shape[0], dtype=dt, device=dev)
+    lse = torch.empty(b, M.nh_local, s, dtype=mean1.dtype, device=dev)
+    z = torch.empty(T, P.lin1_w.shape[1], dtype=dt, device=dev)
+    act = torch.empty_like(z)
+    ln2_keep = torch.empty(T, h, dtype=dt, device=dev)
+    out = torch.empty(T, h, dtype=dt, device=dev)
+    rows = [slice(c * Tc, (c + 1) * Tc) for c in range(nc)]
+    m1 = [None if M.mask_h1 is None else M.mask_h1.reshape(T, h)[r] for r in rows]
+    m2 = [None if M.mask_h2 is None else M.mask_h2.reshape(T, h)[r] for r in rows]
+    masks, pend = [], []
+    with ops.sm_budget(group.free_sms() if nc > 1 else 0):  # from the first collective on, its SMs are taken
+        for c, r in enumerate(rows):
+            ops.gemm(ln1[r], P.qkv_w, out=qkv[r], epilogue=FX_EPI_BIAS, bias=P.qkv_b)   # :166
+            _, _, mk = ops.attn_causal_fwd(qkv[r].view(bc, s, -1), M.nh_local, M.hd, scale, M.p_attn, *M.rng_attn,
+                                           batch0=c * bc, out=ctx[r].view(bc, s, -1), lse=lse[c * bc:(c + 1) * bc])
+            masks.append(mk)
+            ops.gemm(ctx[r], P.out_w, out=A[r])                                      # :340 local matmul
+            # _mp_allreduce + bias, dropout1 + residual (:546-547), norm2 (:554)
+            pend.append(group.fwd_ln_start(A[r], P.out_b, x2[r], M.p_hidden1, *M.rng_h1, m1[c], P.norm2_w, P.norm2_b,
+                                           M.eps, drop_off=c * Tc * h))
+        x1_own, mean2, rstd2, pend2 = [], [], [], []
+        for c, r in enumerate(rows):
+            x1_c, mean_c, rstd_c, ln2_c = group.fwd_ln_finish(pend[c])
+            x1_own.append(x1_c), mean2.append(mean_c), rstd2.append(rstd_c)
+            group.keep_copy(ln2_c, ln2_keep[r])  # linear1's weight gradient needs it in backward
+            ops.gemm(ln2_c, P.lin1_w, out=act[r], epilogue=FX_EPI_BIAS_GELU, bias=P.lin1_b, aux=z[r])  # :558-559
+            ops.gemm(act[r], P.lin2_w, out=A[r])                                     # :558 local matmul
+            pend2.append(group.fwd_out_start(A[r], P.lin2_b, x1_c, M.p_hidden2, *M.rng_h2, m2[c],
+                                             drop_off=c * Tc * h))                   # :556-561
+        for c, r in enumerate(rows):
+            group.fwd_out_finish(pend2[c], out[r])
+    saved = dict(x=x2, ln1=ln1, mean1=mean1, rstd1=rstd1, qkv=qkv, ctx=ctx, lse=lse,
+                 attn_mask=(masks if nc > 1 else masks[0]), x1_own=x1_own, ln2=ln2_keep, mean2=mean2, rstd2=rstd2, z=z,
+                 act=act, shape=(b, s, h), rows=True, chunks=nc)
     return out.view(b, s, h), saved
 
 
-def _wait_kept(t: torch.Tensor) -> torch.Tensor:
-    ev = getattr(t, "_fx_ready", None)
-    if ev is not None:
-        torch.cuda.current_stream().wait_event(ev)
-    return t
-
-
 def decoder_layer_bwd_rows(dout: torch.Tensor, saved: dict, P: LayerParams, M: LayerMeta, group):
-    """Adjoint of decoder_layer_fwd_rows. The two allreduces of dX (backward of _c_identity) carry LayerNorm backward,
-    the skip-path adds and dropout1's backward on the owner's rows, and run on the group's stream underneath the
-    weight-gradient GEMMs; gradients of parameters whose kernels saw only this rank's rows (LayerNorm weight / bias,
-    out_proj / linear2 bias) are summed over the ranks in one small fp32 allreduce at the end."""
+    """Adjoint of decoder_layer_fwd_rows, chunk by chunk. The two allreduces of dX (backward of _c_identity) carry
+    LayerNorm backward, the skip-path adds and dropout1's backward on the owner's rows, and run on the group's stream
+    underneath the other chunk's kernels and the (whole-batch) weight-gradient GEMMs; gradients of parameters whose
+    kernels saw only this rank's rows (LayerNorm weight / bias, out_proj / linear2 bias) are summed over the ranks in
+    one small fp32 allreduce that rides behind the last collective."""
     b, s, h = saved["shape"]
     T = b * s
+    nc = saved["chunks"]
+    bc, Tc = b // nc, (b // nc) * s
     d = dout.reshape(T, h)
+    dev, dt = d.device, d.dtype
     scale = M.hd ** -0.5
     g = {}
     r0, r1 = group.own_rows(T)
-    acc = group.acc_buffer(h, d.device, P.norm1_w.dtype)  # fp32 [6, h]: dgamma2 | dbeta2 | d out_b | dgamma1 | dbeta1 | d lin2_b
+    rows = [slice(c * Tc, (c + 1) * Tc) for c in range(nc)]
+    m1 = [None if M.mask_h1 is None else M.mask_h1.reshape(T, h)[r] for r in rows]
+    A = group.partial_buffer(T, h, dev)
+    acc = group.acc_buffer(h, dev, P.norm1_w.dtype)  # fp32 [6, h]: dgamma2 | dbeta2 | d out_b | dgamma1 | dbeta1 | d lin2_b
 
     d_y2 = ops.bias_dropout_residual_bwd(d, M.p_hidden2, *M.rng_h2, mask_in=M.mask_h2)   # replicated: the GEMMs need all rows
-    d_z = ops.gemm(d_y2, P.lin2_w, trans_b=True, epilogue=FX_EPI_DGELU, aux=saved["z"])
-    part = ops.gemm(d_z, P.lin1_w, trans_b=True, out=group.partial_buffer(T, h, d.device))
-    pending = group.fused_bwd_ln_bdr_start(part, saved["x1_own"], saved["mean2"], saved["rstd2"], P.norm2_w, d,
-                                           M.p_hidden1, *M.rng_h1, M.mask_h1, acc)
-    with ops.sm_budget(group.free_sms()):  # the collective holds its SMs until every rank is through
-        ops.colsum(d_y2[r0:r1], out=acc[5])                                          # own rows; summed over ranks below
+    ops.colsum(d_y2[r0:r1], out=acc[5])                                              # own rows; summed over ranks at the end
+    d_z = torch.empty_like(saved["z"])
+    d_qkv = torch.empty_like(saved["qkv"])
+    dx = torch.empty(T, h, dtype=dt, device=dev)
+    with ops.sm_budget(group.free_sms()):  # a collective holds its SMs until every rank is through
+        pend = []
+        for c, r in enumerate(rows):
+            ops.gemm(d_y2[r], P.lin2_w, trans_b=True, out=d_z[r], epilogue=FX_EPI_DGELU, aux=saved["z"][r])
+            ops.gemm(d_z[r], P.lin1_w, trans_b=True, out=A[r])
+            pend.append(group.bwd_ln_bdr_start(A[r], saved["x1_own"][c], saved["mean2"][c], saved["rstd2"][c], P.norm2_w,
+                                               d[r], M.p_hidden1, *M.rng_h1, m1[c], acc, drop_off=c * Tc * h,
+                                               accumulate=c > 0))
         g["lin2_w"] = ops.gemm(saved["act"], d_y2, trans_a=True, split_k=True)
         del d_y2
         g["lin1_b"] = ops.colsum(d_z)
-        g["lin1_w"] = ops.gemm(_wait_kept(saved["ln2"]), d_z, trans_a=True, split_k=True)
+        g["lin1_w"] = ops.gemm(group.wait_kept(saved["ln2"]), d_z, trans_a=True, split_k=True)
         del d_z
-    d_x1_own, d_ao = group.fused_bwd_ln_bdr_finish(pending)
-    d_ctx = ops.gemm(d_ao, P.out_w, trans_b=True)
-    d_qkv = ops.attn_causal_bwd(d_ctx.view(b, s, -1), saved["qkv"].view(b, s, -1), saved["ctx"].view(b, s, -1),
-                                saved["lse"], saved["attn_mask"], M.nh_local, M.hd, scale, M.p_attn).view(T, -1)
-    del d_ctx
-    part = ops.gemm(d_qkv, P.qkv_w, trans_b=True, out=group.partial_buffer(T, h, d.device))
-    pending = group.fused_bwd_ln_start(part, saved["x"], saved["mean1"], saved["rstd1"], P.norm1_w, d_x1_own, acc)
-    with ops.sm_budget(group.free_sms()):
-        g["out_w"] = ops.gemm(saved["ctx"], d_ao, trans_a=True, split_k=True)
+        d_ao, pend2 = [], []
+        for c, r in enumerate(rows):
+            d_x1_c, d_ao_c = group.bwd_ln_bdr_finish(pend[c])
+            d_ao.append(d_ao_c)
+            d_ctx = ops.gemm(d_ao_c, P.out_w, trans_b=True)
+            ops.attn_causal_bwd(d_ctx.view(bc, s, -1), saved["qkv"][r].view(bc, s, -1), saved["ctx"][r].view(bc, s, -1),
+                                _batch_slice(saved["lse"], b, c, bc), _batch_slice(saved["attn_mask"], b, c, bc),
+                                M.nh_local, M.hd, scale, M.p_attn, dqkv=d_qkv[r].view(bc, s, -1))
+            del d_ctx
+            ops.gemm(d_qkv[r], P.qkv_w, trans_b=True, out=A[r])
+            pend2.append(group.bwd_ln_start(A[r], saved["x"][r], saved["mean1"][r], saved["rstd1"][r], P.norm1_w, d_x1_c,
+                                            acc, accumulate=c > 0, last=c == nc - 1))
+        g["out_w"] = ops.gemm(saved["ctx"], _rows_cat(d_ao), trans_a=True, split_k=True)
+        del d_ao
         g["qkv_b"] = ops.colsum(d_qkv)
         g["qkv_w"] = ops.gemm(saved["ln1"], d_qkv, trans_a=True, split_k=True)
         del d_qkv
-    dx, tot = group.fused_bwd_ln_finish(pending)
+        tot = None
+        for c, r in enumerate(rows):
+            t_ = group.bwd_ln_finish(pend2[c], dx[r])
+            tot = t_ if t_ is not None else tot
     g["norm2_w"], g["norm2_b"], g["norm1_w"], g["norm1_b"] = tot[0], tot[1], tot[3], tot[4]
     g["out_b"], g["lin2_b"] = tot[2].to(P.out_b.dtype), tot[5].to(P.lin2_b.dtype)
     return dx.view(b, s, h), g

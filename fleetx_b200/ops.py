@@ -204,28 +204,47 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, trans_a: bool = False, trans_b: bo
 
 # ------------------------------------------------------------------------------- attention
 def attn_causal_fwd(qkv: torch.Tensor, nh: int, hd: int, scale: float, p_drop: float = 0.0,
-                    seed: int = 0, offset: int = 0):
+                    seed: int = 0, offset: int = 0, batch0: int = 0, out=None, lse=None, mask=None):
     """qkv: bf16 [b, s, nh*3*hd] (packed per head q|k|v). Returns (out [b, s, nh*hd], lse [b, nh, s],
-    mask): mask holds the dropout keep bits (None when p_drop == 0) and goes to attn_causal_bwd."""
+    mask): mask holds the dropout keep bits (None when p_drop == 0) and goes to attn_causal_bwd. batch0: these are
+    sequences [batch0, batch0 + b) of a larger batch (same keep bits as the whole-batch call)."""
     _need(qkv, torch.bfloat16, "qkv")
     b, s = qkv.shape[0], qkv.shape[1]
     if qkv.numel() != b * s * nh * 3 * hd:
         raise _lib.FleetXError("attn_causal_fwd: qkv shape does not match (nh, hd)")
-    out = torch.empty(b, s, nh * hd, dtype=torch.bfloat16, device=qkv.device)
-    lse = torch.empty(b, nh, s, dtype=torch.float32, device=qkv.device)
-    mask = None
+    if out is None:
+        out = torch.empty(b, s, nh * hd, dtype=torch.bfloat16, device=qkv.device)
+    else:  # caller-provided destinations (the batch part of larger tensors)
+        _need(out, torch.bfloat16, "out")
+        if out.numel() != b * s * nh * hd:
+            raise _lib.FleetXError("attn_causal_fwd: bad out tensor")
+    if lse is None:
+        lse = torch.empty(b, nh, s, dtype=torch.float32, device=qkv.device)
+    else:
+        _need(lse, torch.float32, "lse")
+        if lse.numel() != b * nh * s:
+            raise _lib.FleetXError("attn_causal_fwd: bad lse tensor")
     if p_drop > 0:
-        mask = torch.empty(_lib.lib().fx_attn_dropout_mask_bytes(b, s, nh), dtype=torch.uint8, device=qkv.device)
-    check(_lib.lib().fx_attn_causal_fwd(_stream(), _p(qkv), _p(out), _p(lse), _p(mask), b, s, nh, hd, float(scale),
-                                        float(p_drop), int(seed), int(offset)), "fx_attn_causal_fwd")
+        nbytes = _lib.lib().fx_attn_dropout_mask_bytes(b, s, nh)
+        if mask is None:
+            mask = torch.empty(nbytes, dtype=torch.uint8, device=qkv.device)
+        elif _need(mask, torch.uint8, "mask").numel() != nbytes:
+            raise _lib.FleetXError("attn_causal_fwd: bad mask tensor")
+    else:
+        mask = None
+    check(_lib.lib().fx_attn_causal_fwd_at(_stream(), _p(qkv), _p(out), _p(lse), _p(mask), b, s, nh, hd, float(scale),
+                                           float(p_drop), int(seed), int(offset), int(batch0)), "fx_attn_causal_fwd")
     return out, lse, mask
 
 
-def attn_causal_bwd(dout, qkv, out, lse, mask, nh: int, hd: int, scale: float, p_drop: float = 0.0):
+def attn_causal_bwd(dout, qkv, out, lse, mask, nh: int, hd: int, scale: float, p_drop: float = 0.0, dqkv=None):
     _need(dout, torch.bfloat16, "dout"), _need(qkv, torch.bfloat16, "qkv"), _need(out, torch.bfloat16, "out")
     _need(lse, torch.float32, "lse")
     b, s = qkv.shape[0], qkv.shape[1]
-    dqkv = torch.empty_like(qkv)
+    if dqkv is None:
+        dqkv = torch.empty_like(qkv)
+    elif _need(dqkv, torch.bfloat16, "dqkv").numel() != qkv.numel():
+        raise _lib.FleetXError("attn_causal_bwd: bad dqkv tensor")
     ws = _workspace(_lib.lib().fx_attn_causal_bwd_workspace_bytes(b, s, nh, hd), qkv.device)
     check(_lib.lib().fx_attn_causal_bwd(_stream(), _p(dout), _p(qkv), _p(out), _p(lse), _p(mask), _p(dqkv), _p(ws), b,
                                         s, nh, hd, float(scale), float(p_drop)), "fx_attn_causal_bwd")

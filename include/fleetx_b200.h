@@ -142,6 +142,11 @@ int fx_set_sm_budget(int ctas);
 size_t fx_attn_dropout_mask_bytes(int b, int s, int nh);
 int fx_attn_causal_fwd(void* stream, const void* qkv, void* out, float* lse, void* dropout_mask, int b,
                        int s, int nh, int hd, float scale, float p_drop, uint64_t seed, uint64_t offset);
+/* The same call for sequences [batch0, batch0 + b) of a larger batch (the layer pipelines batch halves through
+ * its collectives): qkv / out / lse / dropout_mask point at this part, and the keep bits are those the whole-batch
+ * call draws for these sequences. */
+int fx_attn_causal_fwd_at(void* stream, const void* qkv, void* out, float* lse, void* dropout_mask, int b, int s,
+                          int nh, int hd, float scale, float p_drop, uint64_t seed, uint64_t offset, int batch0);
 size_t fx_attn_causal_bwd_workspace_bytes(int b, int s, int nh, int hd);
 /* dqkv bf16, same packed layout as qkv, fully overwritten. dropout_mask: what the forward wrote.
  * hd == 64 runs ONE kernel that produces dK, dV and adds the dQ contribution of each KV tile into an
@@ -218,7 +223,7 @@ int fx_tp_reduce_scatter_bdr(void* stream, const uint64_t* peer_signal_pads, uin
  *   FX_ROWS_BWD_LN      LayerNorm'(sum; x_full[rows,h], mean, rstd [rows], gamma) + dres[own,h] -> multicast_out;
  *                       acc[2,h] += dgamma | dbeta over the own rows
  * Dropout masks are indexed by position in the whole [rows, h] tensor (the 'global_seed' stream: identical on all
- * ranks). acc is zeroed by the call. No counterpart for the sharing of rows exists in the reference: there every
+ * ranks). No counterpart for the sharing of rows exists in the reference: there every
  * rank repeats the row-wise ops on the replicated tensor; the results are the same tensors. */
 enum { FX_ROWS_FWD_LN = 0, FX_ROWS_FWD_OUT = 1, FX_ROWS_BWD_LN_BDR = 2, FX_ROWS_BWD_LN = 3 };
 typedef struct fx_tp_rows_desc {
@@ -232,6 +237,8 @@ typedef struct fx_tp_rows_desc {
   const void* residual;             /* bf16, see mode                                                      */
   float p;                          /* dropout probability (FWD modes, BWD_LN_BDR)                         */
   uint64_t seed, offset;
+  uint64_t dropout_elem_offset;     /* where this call's [rows, h] starts inside the tensor the mask is defined
+                                       on (row slices of a larger [T, h]: the layer pipelines batch halves)  */
   const uint8_t* mask_in;           /* optional injected keep flags, uint8 [rows, h] (test hook)           */
   const float* gamma;               /* fp32 [h]                                                            */
   const float* beta;                /* fp32 [h] (FWD_LN)                                                   */
@@ -243,6 +250,11 @@ typedef struct fx_tp_rows_desc {
   const void* dres;                 /* bf16, see mode                                                      */
   void* dx_own;                     /* bf16 [own, h]: BWD_LN_BDR out                                       */
   float* acc;                       /* fp32 [3, h] / [2, h] (BWD modes)                                    */
+  int acc_accumulate;               /* 0: the call zeroes acc first; 1: it adds to what is there (a later
+                                       batch chunk of the same backward pass)                               */
+  uint64_t multicast_sum;           /* BWD_LN, optional (sum_out != NULL): once every rank's rows are done, the  */
+  float* sum_out;                   /* fp32 vector behind multicast_sum (sum_n floats in a symmetric buffer: the */
+  int sum_n;                        /* ranks' acc) is summed over the ranks into sum_out, as fx_tp_allreduce_f32  */
 } fx_tp_rows_desc;
 int fx_tp_rows_max_h(void);
 int fx_tp_rows_fused(void* stream, const fx_tp_rows_desc* desc);

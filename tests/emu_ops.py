@@ -142,7 +142,8 @@ def _unpack(qkv, nh, hd):
     return t[0], t[1], t[2]
 
 
-def attn_causal_fwd(qkv, nh, hd, scale, p_drop=0.0, seed=0, offset=0):
+def attn_causal_fwd(qkv, nh, hd, scale, p_drop=0.0, seed=0, offset=0, batch0=0, out=None, lse=None, mask=None):
+    dst = (out, lse, mask)
     CALLS.append("attn_causal_fwd")
     b, s = qkv.shape[0], qkv.shape[1]
     q, k, v = _unpack(qkv, nh, hd)
@@ -152,16 +153,29 @@ def attn_causal_fwd(qkv, nh, hd, scale, p_drop=0.0, seed=0, offset=0):
     pm = torch.exp(sc - lse[..., None])
     keep = None
     if p_drop > 0:
-        if ATTN_KEEP_QUEUE:
-            keep = ATTN_KEEP_QUEUE.pop(0).bool()
+        if ATTN_KEEP_QUEUE:  # a whole-batch mask: calls on parts of the batch take their sequences, the last one pops it
+            full = ATTN_KEEP_QUEUE[0]
+            keep = full[batch0:batch0 + b].bool()
+            if batch0 + b >= full.shape[0]:
+                ATTN_KEEP_QUEUE.pop(0)
         else:
-            keep = torch.from_numpy(np.asarray(philox.attn_dropout_mask(seed, offset, b, nh, s, p_drop))).bool()
+            keep = torch.from_numpy(np.asarray(philox.attn_dropout_mask(seed, offset, batch0 + b, nh, s, p_drop)))[batch0:].bool()
         pm = pm * keep.to(pm.dtype) / (1.0 - p_drop)
     out = (pm @ v).permute(0, 2, 1, 3).reshape(b, s, nh * hd)
+    if dst[0] is not None:
+        dst[0].copy_(out.view(dst[0].shape))
+        out = dst[0]
+    if dst[1] is not None:
+        dst[1].copy_(lse)
+        lse = dst[1]
+    if dst[2] is not None and keep is not None:
+        dst[2].copy_(keep.view(dst[2].shape))
+        keep = dst[2]
     return out, lse, keep
 
 
-def attn_causal_bwd(dout, qkv, out, lse, mask, nh, hd, scale, p_drop=0.0):
+def attn_causal_bwd(dout, qkv, out, lse, mask, nh, hd, scale, p_drop=0.0, dqkv=None):
+    dst = dqkv
     CALLS.append("attn_causal_bwd")
     b, s = qkv.shape[0], qkv.shape[1]
     q, k, v = _unpack(qkv, nh, hd)
@@ -178,11 +192,14 @@ def attn_causal_bwd(dout, qkv, out, lse, mask, nh, hd, scale, p_drop=0.0):
     dq = ds @ k * scale
     dk = ds.transpose(-1, -2) @ q * scale
     dqkv = torch.stack([dq, dk, dv], dim=0).permute(1, 3, 2, 0, 4)  # [b, s, nh, 3, hd]
+    if dst is not None:
+        dst.copy_(dqkv.reshape(dst.shape))
+        return dst
     return dqkv.reshape(qkv.shape)
 
 
 NAMES = ("layernorm_fwd", "layernorm_bwd", "bias_dropout_residual_fwd", "bias_dropout_residual_bwd", "colsum", "gemm",
-         "attn_causal_fwd", "attn_causal_bwd")
+         "attn_causal_fwd", "attn_causal_bwd", "sm_budget")
 
 
 def install(monkeypatch):

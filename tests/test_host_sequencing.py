@@ -141,7 +141,7 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _worker(rank, world, port, name, ret, rows=False):
+def _worker(rank, world, port, name, ret, rows=0):
     import torch.distributed as dist
 
     os.environ["MASTER_ADDR"] = "127.0.0.1"
@@ -157,7 +157,8 @@ def _worker(rank, world, port, name, ret, rows=False):
         assert m["n"] == world
         P, M = params_and_meta(d, m, rank)
         group = _cpu_group(TorchDistGroup)()
-        group.row_owner = rows  # the row-owner order of the layer over the plumbing statement of its collectives
+        group.row_owner = bool(rows)  # the row-owner order of the layer over the plumbing statement of its collectives
+        group.pipeline_chunks = int(rows)  # ... in that many batch chunks
         if m["dropout"] > 0:
             emu_ops.ATTN_KEEP_QUEUE.append(d[f"mask.attn.{rank}"])
         x, dy = d["in.x"], d["in.dy"]
@@ -170,7 +171,7 @@ def _worker(rank, world, port, name, ret, rows=False):
             check(dx, cut(d["out.dx"]), "dx shard")
         else:
             y, saved = Fn.decoder_layer_fwd(x, P, M, group)
-            assert bool(saved.get("rows")) == rows
+            assert bool(saved.get("rows")) == bool(rows) and saved.get("chunks", 0) == (min(rows, x.shape[0]) if rows else 0)
             dx, g = Fn.decoder_layer_bwd(dy, saved, P, M, group)
             check(y, d["out.y"], "y")
             check(dx, d["out.dx"], "dx")
@@ -183,16 +184,18 @@ def _worker(rank, world, port, name, ret, rows=False):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("name,world,rows", [("ref_layer_tp2", 2, False), ("ref_layer_tp4", 4, False),
-                                             ("ref_layer_sp2", 2, False), ("ref_layer_sp4", 4, False),
-                                             ("ref_layer_tp2", 2, True), ("ref_layer_tp4", 4, True)])
+@pytest.mark.parametrize("name,world,rows", [("ref_layer_tp2", 2, 0), ("ref_layer_tp4", 4, 0),
+                                             ("ref_layer_sp2", 2, 0), ("ref_layer_sp4", 4, 0),
+                                             ("ref_layer_tp2", 2, 1), ("ref_layer_tp4", 4, 1),
+                                             ("ref_layer_tp2", 2, 2), ("ref_layer_tp4", 4, 2)])
 def test_tensor_and_sequence_parallel_sequencing_over_gloo(name, world, rows):
     """Each process runs ONE mp rank of the product's own forward / backward (allreduce after the row-parallel
     matmuls, allreduce of dX in front of the column-parallel ones; sequence parallel: all-gather / reduce-scatter,
     shard-local dropout, summed LayerNorm / bias gradients) and must land on the reference's numbers, which came
-    from n simulated ranks of hybrid_model.py / sequence_parallel_utils.py. rows = True: the row-owner order
+    from n simulated ranks of hybrid_model.py / sequence_parallel_utils.py. rows = 1 / 2: the row-owner order
     (functional.decoder_layer_fwd_rows / _bwd_rows: each rank does the row-wise work behind every allreduce on its
-    own T/n rows, gathered results, parameter-gradient partial sums summed at the end)."""
+    own rows, gathered results, parameter-gradient partial sums summed at the end) with the batch in that many
+    chunks."""
     ctx = mp.get_context("spawn")
     ret = ctx.Manager().dict()
     port = _free_port()
