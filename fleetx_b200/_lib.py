@@ -93,7 +93,8 @@ SIGNATURES = {
     "fx_tp_allreduce_f32": (_i, [_vp, _vp, _u64, _i, _i, C.c_uint32, _vp, _i]),
     "fx_attn_dropout_mask_bytes": (_sz, [_i, _i, _i]),
     "fx_attn_causal_fwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _f, _u64, _u64]),
-    "fx_attn_causal_fwd_at": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _f, _u64, _u64, _i]),
+    "fx_attn_causal_fwd_at": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _f, _u64, _u64, _i, _i]),
+    "fx_attn_dropout_mask": (_i, [_vp, _vp, _i, _i, _i, _f, _u64, _u64, _i]),
     "fx_attn_causal_bwd_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "fx_attn_causal_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _f]),
     "fx_embedding_fwd": (_i, [_vp, _vp, _vp, _vp, C.c_int64, C.c_int64, _vp, _vp, _vp, C.c_int64, _i, _i, _f, _u64, _u64]),

@@ -82,9 +82,10 @@ struct MaskParams {
   PhiloxKeys keys;
 };
 
-__global__ void __launch_bounds__(256)
+constexpr int MASK_THREADS = 512;  // one such block fits beside a resident GEMM CTA (no shared memory, 32 registers)
+__global__ void __launch_bounds__(MASK_THREADS)
 attn_dropout_mask_kernel(const MaskParams p) {
-  // CTA = 32 query rows (lane = row) of one (batch, head); its 8 warps walk the kv words 8 at a time up
+  // CTA = 32 query rows (lane = row) of one (batch, head); its 16 warps walk the kv words 16 at a time up
   // to the end of the diagonal 128-tile (tiles beyond it are never read: causal).
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int q = blockIdx.x * 32 + lane;
@@ -94,7 +95,7 @@ attn_dropout_mask_kernel(const MaskParams p) {
   const uint64_t s8 = static_cast<uint64_t>((p.s + 7) / 8);
   const uint64_t grp_row = ((p.bh0 + bh) * p.s + q) * s8;
   uint32_t* out_row = p.mask + (bh * p.s + q) * p.wpr;
-  for (int w = warp; w < n_words; w += 8) {
+  for (int w = warp; w < n_words; w += MASK_THREADS / 32) {
     uint32_t word = 0;
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
@@ -1139,12 +1140,34 @@ extern "C" size_t fx_attn_dropout_mask_bytes(int b, int s, int nh) {
 
 extern "C" int fx_attn_causal_fwd(void* stream, const void* qkv, void* out, float* lse, void* dropout_mask, int b,
                                   int s, int nh, int hd, float scale, float p_drop, uint64_t seed, uint64_t offset) {
-  return fx_attn_causal_fwd_at(stream, qkv, out, lse, dropout_mask, b, s, nh, hd, scale, p_drop, seed, offset, 0);
+  return fx_attn_causal_fwd_at(stream, qkv, out, lse, dropout_mask, b, s, nh, hd, scale, p_drop, seed, offset, 0, 0);
+}
+
+extern "C" int fx_attn_dropout_mask(void* stream, void* dropout_mask, int b, int s, int nh, float p_drop, uint64_t seed,
+                                    uint64_t offset, int batch0) {
+  using namespace fx;
+  FX_CHECK_ARG(b > 0 && s > 0 && nh > 0 && batch0 >= 0, "fx_attn_dropout_mask: empty input (b %d, s %d, nh %d)", b, s, nh);
+  FX_CHECK_ARG(nh <= 65535 && b * nh <= 65535, "fx_attn_dropout_mask: nh and b*nh must be <= 65535");
+  FX_CHECK_ARG(p_drop > 0.f && p_drop < 1.f, "fx_attn_dropout_mask: dropout p must be in (0,1) (got %f)", p_drop);
+  FX_CHECK_ARG(dropout_mask && (uintptr_t)dropout_mask % 16 == 0, "fx_attn_dropout_mask: null or misaligned buffer");
+  attn::MaskParams m{};
+  m.mask = static_cast<uint32_t*>(dropout_mask);
+  m.b = b; m.s = s; m.nh = nh; m.wpr = (s + 127) / 128 * 4;
+  m.thresh2 = dropout_threshold(p_drop) * 0x10001u;
+  m.off_lo = static_cast<uint32_t>(offset); m.off_hi = static_cast<uint32_t>(offset >> 32);
+  m.keys = philox_round_keys(seed);
+  m.bh0 = static_cast<uint64_t>(batch0) * nh;
+  dim3 grid((s + 31) / 32, b * nh);
+  static std::atomic<bool> carve[64];
+  FX_PREFER_MAX_SHARED(attn::attn_dropout_mask_kernel, carve);
+  attn::attn_dropout_mask_kernel<<<grid, attn::MASK_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(m);
+  FX_LAUNCH_CHECK();
+  return FX_OK;
 }
 
 extern "C" int fx_attn_causal_fwd_at(void* stream, const void* qkv, void* out, float* lse, void* dropout_mask, int b,
                                      int s, int nh, int hd, float scale, float p_drop, uint64_t seed, uint64_t offset,
-                                     int batch0) {
+                                     int batch0, int mask_ready) {
   using namespace fx;
   FX_CHECK_ARG(batch0 >= 0, "fx_attn_causal_fwd: negative batch offset");
   FX_CHECK_ARG(b > 0 && s > 0 && nh > 0, "fx_attn_causal_fwd: empty input (b %d, s %d, nh %d)", b, s, nh);
@@ -1158,17 +1181,9 @@ extern "C" int fx_attn_causal_fwd_at(void* stream, const void* qkv, void* out, f
                "fx_attn_causal_fwd: pointers must be 16-byte aligned");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int wpr = (s + 127) / 128 * 4;
-  if (p_drop > 0.f) {
-    attn::MaskParams m{};
-    m.mask = static_cast<uint32_t*>(dropout_mask);
-    m.b = b; m.s = s; m.nh = nh; m.wpr = wpr;
-    m.thresh2 = dropout_threshold(p_drop) * 0x10001u;
-    m.off_lo = static_cast<uint32_t>(offset); m.off_hi = static_cast<uint32_t>(offset >> 32);
-    m.keys = philox_round_keys(seed);
-    m.bh0 = static_cast<uint64_t>(batch0) * nh;
-    dim3 grid((s + 31) / 32, b * nh);
-    attn::attn_dropout_mask_kernel<<<grid, 256, 0, st>>>(m);
-    FX_LAUNCH_CHECK();
+  if (p_drop > 0.f && !mask_ready) {
+    const int rcm = fx_attn_dropout_mask(stream, dropout_mask, b, s, nh, p_drop, seed, offset, batch0);
+    if (rcm) return rcm;
   }
   CUtensorMap map;
   int rc = attn::make_qkv_map(&map, qkv, b, s, nh, hd);

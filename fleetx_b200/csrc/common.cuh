@@ -78,4 +78,17 @@ int make_tma_u32_2d(CUtensorMap* map, const void* base, uint64_t inner, uint64_t
 
 static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 
+// A kernel without shared memory of its own can only share an SM with a resident GEMM CTA (whose dynamic window
+// takes the whole 228 KB carve-out) if it is launched for the same shared-memory / L1 split: ask for the
+// maximum-shared carve-out once per device. FLAGS: a static std::atomic<bool>[64] owned by the caller.
+#define FX_PREFER_MAX_SHARED(kernel, flags)                                                              \
+  do {                                                                                                   \
+    int dev__ = 0;                                                                                       \
+    if (cudaGetDevice(&dev__) == cudaSuccess && dev__ >= 0 && dev__ < 64 && !flags[dev__]) {             \
+      cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout,                       \
+                           cudaSharedmemCarveoutMaxShared);                                              \
+      flags[dev__] = true;                                                                               \
+    }                                                                                                    \
+  } while (0)
+
 }  // namespace fx

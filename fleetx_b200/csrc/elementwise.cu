@@ -4,6 +4,8 @@
 // accesses, one 8-element group per thread per step; the dropout mask is regenerated from
 // Philox in backward instead of being stored. Algorithmic bytes per token (bf16): forward 6h,
 // backward 4h, column sum 2n.
+#include <atomic>
+
 #include "common.cuh"
 #include "philox.cuh"
 #include "tc5.cuh"
@@ -102,31 +104,37 @@ bdr_bwd_kernel(const __nv_bfloat16* __restrict__ dout, __nv_bfloat16* __restrict
 __global__ void __launch_bounds__(256)
 colsum_partial_kernel(const __nv_bfloat16* __restrict__ x, int ldx, float* __restrict__ part,
                       int rows, int n) {
-  __shared__ float red[8][32][9];
+  // block (32, 8): thread (tx, ty) owns 8 columns and every (8 * gridDim.y)-th row from blockIdx.y * 8 + ty on, four
+  // 16-byte loads in flight; each thread stores its own partial row (no shared memory: a block fits beside a
+  // resident GEMM CTA when the host runs the column sums next to the weight-gradient GEMM that reads the same matrix)
   const int col = (blockIdx.x * 32 + threadIdx.x) * 8;
+  if (col >= n) return;
   float acc[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) acc[j] = 0.f;
-  if (col < n) {
-    for (int r = blockIdx.y * 8 + threadIdx.y; r < rows; r += gridDim.y * 8) {
+  const int step = gridDim.y * 8;
+  int r = blockIdx.y * 8 + threadIdx.y;
+  for (; r + 3 * step < rows; r += 4 * step) {
+    uint4 q[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) q[u] = __ldg(reinterpret_cast<const uint4*>(x + (size_t)(r + u * step) * ldx + col));
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
       float v[8];
-      unpack8(__ldg(reinterpret_cast<const uint4*>(x + (size_t)r * ldx + col)), v);
+      unpack8(q[u], v);
 #pragma unroll
       for (int j = 0; j < 8; ++j) acc[j] += v[j];
     }
   }
+  for (; r < rows; r += step) {
+    float v[8];
+    unpack8(__ldg(reinterpret_cast<const uint4*>(x + (size_t)r * ldx + col)), v);
 #pragma unroll
-  for (int j = 0; j < 8; ++j) red[threadIdx.y][threadIdx.x][j] = acc[j];
-  __syncthreads();
-  if (threadIdx.y == 0 && col < n) {
-#pragma unroll
-    for (int i = 1; i < 8; ++i)
-#pragma unroll
-      for (int j = 0; j < 8; ++j) acc[j] += red[i][threadIdx.x][j];
-    float4* o = reinterpret_cast<float4*>(part + (size_t)blockIdx.y * n + col);
-    o[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
-    o[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
+    for (int j = 0; j < 8; ++j) acc[j] += v[j];
   }
+  float4* o = reinterpret_cast<float4*>(part + (size_t)(blockIdx.y * 8 + threadIdx.y) * n + col);
+  o[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
+  o[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
 }
 
 __global__ void __launch_bounds__(256)
@@ -198,7 +206,7 @@ extern "C" int fx_bias_dropout_residual_bwd(void* stream, const void* dout, void
 
 extern "C" size_t fx_colsum_workspace_bytes(int rows, int n) {
   if (rows <= 0 || n <= 0) return 0;
-  return (size_t)fx::ew::colsum_splits(rows, n) * (size_t)n * sizeof(float);
+  return (size_t)fx::ew::colsum_splits(rows, n) * 8 * (size_t)n * sizeof(float);
 }
 
 extern "C" int fx_colsum_bf16(void* stream, const void* x, int ldx, void* out, int out_dtype,
@@ -212,10 +220,13 @@ extern "C" int fx_colsum_bf16(void* stream, const void* x, int ldx, void* out, i
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int splits = ew::colsum_splits(rows, n);
   float* part = static_cast<float*>(workspace);
+  static std::atomic<bool> carve1[64], carve2[64];
+  FX_PREFER_MAX_SHARED(ew::colsum_partial_kernel, carve1);
+  FX_PREFER_MAX_SHARED(ew::colsum_finish_kernel, carve2);
   ew::colsum_partial_kernel<<<dim3(ceil_div(n, 256), splits), dim3(32, 8), 0, st>>>(
       static_cast<const __nv_bfloat16*>(x), ldx, part, rows, n);
   FX_LAUNCH_CHECK();
-  ew::colsum_finish_kernel<<<ceil_div(n, 256), 256, 0, st>>>(part, out, out_dtype == FX_F32, splits, n);
+  ew::colsum_finish_kernel<<<ceil_div(n, 256), 256, 0, st>>>(part, out, out_dtype == FX_F32, splits * 8, n);
   FX_LAUNCH_CHECK();
   return FX_OK;
 }

@@ -59,7 +59,10 @@ struct Cfg {
   static constexpr int STAGES = BN == 256 ? 4 : 6;
   static constexpr int BAR_BYTES = 256;
   static constexpr int STG_BYTES = NUM_EPI_WARPS * 32 * 33 * 4;  // per-epilogue-warp 32x32 fp32 transpose tile (+1 pad)
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + STG_BYTES + 1024;
+  // no alignment slack: the dynamic window starts 1024-aligned (checked in the kernel), and the 1 KB this saves is
+  // what lets a small kernel with no shared memory of its own (dropout keep bits, dropout backward, ...) share the
+  // SM with a resident GEMM CTA when the host runs it on another stream
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + STG_BYTES;
   static constexpr int TMEM_COLS = 2 * BN;
 };
 
@@ -164,8 +167,11 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
             const Params p) {
   using C = Cfg<BN>;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  extern __shared__ __align__(1024) uint8_t smem[];
+  if (threadIdx.x == 0 && (smem_u32(smem) & 1023u) != 0) {
+    printf("fleetx_b200: GEMM shared memory is not 1024-byte aligned\n");
+    __trap();
+  }
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + C::STAGES * C::STAGE_BYTES);
   uint64_t* empty = full + C::STAGES;
   uint64_t* tfull = empty + C::STAGES;

@@ -68,6 +68,69 @@ class LayerMeta:
 
 import os as _os
 
+_side_streams: dict = {}
+_SIDE = _os.environ.get("FX_SIDE", "1") != "0"  # tuning knob: 0 runs the side-stream kernels in line
+
+
+def _side_stream(device) -> "torch.cuda.Stream":
+    """One extra stream per device for small kernels that hide beside a resident GEMM (integer / memory-bound work
+    next to tensor-core work): launched AFTER the GEMM, so the GEMM's CTAs take their SMs first."""
+    key = torch.device(device).index if torch.device(device).index is not None else torch.cuda.current_device()
+    st = _side_streams.get(key)
+    if st is None:
+        st = torch.cuda.Stream(device=device)
+        _side_streams[key] = st
+    return st
+
+
+class _Beside:
+    """Small memory-bound kernels (the bias-gradient column sums) on the side stream, submitted right AFTER the GEMM
+    that reads the same matrix, so they run in that GEMM's shadow (its CTAs are resident first; the small kernel's
+    blocks need no shared memory and fit beside them)."""
+
+    def __init__(self, device):
+        self.on = _SIDE and torch.device(device).type == "cuda"
+        self.st = _side_stream(device) if self.on else None
+        self.used = False
+
+    def mark(self):
+        """Call BEFORE submitting the GEMM: the point at which the small kernel's inputs are ready."""
+        if not self.on:
+            return None
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream())
+        return ev
+
+    def colsum(self, ev, x, out):
+        if not self.on:
+            return ops.colsum(x, out=out)
+        with torch.cuda.stream(self.st):
+            self.st.wait_event(ev)
+            ops.colsum(x, out=out)
+        x.record_stream(self.st)
+        self.used = True
+        return out
+
+    def join(self):
+        if self.on and self.used:
+            torch.cuda.current_stream().wait_stream(self.st)
+            self.used = False
+
+
+def _attn_mask_beside(b, s, M: LayerMeta, device, batch0=0):
+    """Draw the attention keep bits (a pure function of seed / offset / shape) on the side stream; call right after
+    launching the QKV projection. Returns (mask or None, event to wait for before the attention kernel)."""
+    if not _SIDE or not M.p_attn > 0 or not hasattr(ops, "attn_dropout_mask") or not torch.device(device).type == "cuda":
+        return None, None
+    st = _side_stream(device)
+    nbytes_owner = torch.cuda.current_stream()
+    with torch.cuda.stream(st):
+        mask = ops.attn_dropout_mask(b, s, M.nh_local, M.p_attn, *M.rng_attn, device, batch0=batch0)
+        ev = torch.cuda.Event()
+        ev.record(st)
+    mask.record_stream(nbytes_owner)  # allocated under the side stream, consumed on the caller's
+    return mask, ev
+
 # Tuning knob, OFF by default: pipelining two batch halves through the forward allreduces measured
 # slower than the plain order at 2, 4 and 8 GPUs (the allreduce kernel and the other half's GEMMs
 # compete for the same SMs, and half-batch GEMMs quantise worse): 2.93 -> 3.04 ms at 4, 2.49 -> 2.59 at 8.
@@ -186,8 +249,12 @@ def decoder_layer_fwd_rows(x: torch.Tensor, P: LayerParams, M: LayerMeta, group)
     with ops.sm_budget(group.free_sms() if nc > 1 else 0):  # from the first collective on, its SMs are taken
         for c, r in enumerate(rows):
             ops.gemm(ln1[r], P.qkv_w, out=qkv[r], epilogue=FX_EPI_BIAS, bias=P.qkv_b)   # :166
+            mask_pre, mask_ev = _attn_mask_beside(bc, s, M, dev, batch0=c * bc)          # keep bits: beside the projection
+            if mask_ev is not None:
+                torch.cuda.current_stream().wait_event(mask_ev)
             _, _, mk = ops.attn_causal_fwd(qkv[r].view(bc, s, -1), M.nh_local, M.hd, scale, M.p_attn, *M.rng_attn,
-                                           batch0=c * bc, out=ctx[r].view(bc, s, -1), lse=lse[c * bc:(c + 1) * bc])
+                                           batch0=c * bc, out=ctx[r].view(bc, s, -1), lse=lse[c * bc:(c + 1) * bc],
+                                           **({} if mask_pre is None else dict(mask=mask_pre, mask_ready=True)))
             masks.append(mk)
             ops.gemm(ctx[r], P.out_w, out=A[r])                                      # :340 local matmul
             # _mp_allreduce + bias, dropout1 + residual (:546-547), norm2 (:554)
@@ -243,9 +310,11 @@ def decoder_layer_bwd_rows(dout: torch.Tensor, saved: dict, P: LayerParams, M: L
             pend.append(group.bwd_ln_bdr_start(A[r], saved["x1_own"][c], saved["mean2"][c], saved["rstd2"][c], P.norm2_w,
                                                d[r], M.p_hidden1, *M.rng_h1, m1[c], acc, drop_off=c * Tc * h,
                                                accumulate=c > 0))
+        side = _Beside(dev)
+        ev = side.mark()
         g["lin2_w"] = ops.gemm(saved["act"], d_y2, trans_a=True, split_k=True)
         del d_y2
-        g["lin1_b"] = ops.colsum(d_z)
+        g["lin1_b"] = side.colsum(ev, d_z, torch.empty(d_z.shape[1], dtype=dt, device=dev))  # in the GEMM's shadow
         g["lin1_w"] = ops.gemm(group.wait_kept(saved["ln2"]), d_z, trans_a=True, split_k=True)
         del d_z
         d_ao, pend2 = [], []
@@ -260,15 +329,17 @@ def decoder_layer_bwd_rows(dout: torch.Tensor, saved: dict, P: LayerParams, M: L
             ops.gemm(d_qkv[r], P.qkv_w, trans_b=True, out=A[r])
             pend2.append(group.bwd_ln_start(A[r], saved["x"][r], saved["mean1"][r], saved["rstd1"][r], P.norm1_w, d_x1_c,
                                             acc, accumulate=c > 0, last=c == nc - 1))
+        ev = side.mark()
         g["out_w"] = ops.gemm(saved["ctx"], _rows_cat(d_ao), trans_a=True, split_k=True)
         del d_ao
-        g["qkv_b"] = ops.colsum(d_qkv)
+        g["qkv_b"] = side.colsum(ev, d_qkv, torch.empty(d_qkv.shape[1], dtype=dt, device=dev))
         g["qkv_w"] = ops.gemm(saved["ln1"], d_qkv, trans_a=True, split_k=True)
         del d_qkv
         tot = None
         for c, r in enumerate(rows):
             t_ = group.bwd_ln_finish(pend2[c], dx[r])
             tot = t_ if t_ is not None else tot
+        side.join()
     g["norm2_w"], g["norm2_b"], g["norm1_w"], g["norm1_b"] = tot[0], tot[1], tot[3], tot[4]
     g["out_b"], g["lin2_b"] = tot[2].to(P.out_b.dtype), tot[5].to(P.lin2_b.dtype)
     return dx.view(b, s, h), g
@@ -294,7 +365,11 @@ def decoder_layer_fwd(x: torch.Tensor, P: LayerParams, M: LayerMeta, group):
         ln1 = mean1 = rstd1 = None
         attn_in = x2
     qkv = ops.gemm(attn_in, P.qkv_w, epilogue=FX_EPI_BIAS, bias=P.qkv_b)            # :166
-    ctx, lse, attn_mask = ops.attn_causal_fwd(qkv.view(b, s, -1), M.nh_local, M.hd, scale, M.p_attn, *M.rng_attn)  # :167-173, :268-298
+    mask_pre, mask_ev = _attn_mask_beside(b, s, M, x.device)                         # keep bits: beside the projection
+    if mask_ev is not None:
+        torch.cuda.current_stream().wait_event(mask_ev)
+    ctx, lse, attn_mask = ops.attn_causal_fwd(qkv.view(b, s, -1), M.nh_local, M.hd, scale, M.p_attn, *M.rng_attn,
+                                              **({} if mask_pre is None else dict(mask=mask_pre, mask_ready=True)))  # :167-173, :268-298
     ctx2 = ctx.view(T, -1)
     attn_out = ops.gemm(ctx2, P.out_w, out=group.partial_buffer(T, h, x.device))    # :340 local matmul
     # _mp_allreduce, + bias, dropout1 + residual (:546-547) — one fused kernel on a symmetric-memory group
@@ -345,12 +420,14 @@ def decoder_layer_bwd(dout: torch.Tensor, saved: dict, P: LayerParams, M: LayerM
     # backward of _c_identity: allreduce of dX. Nothing on the weight-gradient side depends on it, so the
     # transfer runs on the group's own stream underneath those GEMMs.
     pending = group.all_reduce_start(d_ffn_in)
-    g["lin2_b"] = ops.colsum(d_y2)
+    side = _Beside(d.device)
+    ev = side.mark()
     g["lin2_w"] = ops.gemm(saved["act"], d_y2, trans_a=True, split_k=True)                       # dW2 = act^T · dY
+    g["lin2_b"] = side.colsum(ev, d_y2, torch.empty(h, dtype=d.dtype, device=d.device))
     del d_y2
-    g["lin1_b"] = ops.colsum(d_z)
     ffn_in = saved["ln2"] if M.normalize_before else saved["x1"]
     g["lin1_w"] = ops.gemm(ffn_in, d_z, trans_a=True, split_k=True)
+    g["lin1_b"] = side.colsum(ev, d_z, torch.empty(d_z.shape[1], dtype=d.dtype, device=d.device))
     del d_z
     d_ffn_in = group.all_reduce_finish(pending)
     if M.normalize_before:
@@ -371,14 +448,16 @@ def decoder_layer_bwd(dout: torch.Tensor, saved: dict, P: LayerParams, M: LayerM
     del d_ctx
     d_attn_in = ops.gemm(d_qkv, P.qkv_w, trans_b=True, out=group.partial_buffer(T, h, d.device))
     pending = group.all_reduce_start(d_attn_in)                                     # backward of _c_identity
-    g["out_b"] = ops.colsum(d_ao)
+    ev = side.mark()
     g["out_w"] = ops.gemm(saved["ctx"], d_ao, trans_a=True, split_k=True)
+    g["out_b"] = side.colsum(ev, d_ao, torch.empty(h, dtype=d.dtype, device=d.device))
     del d_ao
-    g["qkv_b"] = ops.colsum(d_qkv)
     attn_in = saved["ln1"] if M.normalize_before else saved["x"]
     g["qkv_w"] = ops.gemm(attn_in, d_qkv, trans_a=True, split_k=True)
+    g["qkv_b"] = side.colsum(ev, d_qkv, torch.empty(d_qkv.shape[1], dtype=d.dtype, device=d.device))
     del d_qkv
     d_attn_in = group.all_reduce_finish(pending)
+    side.join()
     if M.normalize_before:
         dx, g["norm1_w"], g["norm1_b"] = ops.layernorm_bwd(d_attn_in, saved["x"], P.norm1_w, saved["mean1"],
                                                            saved["rstd1"], dresidual=d_r1)

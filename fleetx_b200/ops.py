@@ -204,7 +204,8 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, trans_a: bool = False, trans_b: bo
 
 # ------------------------------------------------------------------------------- attention
 def attn_causal_fwd(qkv: torch.Tensor, nh: int, hd: int, scale: float, p_drop: float = 0.0,
-                    seed: int = 0, offset: int = 0, batch0: int = 0, out=None, lse=None, mask=None):
+                    seed: int = 0, offset: int = 0, batch0: int = 0, out=None, lse=None, mask=None,
+                    mask_ready: bool = False):
     """qkv: bf16 [b, s, nh*3*hd] (packed per head q|k|v). Returns (out [b, s, nh*hd], lse [b, nh, s],
     mask): mask holds the dropout keep bits (None when p_drop == 0) and goes to attn_causal_bwd. batch0: these are
     sequences [batch0, batch0 + b) of a larger batch (same keep bits as the whole-batch call)."""
@@ -233,8 +234,17 @@ def attn_causal_fwd(qkv: torch.Tensor, nh: int, hd: int, scale: float, p_drop: f
     else:
         mask = None
     check(_lib.lib().fx_attn_causal_fwd_at(_stream(), _p(qkv), _p(out), _p(lse), _p(mask), b, s, nh, hd, float(scale),
-                                           float(p_drop), int(seed), int(offset), int(batch0)), "fx_attn_causal_fwd")
+                                           float(p_drop), int(seed), int(offset), int(batch0), int(mask_ready)),
+          "fx_attn_causal_fwd")
     return out, lse, mask
+
+
+def attn_dropout_mask(b: int, s: int, nh: int, p_drop: float, seed: int, offset: int, device, batch0: int = 0):
+    """The keep bits of attention dropout on their own (pass the result to attn_causal_fwd with mask_ready=True)."""
+    mask = torch.empty(_lib.lib().fx_attn_dropout_mask_bytes(b, s, nh), dtype=torch.uint8, device=device)
+    check(_lib.lib().fx_attn_dropout_mask(_stream(), _p(mask), b, s, nh, float(p_drop), int(seed), int(offset),
+                                          int(batch0)), "fx_attn_dropout_mask")
+    return mask
 
 
 def attn_causal_bwd(dout, qkv, out, lse, mask, nh: int, hd: int, scale: float, p_drop: float = 0.0, dqkv=None):

@@ -146,7 +146,13 @@ int fx_attn_causal_fwd(void* stream, const void* qkv, void* out, float* lse, voi
  * its collectives): qkv / out / lse / dropout_mask point at this part, and the keep bits are those the whole-batch
  * call draws for these sequences. */
 int fx_attn_causal_fwd_at(void* stream, const void* qkv, void* out, float* lse, void* dropout_mask, int b, int s,
-                          int nh, int hd, float scale, float p_drop, uint64_t seed, uint64_t offset, int batch0);
+                          int nh, int hd, float scale, float p_drop, uint64_t seed, uint64_t offset, int batch0,
+                          int mask_ready);
+/* The keep bits alone — a pure function of (seed, offset, shape), so a host can draw them on another stream while
+ * the QKV projection runs (integer work beside tensor-core work) and then call fx_attn_causal_fwd_at with
+ * mask_ready = 1, which skips the draw. */
+int fx_attn_dropout_mask(void* stream, void* dropout_mask, int b, int s, int nh, float p_drop, uint64_t seed,
+                         uint64_t offset, int batch0);
 size_t fx_attn_causal_bwd_workspace_bytes(int b, int s, int nh, int hd);
 /* dqkv bf16, same packed layout as qkv, fully overwritten. dropout_mask: what the forward wrote.
  * hd == 64 runs ONE kernel that produces dK, dV and adds the dQ contribution of each KV tile into an
