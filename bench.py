@@ -572,7 +572,8 @@ def run_gpu(args):
             "metric": METRIC, "value": tokens_per_s, "unit": "tokens/s", "n_gpus": n, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": dict(workload_config(args, n), collective=collective),
+            "config": dict(workload_config(args, n), collective=collective,
+                           collective_fallbacks=getattr(group, "fallbacks", {}) or None),
             "e2e": {"value": e2e_tokens_per_s, "unit": "tokens/s", "h2d_bytes_per_step": 2 * T * H * 2,
                     "d2h_bytes_per_step": T * H * 2, "steps": e2e_steps,
                     "pipeline": "double-buffered copies on their own streams: H2D of step i+1 and D2H of step i-1 "

@@ -200,7 +200,7 @@ ce_loss_kernel(const float* __restrict__ gmax, const float* __restrict__ gsum, c
 
 // dlogits[t,c] = (exp(l[t,c] - gmax[t]) / gsum[t] - [c == label]) * dloss * mask[t] / sum(mask)
 __global__ void __launch_bounds__(256)
-ce_bwd_kernel(const __nv_bfloat16* __restrict__ logits, __nv_bfloat16* __restrict__ dlogits,
+ce_bwd_kernel(const __nv_bfloat16* logits, __nv_bfloat16* dlogits,  // may alias (in-place): no __restrict__, no __ldg
               const int64_t* __restrict__ labels, int64_t vocab_start, int vl, const float* __restrict__ gmax,
               const float* __restrict__ gsum, const float* __restrict__ mask, const float* __restrict__ loss_out,
               const float* __restrict__ dloss) {
@@ -213,7 +213,7 @@ ce_bwd_kernel(const __nv_bfloat16* __restrict__ logits, __nv_bfloat16* __restric
   const int nvec = vl >> 3;
   for (int v = threadIdx.x; v < nvec; v += blockDim.x) {
     float x[8];
-    unpack8(__ldg(row + v), x);
+    unpack8(row[v], x);  // plain load: each vector is read, then overwritten, by the same thread
 #pragma unroll
     for (int j = 0; j < 8; ++j) x[j] = __expf(x[j] - m) * inv - ((v * 8 + j) == col ? w : 0.f);
     drow[v] = pack8(x);

@@ -79,6 +79,16 @@ class _GroupOps:
             return y
         return ops.bias_dropout_residual_fwd(y, bias, residual, p, seed, offset, mask_in=mask_in)
 
+    def sp_keep(self, t: torch.Tensor) -> torch.Tensor:
+        """A gathered tensor that must outlive the next collective (it may sit in a communication buffer)."""
+        return t
+
+    def sp_sum_small(self, parts) -> torch.Tensor:
+        """Sum over the ranks of a few small fp32 vectors (the gradients of parameters whose kernels saw only this
+        rank's rows: all_reduce_gradient_hook, sequence_parallel_utils.py:136-140), returned as one flat tensor."""
+        flat = torch.cat([t.reshape(-1) for t in parts])
+        return self.all_reduce_(flat)
+
     # Split form of the plain reduce-scatter (backward of AllGatherOp): the caller puts the weight-gradient
     # GEMM that does not depend on it between the two halves. The base version is synchronous.
     def sp_reduce_scatter_start(self, part, b, s):
@@ -277,6 +287,7 @@ class SymmetricTPGroup(TorchDistGroup):
         self._peer_sigs = (ctypes.c_uint64 * n)(*[int(p) for p in self._hdl.signal_pad_ptrs])
         self._mc = int(self._hdl.multicast_ptr)
         self._lib = _lib
+        self.fallbacks = {}  # name of a call that went to torch.distributed -> how often
         self._epoch = 0
         self._comm_stream = torch.cuda.Stream(device=dev, priority=-1)  # high priority: its blocks go first
         self.num_blocks = num_blocks
@@ -289,7 +300,7 @@ class SymmetricTPGroup(TorchDistGroup):
         self.row_owner = os.environ.get("FX_TP_ROWS", "1") != "0"
         self.rows_blocks = int(os.environ.get("FX_TP_ROWS_BLOCKS", "32"))
         self._acc_h = min(8192, int(_lib.lib().fx_tp_rows_max_h()))
-        if self.row_owner:
+        if True:  # the buffers exist whichever order the layer takes (the small fp32 one also serves sequence parallel)
             self._bufB, self._mcB = [], []
             for _ in range(2):
                 t = symm_mem.empty(max_elems, dtype=torch.bfloat16, device=dev)
@@ -315,8 +326,23 @@ class SymmetricTPGroup(TorchDistGroup):
         torch.cuda.synchronize(dev)
         self._dist.barrier(group=self.pg)
 
+    def _fallback(self, what: str) -> None:
+        """A call this group cannot serve with the library's own kernels (tensor outside the symmetric buffer, too
+        large, wrong dtype, h beyond the row-owner limit) goes to torch.distributed — never quietly: it is counted
+        in self.fallbacks (bench.py prints it) and warned about once per kind; FX_STRICT_COMM=1 makes it an error."""
+        import os
+        import warnings
+
+        if os.environ.get("FX_STRICT_COMM", "0") == "1":
+            raise RuntimeError(f"SymmetricTPGroup.{what}: not servable by the library's collectives (FX_STRICT_COMM=1)")
+        if what not in self.fallbacks:
+            warnings.warn(f"SymmetricTPGroup.{what}: falling back to torch.distributed + separate kernels for this call "
+                          "shape (tensor not in the symmetric buffer / beyond its size); it is much slower", stacklevel=3)
+        self.fallbacks[what] = self.fallbacks.get(what, 0) + 1
+
     def partial_buffer(self, rows: int, cols: int, device) -> torch.Tensor:
         if rows * cols > self.max_elems:
+            self._fallback("partial_buffer")
             return super().partial_buffer(rows, cols, device)
         return self._buf[: rows * cols].view(rows, cols)
 
@@ -325,6 +351,7 @@ class SymmetricTPGroup(TorchDistGroup):
     def sp_all_gather(self, shard: torch.Tensor, b: int, s: int) -> torch.Tensor:
         h = shard.shape[-1]
         if b * s * h > self.max_elems or shard.dtype != torch.bfloat16 or not shard.is_contiguous():
+            self._fallback("sp_all_gather")
             return super().sp_all_gather(shard, b, s)
         self._epoch += 1
         self._lib.check(self._lib.lib().fx_tp_allgather_rows(
@@ -334,6 +361,7 @@ class SymmetricTPGroup(TorchDistGroup):
 
     def sp_reduce_scatter_bdr(self, part, b, s, bias, residual, p, seed, offset, mask_in=None):
         if not self._is_symmetric(part):
+            self._fallback("sp_reduce_scatter_bdr")
             return super().sp_reduce_scatter_bdr(part, b, s, bias, residual, p, seed, offset, mask_in)
         h = part.shape[-1]
         out = torch.empty(s // self.nranks * b, h, dtype=torch.bfloat16, device=part.device)
@@ -348,8 +376,28 @@ class SymmetricTPGroup(TorchDistGroup):
     def sp_reduce_scatter(self, part, b, s):
         return self.sp_reduce_scatter_bdr(part, b, s, None, None, 0.0, 0, 0)
 
+    def sp_keep(self, t: torch.Tensor) -> torch.Tensor:
+        if self.nranks == 1 or not self._is_symmetric(t):
+            return t
+        keep = torch.empty_like(t)
+        keep.copy_(t)  # a device-to-device copy out of the symmetric buffer (the next row-parallel GEMM rewrites it)
+        return keep
+
+    def sp_sum_small(self, parts) -> torch.Tensor:
+        n = sum(t.numel() for t in parts)
+        if n > self._bufC.numel() or n % 4 or any(t.dtype != torch.float32 for t in parts):
+            self._fallback("sp_sum_small")
+            return super().sp_sum_small(parts)
+        # through the library's own small allreduce: an NCCL kernel between the spinning collectives could deadlock
+        o = 0
+        for t in parts:
+            self._bufC[o:o + t.numel()].copy_(t.reshape(-1))
+            o += t.numel()
+        return self.all_reduce_acc(self._bufC[:n])
+
     def sp_reduce_scatter_start(self, part, b, s):
         if not self._is_symmetric(part):
+            self._fallback("sp_reduce_scatter_start")
             return super().sp_reduce_scatter_start(part, b, s)
         h = part.shape[-1]
         out = torch.empty(s // self.nranks * b, h, dtype=torch.bfloat16, device=part.device)  # on the caller's stream
@@ -405,6 +453,7 @@ class SymmetricTPGroup(TorchDistGroup):
 
     def all_reduce_acc(self, acc: torch.Tensor) -> torch.Tensor:
         if acc.data_ptr() != self._bufC.data_ptr():
+            self._fallback("all_reduce_acc")
             return super().all_reduce_acc(acc)
         out = torch.empty_like(acc)
         self._epoch += 1
@@ -457,6 +506,7 @@ class SymmetricTPGroup(TorchDistGroup):
 
     def fwd_ln_start(self, part, bias, residual, p, seed, offset, mask_in, gamma, beta, eps, drop_off=0):
         if not self._rows_ok(part):
+            self._fallback("fwd_ln_start")
             return super().fwd_ln_start(part, bias, residual, p, seed, offset, mask_in, gamma, beta, eps, drop_off)
         rows, h = part.shape
         r0, r1 = self.own_rows(rows)
@@ -477,7 +527,7 @@ class SymmetricTPGroup(TorchDistGroup):
     def keep_copy(self, t: torch.Tensor, dst: torch.Tensor) -> None:
         """The copy runs on a third stream, underneath whatever the caller launches next; the next kernel that
         rewrites B0 waits for it, readers of dst go through wait_kept()."""
-        if not self.row_owner or self._symm_offset_in(t, self._bufB[0]) is None:
+        if self._symm_offset_in(t, self._bufB[0]) is None:
             return super().keep_copy(t, dst)
         ready = torch.cuda.Event()
         ready.record(torch.cuda.current_stream())
@@ -490,13 +540,14 @@ class SymmetricTPGroup(TorchDistGroup):
         self._kept[dst.data_ptr()] = done
 
     def wait_kept(self, t: torch.Tensor) -> torch.Tensor:
-        ev = self._kept.pop(t.data_ptr(), None) if self.row_owner else None
+        ev = self._kept.pop(t.data_ptr(), None)
         if ev is not None:
             torch.cuda.current_stream().wait_event(ev)
         return t
 
     def fwd_out_start(self, part, bias, residual_own, p, seed, offset, mask_in, drop_off=0):
         if not self._rows_ok(part):
+            self._fallback("fwd_out_start")
             return super().fwd_out_start(part, bias, residual_own, p, seed, offset, mask_in, drop_off)
         return self._on_comm_stream(lambda st: self._rows_call(
             st, self._lib.FX_ROWS_FWD_OUT, part, 1, bias=bias, residual=residual_own, p=float(p), seed=int(seed),
@@ -511,6 +562,7 @@ class SymmetricTPGroup(TorchDistGroup):
     def bwd_ln_bdr_start(self, part, x_own, mean_own, rstd_own, gamma, dres, p, seed, offset, mask_in, acc,
                          drop_off=0, accumulate=False):
         if not self._rows_ok(part) or acc.data_ptr() != self._bufC.data_ptr():
+            self._fallback("bwd_ln_bdr_start")
             return super().bwd_ln_bdr_start(part, x_own, mean_own, rstd_own, gamma, dres, p, seed, offset, mask_in, acc,
                                             drop_off, accumulate)
         d_x1 = torch.empty_like(x_own)  # allocated on the caller's stream
@@ -527,6 +579,7 @@ class SymmetricTPGroup(TorchDistGroup):
 
     def bwd_ln_start(self, part, x, mean, rstd, gamma, dres_own, acc, accumulate=False, last=True):
         if not self._rows_ok(part) or acc.data_ptr() != self._bufC.data_ptr():
+            self._fallback("bwd_ln_start")
             return super().bwd_ln_start(part, x, mean, rstd, gamma, dres_own, acc, accumulate, last)
 
         # last: every partial sum is in once this kernel's rows are done, so the sum of acc over the ranks is its tail
@@ -579,6 +632,7 @@ class SymmetricTPGroup(TorchDistGroup):
 
     def all_reduce(self, t: torch.Tensor) -> torch.Tensor:
         if not self._is_symmetric(t):
+            self._fallback("all_reduce")
             return self.all_reduce_(t)
         t2 = t.view(-1, t.shape[-1])
         if self.nranks == 2:  # one-shot peer-load variant: the peer still reads my copy, so the sum goes elsewhere
@@ -590,6 +644,7 @@ class SymmetricTPGroup(TorchDistGroup):
 
     def all_reduce_start(self, t: torch.Tensor):
         if not self._is_symmetric(t):
+            self._fallback("all_reduce_start")
             return super().all_reduce_start(t)
         t2 = t.view(-1, t.shape[-1])
         out = torch.empty_like(t2) if self.nranks == 2 else None  # allocated on the caller's stream
@@ -611,6 +666,7 @@ class SymmetricTPGroup(TorchDistGroup):
 
     def all_reduce_bias_dropout_residual(self, y, bias, residual, p, seed, offset, mask_in=None):
         if not self._is_symmetric(y):
+            self._fallback("all_reduce_bias_dropout_residual")
             return super().all_reduce_bias_dropout_residual(y, bias, residual, p, seed, offset, mask_in)
         y2 = y.view(-1, y.shape[-1])
         out = torch.empty_like(y2)
@@ -701,6 +757,36 @@ class _MpAllReduce(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dy):
         return dy, None
+
+
+class _CConcat(torch.autograd.Function):
+    """Paddle's `_c_concat`: all-gather along the LAST dim forward (rank r's slice lands at columns
+    [r * w, (r + 1) * w)), take this rank's slice of the gradient backward — what parallel_matmul puts behind the
+    vocabulary-split logits when parallel_output=False (hybrid_model.py:59-63). Not on the training hot path (the
+    pretraining criterion consumes the split logits), so torch.distributed does the exchange."""
+
+    @staticmethod
+    def forward(ctx, x, group):
+        ctx.group, ctx.width = group, x.shape[-1]
+        n = group.nranks
+        if n == 1:
+            return x
+        x2 = x.contiguous()
+        flat = torch.empty((n * x2.shape[0],) + tuple(x2.shape[1:]), dtype=x2.dtype, device=x2.device)
+        group._dist.all_gather_into_tensor(flat, x2, group=group.pg)  # rank-major along dim 0
+        # [n, ..., w] -> [..., n * w]
+        return flat.view((n,) + tuple(x2.shape)).movedim(0, -2).reshape(*x2.shape[:-1], n * x2.shape[-1])
+
+    @staticmethod
+    def backward(ctx, dy):
+        g, w = ctx.group, ctx.width
+        if g.nranks == 1:
+            return dy, None
+        return dy[..., g.rank * w:(g.rank + 1) * w].contiguous(), None
+
+
+def c_concat(x: torch.Tensor, group) -> torch.Tensor:
+    return _CConcat.apply(x, group)
 
 
 def c_identity(x: torch.Tensor, group) -> torch.Tensor:

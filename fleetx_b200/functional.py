@@ -519,10 +519,8 @@ def decoder_layer_fwd_sp(x_shard: torch.Tensor, P: LayerParams, M: LayerMeta, gr
     sequence_parallel_utils.py:150-326): x_shard is THIS rank's [s/n, b, h] slice of the sequence-first
     activations; LayerNorm, dropout and the residual adds run on the shard only, an all-gather stands in
     front of each column-parallel matmul and a reduce-scatter (fused with bias + dropout + residual)
-    behind each row-parallel one. Returns ([s/n, b, h], saved)."""
-    if not M.normalize_before:
-        raise NotImplementedError("sequence_parallel with normalize_before=False is not built (the reference "
-                                  "configurations are pre-LN)")
+    behind each row-parallel one. Pre-LN (:533-534, :553-554) and post-LN (:549-550, :563-564) orders.
+    Returns ([s/n, b, h], saved)."""
     sl, b, h = x_shard.shape
     n = group.nranks
     s = sl * n
@@ -530,28 +528,72 @@ def decoder_layer_fwd_sp(x_shard: torch.Tensor, P: LayerParams, M: LayerMeta, gr
     dev = x_shard.device
     xs = x_shard.reshape(Tl, h)
     scale = M.hd ** -0.5
+    pre = M.normalize_before
 
-    ln1, mean1, rstd1 = ops.layernorm_fwd(xs, P.norm1_w, P.norm1_b, M.eps)          # :534 on the shard
-    a_full = group.sp_all_gather(ln1, b, s)                                          # AllGatherOp, utils:225
+    if pre:
+        attn_in, mean1, rstd1 = ops.layernorm_fwd(xs, P.norm1_w, P.norm1_b, M.eps)   # :534 on the shard
+    else:
+        attn_in, mean1, rstd1 = xs, None, None
+    a_full = group.sp_all_gather(attn_in, b, s)                                      # AllGatherOp, utils:225
     qkv = ops.gemm(a_full, P.qkv_w, epilogue=FX_EPI_BIAS, bias=P.qkv_b)
     # the gathered tensor is what the weight gradient needs in backward (the reference keeps it too, as the
     # input of F.linear); it lives in the symmetric buffer, which the next GEMM overwrites: keep a copy
-    a_keep = a_full.clone() if n > 1 else a_full
+    a_keep = group.sp_keep(a_full)
     ctx, lse, attn_mask = ops.attn_causal_fwd(qkv.view(b, s, -1), M.nh_local, M.hd, scale, M.p_attn, *M.rng_attn)
     ctx2 = ctx.view(T, -1)
     part = ops.gemm(ctx2, P.out_w, out=group.partial_buffer(T, h, dev))
     # ReduceScatterOp (utils:319) + bias (:322) + dropout1 + residual (:546-547), one kernel
-    x1 = group.sp_reduce_scatter_bdr(part, b, s, P.out_b, xs, M.p_hidden1, *M.rng_h1, mask_in=M.mask_h1)
-    ln2, mean2, rstd2 = ops.layernorm_fwd(x1, P.norm2_w, P.norm2_b, M.eps)           # :554
-    f_full = group.sp_all_gather(ln2, b, s)
+    r1 = group.sp_reduce_scatter_bdr(part, b, s, P.out_b, xs, M.p_hidden1, *M.rng_h1, mask_in=M.mask_h1)
+    if pre:
+        x1 = r1
+        ffn_in, mean2, rstd2 = ops.layernorm_fwd(x1, P.norm2_w, P.norm2_b, M.eps)    # :554
+    else:
+        x1, mean1, rstd1 = ops.layernorm_fwd(r1, P.norm1_w, P.norm1_b, M.eps)        # :550
+        ffn_in, mean2, rstd2 = x1, None, None
+    f_full = group.sp_all_gather(ffn_in, b, s)
     z = torch.empty(T, P.lin1_w.shape[1], dtype=x_shard.dtype, device=dev)
     act = ops.gemm(f_full, P.lin1_w, epilogue=FX_EPI_BIAS_GELU, bias=P.lin1_b, aux=z)
-    f_keep = f_full.clone() if n > 1 else f_full
+    f_keep = group.sp_keep(f_full)
     part = ops.gemm(act, P.lin2_w, out=group.partial_buffer(T, h, dev))
-    out = group.sp_reduce_scatter_bdr(part, b, s, P.lin2_b, x1, M.p_hidden2, *M.rng_h2, mask_in=M.mask_h2)
-    saved = dict(x=xs, a_full=a_keep, mean1=mean1, rstd1=rstd1, qkv=qkv, ctx=ctx2, lse=lse, attn_mask=attn_mask, x1=x1,
-                 f_full=f_keep, mean2=mean2, rstd2=rstd2, z=z, act=act, shape=(b, s, h))
+    r2 = group.sp_reduce_scatter_bdr(part, b, s, P.lin2_b, x1, M.p_hidden2, *M.rng_h2, mask_in=M.mask_h2)
+    if pre:
+        out, mean3, rstd3 = r2, None, None
+    else:
+        out, mean3, rstd3 = ops.layernorm_fwd(r2, P.norm2_w, P.norm2_b, M.eps)       # :564
+    saved = dict(x=xs, a_full=a_keep, mean1=mean1, rstd1=rstd1, qkv=qkv, ctx=ctx2, lse=lse, attn_mask=attn_mask, r1=r1,
+                 x1=x1, f_full=f_keep, mean2=mean2, rstd2=rstd2, z=z, act=act, r2=r2, mean3=mean3, rstd3=rstd3,
+                 shape=(b, s, h), sp=True)
     return out.view(sl, b, h), saved
+
+
+def prune_saved_sp(saved: dict, M: LayerMeta) -> dict:
+    """prune_saved for the sequence-parallel layer (hybrid_model.py:332-335, 406-408, 537-539 together with
+    :475-520): 'full' keeps this rank's input shard only."""
+    if M.recompute is None:
+        return saved
+    if M.recompute == "full":
+        return dict(x=saved["x"], shape=saved["shape"], sp=True)
+    keep = dict(saved)
+    for k in ("ctx", "lse", "attn_mask"):
+        keep[k] = None
+    if M.recompute == "full_attn":
+        keep["qkv"] = None
+    return keep
+
+
+def rebuild_saved_sp(saved: dict, P: LayerParams, M: LayerMeta, group) -> dict:
+    if M.recompute is None:
+        return saved
+    b, s, h = saved["shape"]
+    if M.recompute == "full":
+        return decoder_layer_fwd_sp(saved["x"].view(s // group.nranks, b, h), P, M, group)[1]
+    full = dict(saved)
+    if full["qkv"] is None:  # from the gathered input of qkv_proj, which backward keeps anyway (weight gradient)
+        full["qkv"] = ops.gemm(full["a_full"], P.qkv_w, epilogue=FX_EPI_BIAS, bias=P.qkv_b)
+    ctx, full["lse"], full["attn_mask"] = ops.attn_causal_fwd(full["qkv"].view(b, s, -1), M.nh_local, M.hd,
+                                                               M.hd ** -0.5, M.p_attn, *M.rng_attn)
+    full["ctx"] = ctx.view(b * s, -1)
+    return full
 
 
 def decoder_layer_bwd_sp(dout_shard: torch.Tensor, saved: dict, P: LayerParams, M: LayerMeta, group):
@@ -566,24 +608,31 @@ def decoder_layer_bwd_sp(dout_shard: torch.Tensor, saved: dict, P: LayerParams, 
     dev = dout_shard.device
     d = dout_shard.reshape(Tl, h)
     scale = M.hd ** -0.5
+    pre = M.normalize_before
     g = {}
 
+    if not pre:  # out = LN2(r2)
+        d, norm2_w, norm2_b = ops.layernorm_bwd(d, saved["r2"], P.norm2_w, saved["mean3"], saved["rstd3"])
     d_y2s = ops.bias_dropout_residual_bwd(d, M.p_hidden2, *M.rng_h2, mask_in=M.mask_h2)
     lin2_b = ops.colsum(d_y2s, out_dtype=torch.float32)
     d_y2 = group.sp_all_gather(d_y2s, b, s)                                          # backward of ReduceScatterOp
     d_z = ops.gemm(d_y2, P.lin2_w, trans_b=True, epilogue=FX_EPI_DGELU, aux=saved["z"])
     g["lin2_w"] = ops.gemm(saved["act"], d_y2, trans_a=True, split_k=True)
-    d_ln2_part = ops.gemm(d_z, P.lin1_w, trans_b=True, out=group.partial_buffer(T, h, dev))
+    d_ffn_part = ops.gemm(d_z, P.lin1_w, trans_b=True, out=group.partial_buffer(T, h, dev))
     # backward of AllGatherOp; nothing in linear1's weight gradient depends on it, so the transfer runs on the
     # group's stream underneath that GEMM
-    pending = group.sp_reduce_scatter_start(d_ln2_part, b, s)
+    pending = group.sp_reduce_scatter_start(d_ffn_part, b, s)
     g["lin1_b"] = ops.colsum(d_z)
     g["lin1_w"] = ops.gemm(saved["f_full"], d_z, trans_a=True, split_k=True)
     del d_z
-    d_ln2s = group.sp_reduce_scatter_finish(pending)
-    d_x1s, norm2_w, norm2_b = ops.layernorm_bwd(d_ln2s, saved["x1"], P.norm2_w, saved["mean2"], saved["rstd2"],
-                                                dresidual=d)
-    d_aos = ops.bias_dropout_residual_bwd(d_x1s, M.p_hidden1, *M.rng_h1, mask_in=M.mask_h1)
+    d_ffn_in = group.sp_reduce_scatter_finish(pending)
+    if pre:  # x1 feeds LN2 and the skip: d(x1) = LN2'(d_ffn_in) + d
+        d_r1, norm2_w, norm2_b = ops.layernorm_bwd(d_ffn_in, saved["x1"], P.norm2_w, saved["mean2"], saved["rstd2"],
+                                                   dresidual=d)
+    else:    # x1 = LN1(r1) feeds linear1 and the skip: d(x1) = d_ffn_in + d, then through LN1
+        d_x1 = ops.bias_dropout_residual_fwd(d_ffn_in, None, d, 0.0, 0, 0)
+        d_r1, norm1_w, norm1_b = ops.layernorm_bwd(d_x1, saved["r1"], P.norm1_w, saved["mean1"], saved["rstd1"])
+    d_aos = ops.bias_dropout_residual_bwd(d_r1, M.p_hidden1, *M.rng_h1, mask_in=M.mask_h1)
     out_b = ops.colsum(d_aos, out_dtype=torch.float32)
     d_ao = group.sp_all_gather(d_aos, b, s)
     d_ctx = ops.gemm(d_ao, P.out_w, trans_b=True)
@@ -591,18 +640,20 @@ def decoder_layer_bwd_sp(dout_shard: torch.Tensor, saved: dict, P: LayerParams, 
     d_qkv = ops.attn_causal_bwd(d_ctx.view(b, s, -1), saved["qkv"].view(b, s, -1), saved["ctx"].view(b, s, -1),
                                 saved["lse"], saved["attn_mask"], M.nh_local, M.hd, scale, M.p_attn).view(T, -1)
     del d_ctx
-    d_ln1_part = ops.gemm(d_qkv, P.qkv_w, trans_b=True, out=group.partial_buffer(T, h, dev))
-    pending = group.sp_reduce_scatter_start(d_ln1_part, b, s)
+    d_in_part = ops.gemm(d_qkv, P.qkv_w, trans_b=True, out=group.partial_buffer(T, h, dev))
+    pending = group.sp_reduce_scatter_start(d_in_part, b, s)
     g["qkv_b"] = ops.colsum(d_qkv)
     g["qkv_w"] = ops.gemm(saved["a_full"], d_qkv, trans_a=True, split_k=True)
     del d_qkv
-    d_ln1s = group.sp_reduce_scatter_finish(pending)
-    dxs, norm1_w, norm1_b = ops.layernorm_bwd(d_ln1s, saved["x"], P.norm1_w, saved["mean1"], saved["rstd1"],
-                                              dresidual=d_x1s)
+    d_in = group.sp_reduce_scatter_finish(pending)
+    if pre:
+        dxs, norm1_w, norm1_b = ops.layernorm_bwd(d_in, saved["x"], P.norm1_w, saved["mean1"], saved["rstd1"],
+                                                  dresidual=d_r1)
+    else:
+        dxs = ops.bias_dropout_residual_fwd(d_in, None, d_r1, 0.0, 0, 0)
     # one small fp32 allreduce for the six shard-local parameter gradients
     parts = [norm1_w, norm1_b, norm2_w, norm2_b, out_b, lin2_b]
-    flat = torch.cat([t.reshape(-1) for t in parts])
-    group.all_reduce_(flat)
+    flat = group.sp_sum_small(parts)
     o = 0
     for name, t in zip(("norm1_w", "norm1_b", "norm2_w", "norm2_b", "out_b", "lin2_b"), parts):
         v = flat[o:o + t.numel()].view(t.shape)
@@ -624,10 +675,8 @@ class DecoderLayerFunction(torch.autograd.Function):
         if meta.recompute is not None and meta.recompute not in RECOMPUTE_GRANULARITIES:
             raise ValueError(f"recompute_granularity must be one of {RECOMPUTE_GRANULARITIES}, got {meta.recompute!r}")
         if meta.sequence_parallel:
-            if meta.recompute is not None:
-                raise NotImplementedError("recompute together with sequence_parallel is not built")
             out, saved = decoder_layer_fwd_sp(x, P, meta, group)
-            ctx.saved, ctx.P, ctx.meta, ctx.group = saved, P, meta, group
+            ctx.saved, ctx.P, ctx.meta, ctx.group = prune_saved_sp(saved, meta), P, meta, group
             return out
         out, saved = decoder_layer_fwd(x, P, meta, group)
         ctx.saved, ctx.P, ctx.meta, ctx.group = prune_saved(saved, meta), P, meta, group
@@ -636,7 +685,8 @@ class DecoderLayerFunction(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dout):
         if ctx.meta.sequence_parallel:
-            dx, g = decoder_layer_bwd_sp(dout.contiguous(), ctx.saved, ctx.P, ctx.meta, ctx.group)
+            saved = rebuild_saved_sp(ctx.saved, ctx.P, ctx.meta, ctx.group)
+            dx, g = decoder_layer_bwd_sp(dout.contiguous(), saved, ctx.P, ctx.meta, ctx.group)
             ctx.saved = None
             return (dx, None, None) + tuple(g[k] for k in _GRAD_ORDER)
         saved = rebuild_saved(ctx.saved, ctx.P, ctx.meta, ctx.group)

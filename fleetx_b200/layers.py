@@ -29,6 +29,32 @@ def _init_weight(shape, device, dtype) -> torch.Tensor:
     return (torch.randn(*shape, dtype=torch.float32) * _INIT_STD).to(device=device, dtype=dtype)
 
 
+_causal_checked: dict = {}
+
+
+def accept_causal_mask(mask: Optional[torch.Tensor], s: int, what: str) -> None:
+    """The explicit-mask branch of core_attn (hybrid_model.py:273-275: softmax(product + attn_mask)) for the mask the
+    reference's own model builds in eval, -1e4 * triu(ones, 1) (:716-726): in fp32 that is the fused causal softmax
+    up to exp(-1e4) == 0, so the causal kernel serves it. The tensor is checked once (cached by storage / version);
+    any other additive mask (a padding mask folded in) would need a kernel that reads it and is refused."""
+    if mask is None:
+        return
+    key = (mask.data_ptr(), tuple(mask.shape), mask._version, str(mask.device))
+    ok = _causal_checked.get(key)
+    if ok is None:
+        m = mask.detach()
+        ok = m.dim() >= 2 and m.shape[-1] == s and m.shape[-2] == s and all(d == 1 for d in m.shape[:-2])
+        if ok:
+            m2 = m.reshape(s, s).float()
+            ok = bool(((m2.tril() == 0).all() & (m2.triu(1) + torch.tril(torch.full_like(m2, -1e4)) <= -9999.0).all()).item())
+        if len(_causal_checked) > 64:
+            _causal_checked.clear()
+        _causal_checked[key] = ok
+    if not ok:
+        raise NotImplementedError(f"{what}: only the causal additive mask (-1e4 * triu(1), what the reference's model "
+                                  "passes in eval) is served, by the fused causal kernel; other masks are not built")
+
+
 class ColumnParallelLinear(nn.Module):
     """Y = X·W + b with W [in, out] split by columns over the mp group; gather_output is not
     supported on this path (the decoder layer always passes gather_output=False,
@@ -196,6 +222,7 @@ class MultiHeadAttention(nn.Module):
         return self.Cache(key, value)
 
     _CAP_STEP = 256  # cache buffers grow in steps, so appending is in place most of the time
+    _cache_fill: dict = {}  # (k buffer, v buffer) addresses -> rows filled: who may append in place
 
     def _cache_buffers(self, cache, need: int):
         """The [b, nh, cap, hd] buffers behind cache.k / cache.v (views [:, :, :L] of them) with cap >= need:
@@ -205,7 +232,11 @@ class MultiHeadAttention(nn.Module):
         bk, bv = k._base, v._base
         ok = (bk is not None and bv is not None and bk.dim() == 4 and bk.is_contiguous() and bv.is_contiguous()
               and bk.shape[2] >= need and bk.shape == bv.shape and bk.data_ptr() == k.data_ptr()
-              and bv.data_ptr() == v.data_ptr() and bk.shape[:2] == k.shape[:2] and bk.shape[3] == k.shape[3])
+              and bv.data_ptr() == v.data_ptr() and bk.shape[:2] == k.shape[:2] and bk.shape[3] == k.shape[3]
+              # only the NEWEST view of a buffer may grow in place: decoding again from an older Cache (beam search,
+              # speculative decoding) must not overwrite rows a later Cache still shows — the reference concatenates
+              # into fresh tensors (hybrid_model.py:178-184)
+              and self._cache_fill.get((bk.data_ptr(), bv.data_ptr())) == L)
         if ok:
             return bk, bv
         cap = max((need + self._CAP_STEP - 1) // self._CAP_STEP * self._CAP_STEP, 2 * L)
@@ -214,6 +245,9 @@ class MultiHeadAttention(nn.Module):
         if L:
             nk[:, :, :L].copy_(k)
             nv[:, :, :L].copy_(v)
+        if len(self._cache_fill) > 256:
+            self._cache_fill.clear()  # entries of long-gone buffers; a miss only costs one copy
+        self._cache_fill[(nk.data_ptr(), nv.data_ptr())] = L
         return nk, nv
 
     def attend_cached(self, mix: torch.Tensor, cache):
@@ -225,6 +259,7 @@ class MultiHeadAttention(nn.Module):
         L = cache.k.shape[2]
         bk, bv = self._cache_buffers(cache, L + t)
         ops.kv_cache_append(mix, bk, bv, self.num_heads, self.head_dim, L)
+        self._cache_fill[(bk.data_ptr(), bv.data_ptr())] = L + t  # rows of the buffers in use now
         scale = self.head_dim ** -0.5
         if L == 0 and t >= 64:  # a prompt: the tensor-core kernel
             ctx = ops.attn_causal_fwd(mix, self.num_heads, self.head_dim, scale)[0]
@@ -245,9 +280,7 @@ class MultiHeadAttention(nn.Module):
                                                     cache if cache is not None else self.gen_cache(query))
                 out = self.out_proj(ctx)
             return (out, new_cache) if use_cache else out
-        if attn_mask is not None:
-            raise NotImplementedError("only the causal mask is fused (training passes attn_mask=None, "
-                                      "hybrid_model.py:733-734); the model's eval mask is the same causal mask")
+        accept_causal_mask(attn_mask, query.shape[1], "MultiHeadAttention(attn_mask)")  # :273-275 with the model's mask
         if (key is not None and key is not query) or (value is not None and value is not query):
             raise NotImplementedError("self-attention only")
         if self.sequence_parallel:
@@ -282,8 +315,6 @@ class TransformerDecoderLayer(nn.Module):
         self.use_recompute = use_recompute
         self.recompute_granularity = recompute_granularity
         self.sequence_parallel = sequence_parallel
-        if sequence_parallel and not normalize_before:
-            raise NotImplementedError("sequence_parallel with normalize_before=False is not built")
         if activation != "gelu":
             # the reference stores `activation` but hard-codes F.gelu(approximate=True) (:523, :558)
             raise NotImplementedError("the reference layer always applies tanh-GELU")
@@ -369,8 +400,8 @@ class TransformerDecoderLayer(nn.Module):
     def forward(self, tgt, memory=None, tgt_mask=None, use_cache=False, cache=None):
         if use_cache or cache is not None:
             return self._forward_cached(tgt, use_cache, cache)
-        if tgt_mask is not None:
-            raise NotImplementedError("only the causal mask is fused (training passes tgt_mask=None)")
+        accept_causal_mask(tgt_mask, tgt.shape[0] * getattr(self.model_parallel_group, "nranks", 1) if self.sequence_parallel
+                           else tgt.shape[1], "TransformerDecoderLayer(tgt_mask)")  # :273-275 with the model's mask
         if not tgt.is_cuda:
             raise RuntimeError("TransformerDecoderLayer needs CUDA tensors: there is no CPU path")
         return Fn.DecoderLayerFunction.apply(tgt.contiguous(), self._meta(), self.model_parallel_group,

@@ -22,7 +22,7 @@ from torch import nn
 
 from . import _lib, ops
 from ._lib import check
-from .dist import c_identity, resolve_group
+from .dist import c_concat, c_identity, resolve_group
 from .layers import LayerNorm, TransformerDecoderLayer, _init_weight
 from .rng import get_rng_state_tracker
 
@@ -108,13 +108,13 @@ class LogitsFunction(torch.autograd.Function):
 
 
 def parallel_matmul(lm_output, logit_weights, parallel_output, mp_group=None):
-    """hybrid_model.py:45-66. parallel_output=False (concatenating the vocabulary slices) is not built: the
-    pretraining criterion consumes the split logits."""
+    """hybrid_model.py:45-66: _c_identity, the matmul against this rank's vocabulary slice, and — with
+    parallel_output=False (:59-63, the eval / generation callers) — _c_concat of the slices into full logits."""
     group = resolve_group(mp_group)
     if group.nranks > 1:
-        if not parallel_output:
-            raise NotImplementedError("parallel_matmul(parallel_output=False): _c_concat of the logits is not built")
         lm_output = c_identity(lm_output, group)
+        logits = LogitsFunction.apply(lm_output, logit_weights)
+        return logits if parallel_output else c_concat(logits, group)
     return LogitsFunction.apply(lm_output, logit_weights)
 
 
@@ -153,6 +153,10 @@ class MaskedCrossEntropyFunction(torch.autograd.Function):
         lg, lab, gmax, stats, out2, mask = ctx.saved_tensors
         vocab_start, T, vl, has_mask, shape = ctx.cfg
         dl = dloss.to(torch.float32).reshape(1).contiguous()
+        if getattr(ctx, "consumed", False):
+            raise RuntimeError("MaskedCrossEntropyFunction: dlogits are written over the logits, so this node can be "
+                               "differentiated once (no retain_graph / double backward)")
+        ctx.consumed = True
         check(_lib.lib().fx_cross_entropy_bwd(_stream(), _p(lg), _p(lg), _p(lab), vocab_start, T, vl, _p(gmax), _p(stats[1]),
                                               _p(mask) if has_mask else None, _p(out2), _p(dl)), "fx_cross_entropy_bwd")
         return lg.view(shape), None, None, None, None
@@ -305,7 +309,11 @@ class GPTModelHybrid(nn.Module):
 
     def forward(self, input_ids, position_ids=None, attention_mask=None, use_cache=False, cache=None):
         if attention_mask is not None:
-            raise NotImplementedError("only the causal mask is fused (training passes no attention_mask)")
+            # :716-729: in eval the reference adds its causal mask (-1e4 * triu(1)) to a given attention_mask and hands
+            # the sum to the layers; a mask that already IS that causal mask is served by the fused causal kernel
+            from .layers import accept_causal_mask
+
+            accept_causal_mask(attention_mask, input_ids.shape[-1], "GPTModelHybrid(attention_mask)")
         if position_ids is None and cache is not None:  # :697-705: positions continue behind the cached tokens
             past = cache[0].k.shape[-2]
             position_ids = torch.arange(past, past + input_ids.shape[-1], dtype=torch.int64, device=input_ids.device)

@@ -74,10 +74,14 @@ class FusedAdamW:
         self.lr = float(lr)
 
     def _upload_table(self) -> None:
+        self._grad_keep = []  # contiguous copies of strided gradients stay alive until the next step's table is built
         for i, (name, p) in enumerate(self.params):
             if p.grad is None:
                 raise _lib.FleetXError(f"FusedAdamW.step: parameter {name} has no gradient")
-            g = p.grad if p.grad.is_contiguous() else p.grad.contiguous()
+            g = p.grad
+            if not g.is_contiguous():
+                g = g.contiguous()
+                self._grad_keep.append(g)  # the kernels read this block after this function returns
             self._table_host[i].grad = g.data_ptr()
             self._table_host[i].grad_f32 = int(g.dtype == torch.float32)
         if self._copied is not None:

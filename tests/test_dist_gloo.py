@@ -77,6 +77,23 @@ def _worker(rank, world, port, ret):
             ok = ok and torch.allclose(v.grad, ref_shard[k], atol=1e-10)
         for k, v in rep.items():  # replicated parameters see the full gradient on every rank
             ok = ok and torch.allclose(v.grad, g_ref[k], atol=1e-10)
+        # parallel_matmul(parallel_output=False) (hybrid_model.py:45-66): logits against this rank's vocabulary slice,
+        # _c_concat along the last dim; backward = this rank's columns of the gradient, then _c_identity's allreduce
+        from fleetx_b200.dist import c_concat, c_identity
+
+        gv = torch.Generator().manual_seed(5)
+        wte = torch.randn(8 * world, 64, generator=gv, dtype=torch.float64)     # [vocab, h], split by rows
+        hid = torch.randn(2, 16, 64, generator=gv, dtype=torch.float64)
+        dlog = torch.randn(2, 16, 8 * world, generator=gv, dtype=torch.float64)
+        w_r = wte[rank * 8:(rank + 1) * 8].clone().requires_grad_(True)
+        hr = hid.clone().requires_grad_(True)
+        logits = c_concat(c_identity(hr, group) @ w_r.t(), group)
+        logits.backward(dlog)
+        hf, wf = hid.clone().requires_grad_(True), wte.clone().requires_grad_(True)
+        ref = hf @ wf.t()
+        ref.backward(dlog)
+        ok = ok and torch.allclose(logits, ref, atol=1e-12) and torch.allclose(hr.grad, hf.grad, atol=1e-11)
+        ok = ok and torch.allclose(w_r.grad, wf.grad[rank * 8:(rank + 1) * 8], atol=1e-11)
         # plain collective plumbing
         t = torch.full((4,), float(rank + 1), dtype=torch.float64)
         group.all_reduce_(t)

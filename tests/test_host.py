@@ -62,8 +62,8 @@ def test_layer_api_surface_on_cpu():
     with pytest.raises(ValueError):
         TransformerDecoderLayer(128, 2, 512, num_partitions=2, device="cpu")   # group size is 1
     assert TransformerDecoderLayer(128, 2, 512, sequence_parallel=True, device="cpu").sequence_parallel
-    with pytest.raises(NotImplementedError):  # sequence parallel is built for the pre-LN layer only
-        TransformerDecoderLayer(128, 2, 512, sequence_parallel=True, normalize_before=False, device="cpu")
+    assert not TransformerDecoderLayer(128, 2, 512, sequence_parallel=True, normalize_before=False,
+                                       device="cpu").normalize_before  # post-LN sequence parallel is built too
     from fleetx_b200.layers import ColumnSequenceParallelLinear, RowSequenceParallelLinear
     with pytest.raises(AssertionError):   # sequence_parallel_utils.py:171-172, :262-263
         ColumnSequenceParallelLinear(16, 32, has_bias=True, gather_output=True, device="cpu")

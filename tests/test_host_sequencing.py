@@ -165,10 +165,21 @@ def _worker(rank, world, port, name, ret, rows=0):
         if m["sequence_parallel"]:
             sl = m["s"] // world
             cut = lambda t: t[:, rank * sl:(rank + 1) * sl].transpose(0, 1).contiguous()  # noqa: E731  [s/n, b, h]
-            y, saved = Fn.decoder_layer_fwd_sp(cut(x), P, M, group)
-            dx, g = Fn.decoder_layer_bwd_sp(cut(dy), saved, P, M, group)
-            check(y, cut(d["out.y"]), "y shard")
-            check(dx, cut(d["out.dx"]), "dx shard")
+            # plain, and every recompute granularity (hybrid_model.py:332-335, 406-408, 537-539 under :475-520)
+            for rc in (None, "full", "full_attn", "core_attn"):
+                M.recompute = rc
+                if m["dropout"] > 0 and rc is not None:  # forward + its re-run in backward each take the attention mask
+                    emu_ops.ATTN_KEEP_QUEUE.extend([d[f"mask.attn.{rank}"]] * 2)
+                y, saved = Fn.decoder_layer_fwd_sp(cut(x), P, M, group)
+                kept = Fn.prune_saved_sp(saved, M)
+                if rc == "full":
+                    assert set(kept) == {"x", "shape", "sp"}
+                del saved
+                dx, g = Fn.decoder_layer_bwd_sp(cut(dy), Fn.rebuild_saved_sp(kept, P, M, group), P, M, group)
+                check(y, cut(d["out.y"]), f"y shard ({rc})")
+                check(dx, cut(d["out.dx"]), f"dx shard ({rc})")
+                check_grads(g, d, m, rank)
+            M.recompute = None
         else:
             y, saved = Fn.decoder_layer_fwd(x, P, M, group)
             assert bool(saved.get("rows")) == bool(rows) and saved.get("chunks", 0) == (min(rows, x.shape[0]) if rows else 0)
@@ -186,6 +197,7 @@ def _worker(rank, world, port, name, ret, rows=0):
 
 @pytest.mark.parametrize("name,world,rows", [("ref_layer_tp2", 2, 0), ("ref_layer_tp4", 4, 0),
                                              ("ref_layer_sp2", 2, 0), ("ref_layer_sp4", 4, 0),
+                                             ("ref_layer_postln_tp2", 2, 0), ("ref_layer_postln_sp2", 2, 0),
                                              ("ref_layer_tp2", 2, 1), ("ref_layer_tp4", 4, 1),
                                              ("ref_layer_tp2", 2, 2), ("ref_layer_tp4", 4, 2)])
 def test_tensor_and_sequence_parallel_sequencing_over_gloo(name, world, rows):

@@ -74,3 +74,25 @@ def test_cached_layer_api():
     assert y.shape == x.shape and c1.k.shape == (1, 2, 8, 64)
     with pytest.raises(NotImplementedError):
         layer.self_attn.gen_cache(x, type=MultiHeadAttention.StaticCache)
+
+
+def test_decoding_twice_from_one_cache_does_not_clobber_the_other_branch():
+    """Beam / speculative decoding: two different tokens appended to the SAME earlier Cache. The reference concatenates
+    into fresh tensors (hybrid_model.py:178-184), so both branches keep their own rows; here only the newest view of
+    a buffer may grow in place, the second branch gets a copy."""
+    from fleetx_b200.layers import TransformerDecoderLayer
+
+    torch.manual_seed(0)
+    layer = TransformerDecoderLayer(128, 2, 512)
+    layer.eval()
+    prompt = torch.randn(1, 8, 128).to(torch.bfloat16).cuda()
+    ta = torch.randn(1, 1, 128).to(torch.bfloat16).cuda()
+    tb = torch.randn(1, 1, 128).to(torch.bfloat16).cuda()
+    _, c1 = layer(prompt, use_cache=True, cache=layer.gen_cache(prompt))
+    ya, ca = layer(ta, use_cache=True, cache=c1)     # grows c1's buffer in place
+    ka = ca.k.clone()
+    yb, cb = layer(tb, use_cache=True, cache=c1)     # same parent: must not write into ca's row 8
+    assert torch.equal(ca.k, ka) and not torch.equal(cb.k[:, :, 8], ca.k[:, :, 8])
+    assert torch.equal(cb.k[:, :, :8], ca.k[:, :, :8]) and ca.k.shape == cb.k.shape == (1, 2, 9, 64)
+    ya2, _ = layer(ta, use_cache=True, cache=c1)     # and branch a again gives branch a's answer
+    assert torch.equal(ya2, ya)

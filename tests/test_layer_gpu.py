@@ -116,6 +116,31 @@ def test_layer_eval_mode_and_recompute_determinism():
     assert not torch.equal(y1, y_other)
 
 
+def test_layer_with_the_models_explicit_causal_mask():
+    """The explicit-mask branch (hybrid_model.py:273-275) with the mask the reference's model builds in eval
+    (-1e4 * triu(1), :716-726): served by the fused causal kernel, compared with the oracle's softmax(product + mask);
+    BASELINE configs[0]'s shape. Any other additive mask is refused."""
+    from selfcheck import layer_from_oracle_params
+
+    b, s, h, nh, f = 1, 1024, 1024, 16, 4096
+    cfg = O.LayerConfig(d_model=h, nhead=nh, dim_feedforward=f, dropout=0.0)
+    params, x, dy = _setup(cfg, b, s)
+    mask = torch.triu(torch.ones(s, s) * -1e4, diagonal=1)
+    y_ref, dx_ref, g_ref = O.decoder_layer_fwd_bwd(x.float(), dy.float(), params, cfg, None, attn_mask=mask)
+    layer = layer_from_oracle_params(cfg, params)
+    layer.train()
+    xd = x.cuda().requires_grad_(True)
+    y = layer(xd, tgt_mask=mask.cuda())
+    y.backward(dy.cuda())
+    _check(y, xd.grad, {n: p.grad for n, p in layer.named_parameters()}, y_ref, dx_ref, g_ref)
+    y4 = layer(x.cuda(), tgt_mask=mask.cuda()[None, None])  # [1, 1, s, s] as the model broadcasts it
+    assert torch.equal(y4, y)
+    bad = mask.clone()
+    bad[5, 2] = -1e4  # a padding-style entry below the diagonal
+    with pytest.raises(NotImplementedError):
+        layer(x.cuda(), tgt_mask=bad.cuda())
+
+
 def test_standalone_parallel_linears_and_attention_module():
     from fleetx_b200.layers import ColumnParallelLinear, MultiHeadAttention, RowParallelLinear
 

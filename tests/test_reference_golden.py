@@ -30,7 +30,7 @@ TOL = 1e-10
 HAVE_REFERENCE = os.path.isfile("/root/reference/ppfleetx/models/language_model/gpt/dygraph/hybrid_model.py")
 
 LAYER_FIXTURES = ["ref_layer_n1", "ref_layer_n1_nodrop", "ref_layer_postln_n1", "ref_layer_tp2", "ref_layer_tp4",
-                  "ref_layer_sp2", "ref_layer_sp4"]
+                  "ref_layer_sp2", "ref_layer_sp4", "ref_layer_postln_tp2", "ref_layer_postln_sp2"]
 MODEL_FIXTURES = ["ref_model_n1", "ref_model_tp2", "ref_model_sp2"]
 
 

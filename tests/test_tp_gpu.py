@@ -83,7 +83,9 @@ def _worker(rank, world, port, ret, kind):
         # the layer, twice (the second call reuses the symmetric buffer and the epoch flags), every tensor against
         # the oracle's simulation of `world` mp ranks; sequence_parallel: this rank feeds / returns its [s/n, b, h]
         # shard and the oracle is the plain layer with shard-sized hidden masks repeated over the ranks
-        errs = layer_parity(group, b, s, h, nh, ffn, dropout=0.1, seed=1024, sequence_parallel=kind in ("sp", "sp_nccl"),
+        errs = layer_parity(group, b, s, h, nh, ffn, dropout=0.1, seed=1024, sequence_parallel=kind.startswith("sp"),
+                            normalize_before="postln" not in kind,
+                            recompute={"sp_recompute": "full", "sp_recompute_attn": "core_attn"}.get(kind),
                             device=f"cuda:{rank}", repeats=2)
         worst = max(errs.values())
         if kind == "native":
@@ -117,8 +119,9 @@ def _worker(rank, world, port, ret, kind):
         dist.destroy_process_group()
 
 
-KINDS = ["nccl", "symmetric", "symmetric_v0", "symmetric_v1", "native", "sp", "sp_nccl", "model", "model_sp"]
-CASES = [(2, k) for k in KINDS] + [(w, k) for w in (4, 8) for k in ("symmetric", "symmetric_v1", "native", "sp", "model", "model_sp")]
+KINDS = ["nccl", "symmetric", "symmetric_v0", "symmetric_v1", "native", "sp", "sp_nccl", "model", "model_sp",
+         "postln", "sp_postln", "sp_recompute", "sp_recompute_attn"]
+CASES = [(2, k) for k in KINDS] + [(w, k) for w in (4, 8) for k in ("symmetric", "symmetric_v1", "native", "sp", "model", "model_sp", "sp_postln", "sp_recompute")]
 
 
 @pytest.mark.parametrize("world,kind", CASES)
@@ -128,7 +131,9 @@ def test_tp_layer_matches_oracle(world, kind):
     behind every allreduce on its own rows); "symmetric_v0" / "_v1": the replicated order over the fused allreduce
     kernel of csrc/comm.cu, forced to its multicast resp. owner-keeps variant; "native": additionally the whole-layer C entry points (csrc/layer.cu) driving that kernel
     through an fx_tp_comm; "sp" / "sp_nccl": sequence_parallel=True with the library's all-gather / reduce-scatter
-    kernel, resp. torch.distributed collectives + permutes; "model" / "model_sp": the whole model."""
+    kernel, resp. torch.distributed collectives + permutes; "model" / "model_sp": the whole model; "postln": the
+    post-LN layer (normalize_before=False); "sp_postln", "sp_recompute" (granularity full), "sp_recompute_attn"
+    (core_attn): sequence parallel combined with post-LN resp. activation recompute."""
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
     ctx = mp.get_context("spawn")

@@ -333,6 +333,8 @@ def main():
     layer_case("ref_layer_tp4", c, n=4)
     layer_case("ref_layer_sp2", c, n=2, sp=True)
     layer_case("ref_layer_sp4", c, n=4, sp=True)
+    layer_case("ref_layer_postln_tp2", c, n=2, pre_ln=False)
+    layer_case("ref_layer_postln_sp2", c, n=2, sp=True, pre_ln=False)
     model_case("ref_model_n1", c)
     model_case("ref_model_tp2", c, n=2)
     model_case("ref_model_sp2", c, n=2, sp=True)
