@@ -9,7 +9,7 @@ NG=$(nvidia-smi -L 2>/dev/null | wc -l)
 FILTER="${1:-}"
 python __graft_entry__.py > gpurun_out/build_n$NG.log 2>&1
 if [ -n "$FILTER" ]; then
-  timeout 900 python -m pytest tests/test_tp_gpu.py -x -q -m gpu -k "$FILTER" > gpurun_out/tests_tp_n$NG.log 2>&1
+  FX_TP_TESTS=all timeout 900 python -m pytest tests/test_tp_gpu.py -x -q -m gpu -k "$FILTER" > gpurun_out/tests_tp_n$NG.log 2>&1
   echo "pytest rc=$?" >> gpurun_out/tests_tp_n$NG.log
 fi
 PORT=29531
