@@ -107,3 +107,54 @@ def test_lr_scheduler_matches_the_reference_schedule():
     assert abs(sch.get_lr() - (1e-5 + 0.5 * (math.cos(math.pi) + 1) * 4e-5)) < 1e-12
     sch.step(360001)
     assert sch.get_lr() == 1e-5
+
+
+def test_split_k_proposal_and_cta_budget_are_host_arithmetic():
+    """fx_gemm_splitk_splits / fx_set_sm_budget touch no device memory: the weight-gradient shapes of mp 8 get a
+    split, the 1-GPU shapes do not; the budget is per thread and returns the previous value."""
+    from fleetx_b200 import _lib
+
+    lib = _lib.lib()
+    try:
+        one = [lib.fx_gemm_splitk_splits(*shp) for shp in ((2048, 8192, 16384), (8192, 2048, 16384), (2048, 6144, 16384))]
+    except Exception:  # pragma: no cover
+        pytest.skip("needs the CUDA runtime's device count")
+    assert one == [1, 1, 1]                                   # >= one wave of tiles: no split
+    assert lib.fx_gemm_splitk_splits(256, 2048, 16384) > 1    # dW_out at mp 8: 16 tiles
+    assert lib.fx_gemm_splitk_splits(2048, 768, 16384) > 1    # dW_qkv at mp 8: 48 tiles
+    assert lib.fx_gemm_splitk_splits(256, 2048, 2048) == 1    # short K: not worth the partial tiles
+    assert lib.fx_gemm_splitk_workspace_bytes(256, 2048, 4) == 4 * 256 * 2048 * 4
+    assert lib.fx_gemm_splitk_workspace_bytes(256, 2048, 1) == 0
+    old = lib.fx_set_sm_budget(100)
+    assert lib.fx_set_sm_budget(old) == 100
+
+
+def test_chunk_helpers_and_causal_mask_acceptance():
+    from fleetx_b200 import functional as Fn
+    from fleetx_b200.layers import accept_causal_mask
+
+    buf = torch.arange(24, dtype=torch.float32).view(6, 4)
+    parts = [buf[0:2], buf[2:4], buf[4:6]]
+    cat = Fn._rows_cat(parts)
+    assert cat.data_ptr() == buf.data_ptr() and torch.equal(cat, buf)          # back-to-back views: no copy
+    assert torch.equal(Fn._rows_cat([buf[0:2], buf[4:6]]), torch.cat([buf[0:2], buf[4:6]]))
+    lse = torch.arange(2 * 3 * 5, dtype=torch.float32).view(2, 3, 5)
+    assert torch.equal(Fn._batch_slice(lse, 2, 1, 1), lse[1:2])
+    flat = torch.arange(8, dtype=torch.uint8)
+    assert torch.equal(Fn._batch_slice(flat, 2, 1, 1), flat[4:])
+    assert Fn._batch_slice(["a", "b"], 2, 1, 1) == "b" and Fn._batch_slice(None, 2, 0, 1) is None
+
+    class G:
+        pipeline_chunks = 2
+    assert Fn._chunks(8, G()) == 2 and Fn._chunks(3, G()) == 1 and Fn._chunks(8, object()) == 1
+
+    s = 6
+    causal = torch.triu(torch.ones(s, s) * -1e4, diagonal=1)
+    accept_causal_mask(None, s, "t")
+    accept_causal_mask(causal, s, "t")
+    accept_causal_mask(causal[None, None], s, "t")
+    bad = causal.clone()
+    bad[3, 1] = -1e4
+    for m in (bad, causal[:, :4], torch.zeros(s, s)):
+        with pytest.raises(NotImplementedError):
+            accept_causal_mask(m, s, "t")

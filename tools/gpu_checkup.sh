@@ -14,12 +14,5 @@ timeout 200 python tools/bench_native.py > gpurun_out/bench_native.log 2>&1
 nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -o tools/micro/membound_v2 tools/micro/membound_v2.cu -ldl \
   > gpurun_out/membound_build.log 2>&1 \
   && timeout 120 tools/micro/membound_v2 fleetx_b200/lib/libfleetx_b200.so 16384 2048 > gpurun_out/membound_v2.log 2>&1
-# multi-GPU boxes only (gpurun --gpus N): the per-source arrival signalling prototype (tools/micro/ag_pipeline.cu)
-NG=$(nvidia-smi -L 2>/dev/null | wc -l)
-if [ "$NG" -ge 2 ]; then
-  nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -o tools/micro/ag_pipeline tools/micro/ag_pipeline.cu \
-    > gpurun_out/ag_build.log 2>&1 \
-    && timeout 120 tools/micro/ag_pipeline "$NG" 8 16 10 > gpurun_out/ag_pipeline.log 2>&1
-fi
 timeout 200 python tools/bench_ops.py > gpurun_out/bench_ops.log 2>&1
 tail -3 gpurun_out/tests_gpu.log; cat gpurun_out/bench_native.log gpurun_out/membound_v2.log 2>/dev/null | tail -20
