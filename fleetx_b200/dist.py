@@ -536,6 +536,9 @@ class SymmetricTPGroup(TorchDistGroup):
             dst.copy_(t, non_blocking=True)
             done = torch.cuda.Event()
             done.record(self._copy_stream)
+        # dst was allocated on the caller's stream: if it is dropped before anyone waits for the copy (a forward
+        # without backward), the allocator must not hand its memory out while the copy stream still writes it
+        dst.record_stream(self._copy_stream)
         self._b0_copies.append(done)
         self._kept[dst.data_ptr()] = done
 
