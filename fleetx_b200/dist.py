@@ -543,9 +543,10 @@ class SymmetricTPGroup(TorchDistGroup):
         self._kept[dst.data_ptr()] = done
 
     def wait_kept(self, t: torch.Tensor) -> torch.Tensor:
-        ev = self._kept.pop(t.data_ptr(), None)
-        if ev is not None:
-            torch.cuda.current_stream().wait_event(ev)
+        lo = t.data_ptr()
+        hi = lo + t.numel() * t.element_size()
+        for ptr in [k for k in self._kept if lo <= k < hi]:  # every copy that landed inside t (one per batch chunk)
+            torch.cuda.current_stream().wait_event(self._kept.pop(ptr))
         return t
 
     def fwd_out_start(self, part, bias, residual_own, p, seed, offset, mask_in, drop_off=0):
